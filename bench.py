@@ -1,0 +1,308 @@
+#!/usr/bin/env python
+"""bench.py -- FM train examples/sec on synthetic Criteo-shaped data (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--dist uniform|zipf]
+
+A step = one pass of the whole hot path (parse -> unique -> lookup -> score -> loss ->
+grad -> sparse Adagrad) over one batch of synthetic text (cfg2: 39 fields, 2^24 hashed
+vocab, factor 16, batch 65536 per GPU).  Prints ONE JSON line (see the task contract):
+value = device-resident throughput, e2e = through the host-buffer API with the H2D copy
+of each batch's text and the D2H read of its loss inside the timed region, roofline =
+the dominant kernel against the measured HBM peak, cpu_baseline = the oracle's
+faithful-threaded restatement of the reference CPU ops on this box's host cores.
+
+--impl reference times only the CPU restatement (the TF-hosted original cannot run here).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import bench_data  # noqa: E402
+
+CFG = dict(vocab=1 << 24, factor_num=16, batch=65536, nnz_per_line=39, hash_feature_id=True,
+           loss_type="logistic", learning_rate=0.01, init_acc=0.1, factor_lambda=1e-5, bias_lambda=1e-5)
+METRIC, UNIT = "fm_train_examples_per_sec", "examples/s"
+STAGES = ["parse_count", "parse_fill", "unique", "lookup", "score", "loss", "grad", "adagrad"]
+# my kernels per step: count, poses scan, fill | insert, rank scan, finish | lookup | score, reduce |
+# loss, reduce | zero rows, grad | adagrad
+KERNELS_PER_STEP = 14
+
+
+def measured_peak_gbs():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+def algorithmic_bytes(n, u, b, k, text_bytes):
+    """compulsory bytes per stage (fp32; ids i64 at the parser output)"""
+    rb = 4 * (k + 1)
+    return {
+        "parse": text_bytes + 12 * n + 8 * b,          # count + fill together
+        "unique": 12 * n + 8 * u + 4 * (b + 1),
+        "lookup": 8 * u + 2 * u * rb,
+        "score": 8 * n + 4 * (b + 1) + u * rb + 4 * b,
+        "loss": 16 * b,
+        "grad": 8 * n + 4 * (b + 1) + 4 * b + 2 * u * rb,
+        "adagrad": 8 * u + 5 * u * rb,
+    }
+
+
+class ClockSampler(threading.Thread):
+    """samples SM clock + throttle reasons of one GPU while the timed region runs (NVML)"""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self._stop_evt = index, [], set(), None, threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+        }
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.05)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def cpu_baseline(steps, warmup, sample_lines, dist, threads):
+    """the oracle's faithful-threaded restatement of the reference CPU ops, one step per batch"""
+    from oracle import oracle as O
+    k, vocab = CFG["factor_num"], CFG["vocab"]
+    rng = np.random.default_rng(0)
+    blocks = (rng.random((1, vocab + 1, k + 1), dtype=np.float32) - 0.5) * 0.02
+    acc = np.full_like(blocks, np.float32(CFG["init_acc"]))
+    batches = [bench_data.criteo_batch(sample_lines, 100 + i, dist)[:2] for i in range(min(2, steps + warmup))]
+    stage = np.zeros(7)
+    total = 0.0
+    for i in range(warmup + steps):
+        text, off = batches[i % len(batches)]
+        t0 = time.perf_counter()
+        _, ts, _ = O.train_step_faithful(text, off, vocab, True, 1, k, blocks, acc, None, CFG["loss_type"],
+                                         CFG["factor_lambda"], CFG["bias_lambda"], CFG["learning_rate"],
+                                         CFG["batch"], threads)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            total += dt
+            stage += ts
+    names = ["parse", "unique", "lookup", "score", "loss", "grad", "adagrad"]
+    return {"value": steps * sample_lines / total, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": "%d steps of %d-line cfg2 batches (%s ids), all stages, oracle faithful-threaded build"
+                      % (steps, sample_lines, dist),
+            "ms_per_step": 1e3 * total / steps,
+            "stage_ms": {n: round(1e3 * s / steps, 3) for n, s in zip(names, stage)}}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path (restated; kind 'port')"""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    sample = 16384
+    base = cpu_baseline(args.steps, max(args.warmup, 1), sample, args.dist, threads)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": base["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, 1, sample),
+        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "stage_ms")},
+        "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args, n_gpus, batch):
+    return {"workload": "cfg2: synthetic Criteo shape, 39 fields, 2^24 hashed vocab, factor 16, "
+                        "batch %d per GPU, logistic loss, Adagrad(0.01, 0.1), lambda 1e-5" % batch,
+            "ids": args.dist, "batch_per_gpu": batch, "global_batch": batch * n_gpus, "factor_num": CFG["factor_num"],
+            "vocabulary_size": CFG["vocab"], "distinct_batches": args.batches,
+            "l2_policy": "inputs larger than L2: %d distinct text batches (~37 MB each) + random rows of a "
+                         "1.3 GB table / accumulator per step" % args.batches,
+            "parallelism": "single GPU" if n_gpus == 1 else "vocab-sharded x%d (id %% G), NCCL all-to-all" % n_gpus}
+
+
+def run_ours(args):
+    import torch
+    from fast_tffm_b200.fm_model import Model
+    from fast_tffm_b200.fm_ops import PackedLines
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        from bench_sharded import run_sharded  # vocab-sharded path
+        return run_sharded(args, CFG, workload_config)
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    b, k = CFG["batch"], CFG["factor_num"]
+    m = Model(vocabulary_size=CFG["vocab"], factor_num=k, batch_size=b, hash_feature_id=True,
+              loss_type=CFG["loss_type"], learning_rate=CFG["learning_rate"],
+              adagrad_init_accumulator=CFG["init_acc"], factor_lambda=CFG["factor_lambda"],
+              bias_lambda=CFG["bias_lambda"]).build(dev, seed=0, max_nnz_per_line=CFG["nnz_per_line"])
+
+    host, devb = [], []
+    for i in range(args.batches):
+        text, off, nnz = bench_data.criteo_batch(b, 1 + i, args.dist)
+        ht = torch.from_numpy(bench_data.pad16(text)).pin_memory()
+        ho = torch.from_numpy(off).pin_memory()
+        host.append(PackedLines(ht, ho))
+        devb.append(PackedLines(ht.to(dev), ho.to(dev)))
+    text_bytes = int(host[0].offsets[-1])
+
+    # ---- device-resident throughput (value) + per-stage CUDA events ----------------
+    for i in range(args.warmup):
+        m.train_step_async(devb[i % len(devb)])
+    torch.cuda.synchronize()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(STAGES) + 1)] for _ in range(args.steps)]
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    torch.cuda.synchronize()
+    for s in range(args.steps):
+        cursor = [0]
+        ev[s][0].record()
+
+        def mark(name, evs=ev[s], cursor=cursor):
+            cursor[0] += 1
+            evs[cursor[0]].record()
+        bufs = m.train_step_async(devb[s % len(devb)], mark=mark)
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    total_ms = ev[0][0].elapsed_time(ev[-1][-1])
+    stage_ms = {n: sum(ev[s][i].elapsed_time(ev[s][i + 1]) for s in range(args.steps)) / args.steps
+                for i, n in enumerate(STAGES)}
+    st = bufs["status"].cpu()
+    assert int(st[0]) == -1, "parse error in the benchmark data"
+    nnz, n_unique = int(st[1]), int(st[4])
+    loss = float(st[6:8].view(torch.float32)[0])
+    value = args.steps * b / (total_ms * 1e-3)
+
+    # ---- roofline of the dominant stage -------------------------------------------
+    alg = algorithmic_bytes(nnz, n_unique, b, k, text_bytes)
+    merged = dict(stage_ms)
+    merged["parse"] = merged.pop("parse_count") + merged.pop("parse_fill")
+    peak, peak_kind = measured_peak_gbs()
+    per_stage = {n: {"ms": round(ms, 4), "alg_mb": round(alg[n] / 1e6, 2),
+                     "gbs": round(alg[n] / (ms * 1e-3) / 1e9, 1) if ms > 0 else None,
+                     "frac": round(alg[n] / (ms * 1e-3) / 1e9 / peak, 4) if ms > 0 else None}
+                 for n, ms in merged.items()}
+    # the dominant GATHER/SCATTER kernel: the longest of the table-touching stages
+    dom = max(("lookup", "score", "grad", "adagrad", "unique", "parse"), key=lambda n: merged[n])
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": per_stage[dom]["gbs"], "peak": peak,
+                "peak_kind": peak_kind, "unit": "GB/s", "frac": per_stage[dom]["frac"], "traffic": None,
+                "step_frac": round(sum(alg.values()) / (total_ms / args.steps * 1e-3) / 1e9 / peak, 4),
+                "stages": per_stage}
+
+    # ---- end to end through the host-buffer API -----------------------------------
+    h2d = int(host[0].text.numel() + host[0].offsets.numel() * 8)
+    d2h = int(bufs["status"].numel() * 8)
+    stage_in = [PackedLines(torch.empty_like(devb[0].text), torch.empty_like(devb[0].offsets)) for _ in range(2)]
+    copy_stream = torch.cuda.Stream()
+    pinned_status = torch.empty(args.steps + args.warmup, 8, dtype=torch.int64).pin_memory()
+    ready = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
+
+    def e2e_loop(n_steps, base):
+        # double-buffered: the copy of batch s+1 runs on copy_stream while batch s computes
+        main = torch.cuda.current_stream()
+        for s in range(n_steps):
+            slot = s % 2
+            with torch.cuda.stream(copy_stream):
+                if s >= 2:
+                    copy_stream.wait_event(consumed[slot])
+                hb = host[(base + s) % len(host)]
+                stage_in[slot].text.copy_(hb.text, non_blocking=True)
+                stage_in[slot].offsets.copy_(hb.offsets, non_blocking=True)
+                ready[slot].record(copy_stream)
+            main.wait_event(ready[slot])
+            bb = m.train_step_async(stage_in[slot])
+            consumed[slot].record(main)
+            pinned_status[base + s].copy_(bb["status"], non_blocking=True)   # loss + status back to the host
+
+    e2e_loop(args.warmup, 0)
+    torch.cuda.synchronize()
+    t0 = torch.cuda.Event(enable_timing=True)
+    t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    e2e_loop(args.steps, args.warmup)
+    t1.record()
+    torch.cuda.synchronize()
+    e2e_ms = t0.elapsed_time(t1)
+    assert int(pinned_status[-1, 0]) == -1
+    e2e_value = args.steps * b / (e2e_ms * 1e-3)
+
+    base = cpu_baseline(2, 1, 16384, args.dist, os.cpu_count() or 1) if not args.no_cpu_baseline else None
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(args, 1, b),
+        "roofline": roofline,
+        "cpu_baseline": None if base is None else {k_: base[k_] for k_ in ("value", "unit", "cores", "kind", "sample", "stage_ms")},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": e2e_ms / args.steps},
+        "gpu_launches": KERNELS_PER_STEP * args.steps,
+        "clocks": clocks,
+        "final_loss": loss, "nnz_per_step": nnz, "unique_per_step": n_unique,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--dist", default="uniform", choices=["uniform", "zipf"])
+    ap.add_argument("--batches", type=int, default=8, help="distinct synthetic batches cycled through")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,322 @@
+"""Host mirror of the reference's model layer (tffm/fm_model.py) for the hot path.
+
+``Model`` reads the same INI file (sample.cfg; keys of fm_model.py:367-475) and
+strings the ops together the way the reference graph does:
+
+    parse -> unique + cumsum -> embedding_lookup -> fm_scorer            (:69-73, :291-293)
+    loss (+ reg / batch_size) -> fm_grad -> sparse Adagrad               (:311-348)
+
+but as one sync-free chain of C-ABI calls on the current CUDA stream: every
+size that depends on the data (nnz, number of unique ids) stays on the device,
+buffers are allocated once for the configured batch, and the host reads one
+small status block per step.
+
+What is NOT here (TF runtime machinery, out of scope per SURVEY.md section 8):
+queue runners, the gRPC parameter server, SavedModel export, summaries.
+"""
+import configparser
+import glob
+import os
+
+import torch
+
+from . import _lib
+from ._lib import check, load, ptr, stream
+from .fm_ops import FmParseError, PackedLines, pack_lines
+
+
+def _no_mark(name):
+    pass
+
+
+def _ld_for(factor_num):
+    """row stride of the table in floats: K+1 rounded up to 4 so rows are 16-byte aligned"""
+    return (factor_num + 1 + 3) // 4 * 4
+
+
+class Model(object):
+    # defaults of the reference class attributes (tffm/fm_model.py:10-32)
+    vocabulary_size = 8000000
+    vocabulary_block_num = 100
+    factor_num = 10
+    hash_feature_id = False
+    log_dir = None
+    model_file = None
+    batch_size = 50000
+    init_value_range = 0.01
+    factor_lambda = 0.0
+    bias_lambda = 0.0
+    learning_rate = 0.01
+    adagrad_init_accumulator = 0.1
+    num_epochs = 10
+    loss_type = 'mse'
+    save_steps = 100
+    save_summaries_steps = 100
+    queue_size = 10000
+    shuffle_threads = 1
+    tolerance = None
+
+    def __init__(self, config_file=None, **overrides):
+        self.train_files, self.weight_files, self.predict_files = [], [], []
+        self.validation_data_files, self.validation_weight_files = [], []
+        if config_file is not None:
+            self._get_config(config_file)
+        for k, v in overrides.items():
+            if not hasattr(self, k):
+                raise AttributeError("unknown model option %r" % k)
+            setattr(self, k, v)
+        self.table = self.accum = None
+        self.global_step = 0
+        self._bufs = None
+
+    # ---- INI config, same sections / keys as tffm/fm_model.py:367-475 -----------------
+    def _get_config(self, config_file, verbose=True):
+        cfg = configparser.ConfigParser(interpolation=None)
+        if not cfg.read(config_file):
+            raise IOError("cannot read config file %s" % config_file)
+        G, T, P = 'General', 'Train', 'Predict'
+
+        def read(section, option, not_null=True):
+            if not cfg.has_option(section, option):
+                if not_null:
+                    raise ValueError("%s is undefined." % option)
+                return None
+            value = cfg.get(section, option)
+            if verbose:
+                print('  {0} = {1}'.format(option, value))
+            return value
+
+        def read_strs(section, option, not_null=True):
+            val = read(section, option, not_null)
+            return None if val is None else [s.strip() for s in val.split(',')]
+
+        def expand(patterns):
+            return sorted(sum((glob.glob(f) for f in patterns), []))
+
+        if verbose:
+            print('Config: ')
+        self.vocabulary_size = int(read(G, 'vocabulary_size'))
+        self.vocabulary_block_num = int(read(G, 'vocabulary_block_num'))
+        self.factor_num = int(read(G, 'factor_num'))
+        self.hash_feature_id = read(G, 'hash_feature_id').strip().lower() == 'true'
+        self.log_dir = read(G, 'log_dir', False)
+        self.model_file = read(G, 'model_file', False)
+        if cfg.has_option(G, 'save_summaries_steps'):
+            self.save_summaries_steps = int(read(G, 'save_summaries_steps'))
+        self.batch_size = int(read(T, 'batch_size'))
+        self.init_value_range = float(read(T, 'init_value_range'))
+        self.factor_lambda = float(read(T, 'factor_lambda'))
+        self.bias_lambda = float(read(T, 'bias_lambda'))
+        self.num_epochs = int(read(T, 'epoch_num'))
+        self.learning_rate = float(read(T, 'learning_rate'))
+        self.adagrad_init_accumulator = float(read(T, 'adagrad.initial_accumulator'))
+        self.loss_type = read(T, 'loss_type').strip().lower()
+        if self.loss_type not in ('logistic', 'mse'):
+            raise ValueError("loss_type must be logistic or mse")
+        v = read(T, 'save_steps', False)
+        if v is not None:
+            self.save_steps = int(v)
+        if cfg.has_option(T, 'queue_size'):
+            self.queue_size = int(read(T, 'queue_size'))
+        if cfg.has_option(T, 'shuffle_threads'):
+            self.shuffle_threads = int(read(T, 'shuffle_threads'))
+        train_files = read_strs(T, 'train_files')
+        self.train_files = expand(train_files)
+        weight_files = read_strs(T, 'weight_files', False)
+        if weight_files is not None:
+            self.weight_files = expand(weight_files)
+            if len(train_files) != len(weight_files):
+                raise ValueError('The numbers of train files and weight files do not match.')
+        vfiles = read_strs(T, 'validation_files', False)
+        if vfiles is not None:
+            self.validation_data_files = expand(vfiles)
+            self.tolerance = float(read(T, 'tolerance'))
+        vwfiles = read_strs(T, 'validation_weight_files', False)
+        if vwfiles is not None:
+            self.validation_weight_files = expand(vwfiles)
+            if vfiles is None or len(vfiles) != len(vwfiles):
+                raise ValueError('The numbers of validation data files and validation weight files do not match.')
+        pfiles = read_strs(P, 'predict_files', False)
+        self.predict_files = expand(pfiles) if pfiles is not None else []
+
+    # ---- the vocabulary table ------------------------------------------------------
+    def build(self, device=None, init_table=None, seed=None, max_nnz_per_line=None):
+        """Allocates table + Adagrad accumulator in HBM.  The table is ONE array
+        [vocabulary_size, ld] (row = feature id, ld = K+1 rounded up to 4 floats); the
+        reference's vocabulary_block_num blocks (fm_model.py:269-284) are a relabelling
+        applied when checkpoints are written (blocks_state / load_blocks_state).
+        init: uniform(-init_value_range, init_value_range) (:278-281) or `init_table`
+        ([vocabulary_size, K+1], for parity runs)."""
+        load()
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        self.device = torch.device(device)
+        k, v = self.factor_num, self.vocabulary_size
+        self.ld = _ld_for(k)
+        self.table = torch.zeros(v, self.ld, dtype=torch.float32, device=self.device)
+        if init_table is not None:
+            self.table[:, :k + 1] = torch.as_tensor(init_table, dtype=torch.float32)[:, :k + 1].to(self.device)
+        else:
+            gen = torch.Generator(device=self.device)
+            if seed is not None:
+                gen.manual_seed(seed)
+            self.table[:, :k + 1].uniform_(-self.init_value_range, self.init_value_range, generator=gen)
+        self.accum = torch.full_like(self.table, self.adagrad_init_accumulator)
+        self._bufs = None
+        self._max_nnz_per_line = max_nnz_per_line
+        return self
+
+    def _buffers(self, n_lines, text_bytes):
+        """per-batch device buffers, allocated once and grown on demand"""
+        # every feature costs at least two bytes (" x"), so nnz <= text_bytes / 2
+        cap = int(text_bytes // 2 + 1)
+        if self._max_nnz_per_line:
+            cap = min(cap, int(n_lines * self._max_nnz_per_line))
+        b = self._bufs
+        if b is not None and b["lines"] >= n_lines and b["cap"] >= cap:
+            return b
+        lib, dev = load(), self.device
+        lines = max(n_lines, b["lines"] if b else 0)
+        cap = max(cap, b["cap"] if b else 0)
+        f32, i32, i64 = torch.float32, torch.int32, torch.int64
+        b = dict(
+            lines=lines, cap=cap,
+            labels=torch.empty(lines, dtype=f32, device=dev), sizes=torch.empty(lines, dtype=i32, device=dev),
+            poses=torch.empty(lines + 1, dtype=i32, device=dev), ids=torch.empty(cap, dtype=i64, device=dev),
+            vals=torch.empty(cap, dtype=f32, device=dev), ori=torch.empty(cap, dtype=i64, device=dev),
+            local=torch.empty(cap, dtype=i32, device=dev), rows=torch.empty(cap, self.ld, dtype=f32, device=dev),
+            grad=torch.empty(cap, self.ld, dtype=f32, device=dev), pred=torch.empty(lines, dtype=f32, device=dev),
+            pred_grad=torch.empty(lines, dtype=f32, device=dev),
+            # [first_error, nnz, n_lines, reserved] (fm_parse_status), n_unique, then loss and reg as f32 bits
+            status=torch.zeros(8, dtype=i64, device=dev),
+            ws_parse=_lib.workspace(lib.fm_parse_workspace(lines), dev),
+            ws_unique=_lib.workspace(lib.fm_unique_workspace(cap), dev),
+            ws_score=_lib.workspace(lib.fm_score_workspace(lines), dev),
+            ws_loss=_lib.workspace(lib.fm_loss_workspace(lines), dev),
+        )
+        b["scalars"] = b["status"][6:8].view(torch.float32)  # [loss, -, reg, -]
+        self._bufs = b
+        return b
+
+    def _forward(self, packed, b, mark=_no_mark):
+        """parse -> unique -> lookup -> score, all sizes device-resident.
+        mark(name) is called after each stage is enqueued (bench.py records CUDA events there)."""
+        lib, st = load(), stream()
+        n_lines = packed.n_lines
+        k, hashed = self.factor_num, int(self.hash_feature_id)
+        status, nnz_dev, nuniq_dev = ptr(b["status"]), _off(b["status"], 1), _off(b["status"], 4)
+        check(lib.fm_parse_count(ptr(packed.text), ptr(packed.offsets), n_lines, self.vocabulary_size, hashed,
+                                 ptr(b["sizes"]), ptr(b["poses"]), status, ptr(b["ws_parse"]),
+                                 b["ws_parse"].numel(), st), "fm_parse_count")
+        mark("parse_count")
+        check(lib.fm_parse_fill(ptr(packed.text), ptr(packed.offsets), n_lines, self.vocabulary_size, hashed,
+                                ptr(b["poses"]), ptr(b["labels"]), ptr(b["ids"]), ptr(b["vals"]), b["cap"], status,
+                                st), "fm_parse_fill")
+        mark("parse_fill")
+        check(lib.fm_unique(ptr(b["ids"]), b["cap"], nnz_dev, ptr(b["ori"]), ptr(b["local"]), nuniq_dev,
+                            ptr(b["ws_unique"]), b["ws_unique"].numel(), st), "fm_unique")
+        mark("unique")
+        check(lib.fm_lookup(ptr(self.table), self.ld, ptr(b["ori"]), b["cap"], nuniq_dev, k, ptr(b["rows"]), self.ld,
+                            st), "fm_lookup")
+        mark("lookup")
+        check(lib.fm_score(ptr(b["local"]), ptr(b["rows"]), self.ld, ptr(b["vals"]), ptr(b["poses"]), n_lines, k,
+                           self.factor_lambda, self.bias_lambda, ptr(b["pred"]), _off(b["status"], 7),
+                           ptr(b["ws_score"]), b["ws_score"].numel(), st), "fm_score")
+        mark("score")
+
+    def train_step_async(self, packed: PackedLines, weights=None, mark=_no_mark):
+        """One training step on a device-resident batch; enqueues only.  Returns the
+        buffers dict: status[0] parse status word, status[1] nnz, status[4] n_unique,
+        scalars[0] loss, scalars[2] reg."""
+        b = self._buffers(packed.n_lines, packed.text.numel())
+        lib, st = load(), stream()
+        n_lines, k = packed.n_lines, self.factor_num
+        self._forward(packed, b, mark)
+        nuniq_dev = _off(b["status"], 4)
+        check(lib.fm_loss_grad(ptr(b["pred"]), ptr(b["labels"]), ptr(weights), n_lines,
+                               _lib.LOSS_KIND[self.loss_type], _off(b["status"], 6), ptr(b["pred_grad"]),
+                               ptr(b["ws_loss"]), b["ws_loss"].numel(), st), "fm_loss_grad")
+        mark("loss")
+        # objective = loss + reg_score / batch_size with the CONFIGURED batch size (fm_model.py:345-347)
+        check(lib.fm_grad(ptr(b["local"]), ptr(b["rows"]), self.ld, ptr(b["vals"]), ptr(b["poses"]), n_lines, k,
+                          self.factor_lambda, self.bias_lambda, ptr(b["pred_grad"]), 1.0 / self.batch_size, None,
+                          b["cap"], nuniq_dev, ptr(b["grad"]), st), "fm_grad")
+        mark("grad")
+        check(lib.fm_sparse_adagrad(ptr(self.table), ptr(self.accum), self.ld, ptr(b["ori"]), b["cap"], nuniq_dev, k,
+                                    ptr(b["grad"]), self.ld, self.learning_rate, ptr(b["status"]), st),
+              "fm_sparse_adagrad")
+        mark("adagrad")
+        self.global_step += 1
+        return b
+
+    def train_step(self, lines, weights=None):
+        """lines: list of str / PackedLines (host or device); weights: per-example floats or None.
+        Returns the batch loss (python float); raises FmParseError like the op would."""
+        packed, weights = self._to_device(lines, weights)
+        b = self.train_step_async(packed, weights)
+        host = b["status"].cpu()
+        _raise(host, packed)
+        return float(host[6:8].view(torch.float32)[0])
+
+    def predict_async(self, packed: PackedLines):
+        b = self._buffers(packed.n_lines, packed.text.numel())
+        self._forward(packed, b)
+        return b
+
+    def predict(self, lines):
+        """raw pred_score per line (no sigmoid), as tffm/fm_model.py:128-142"""
+        packed, _ = self._to_device(lines, None)
+        b = self.predict_async(packed)
+        host = b["status"].cpu()
+        _raise(host, packed)
+        return b["pred"][:packed.n_lines].clone()
+
+    def _to_device(self, lines, weights):
+        packed = lines if isinstance(lines, PackedLines) else pack_lines(list(lines))
+        if not packed.text.is_cuda:
+            packed = packed.to(self.device, non_blocking=False)
+        if weights is not None and not (isinstance(weights, torch.Tensor) and weights.is_cuda):
+            weights = torch.as_tensor(weights, dtype=torch.float32).to(self.device)
+        return packed, weights
+
+    # ---- checkpoint layout of the reference: vocab_block_i[id // nb] for id % nb == i ----
+    def blocks_state(self):
+        """{'vocab_block_%d': f32[V//nb+1, K+1], 'vocab_block_%d/Adagrad': ...} on the host"""
+        nb, v, k = self.vocabulary_block_num, self.vocabulary_size, self.factor_num
+        rows = v // nb + 1
+        out = {"global_step": self.global_step}
+        for name, src in (("", self.table), ("/Adagrad", self.accum)):
+            for i in range(nb):
+                blk = torch.zeros(rows, k + 1, dtype=torch.float32)
+                part = src[i::nb, :k + 1].cpu()
+                blk[:part.shape[0]] = part
+                out["vocab_block_%d%s" % (i, name)] = blk
+        return out
+
+    def load_blocks_state(self, state):
+        nb, k = self.vocabulary_block_num, self.factor_num
+        for name, dst in (("", self.table), ("/Adagrad", self.accum)):
+            for i in range(nb):
+                n = dst[i::nb].shape[0]
+                dst[i::nb, :k + 1] = state["vocab_block_%d%s" % (i, name)][:n].to(self.device)
+        self.global_step = int(state.get("global_step", 0))
+
+    def save(self, path):
+        os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+        torch.save(self.blocks_state(), path)
+
+    def restore(self, path):
+        self.load_blocks_state(torch.load(path, map_location="cpu"))
+
+
+def _off(t, index):
+    """device pointer to element `index` of a tensor"""
+    import ctypes
+    return ctypes.c_void_p(t.data_ptr() + index * t.element_size())
+
+
+def _raise(status_host, packed):
+    first = int(status_host[0]) & 0xFFFFFFFFFFFFFFFF
+    if first != _lib.NO_ERROR:
+        kind, line_no = first & 7, first >> 3
+        raise FmParseError(kind, line_no, packed.line(line_no) if line_no < packed.n_lines else "")

@@ -1,0 +1,167 @@
+/*
+ * fm_b200.h -- C ABI of libfm_b200.so: the fast_tffm sparse-FM hot path
+ * (parse -> unique -> lookup -> score -> loss -> grad -> sparse Adagrad) as
+ * hand-written sm_100a CUDA kernels.
+ *
+ * Conventions (they hold for every entry point unless it says otherwise):
+ *   - every pointer is a DEVICE pointer unless named host_*; the caller
+ *     allocates every input, output and workspace; the library never
+ *     allocates, frees or synchronises;
+ *   - work is enqueued on `stream` (a cudaStream_t passed as void*), on the
+ *     device that is current on the calling thread;
+ *   - the return value is 0 on success or a negative FM_E_* code; a message
+ *     for the calling thread's last failure is at fm_last_error();
+ *   - entry points hold no state between calls and may be called from several
+ *     host threads on different streams;
+ *   - "file:line" citations point into the reference tree (douban/fast_tffm).
+ */
+#ifndef FM_B200_H_
+#define FM_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FM_B200_ABI_VERSION 1
+
+enum {
+  FM_OK = 0,
+  FM_E_INVALID = -1, /* bad argument (null pointer, negative size, ...) */
+  FM_E_WORKSPACE = -2, /* workspace too small */
+  FM_E_CUDA = -3,    /* a CUDA runtime call failed; see fm_last_error() */
+  FM_E_LIMIT = -4    /* size beyond what the entry point supports */
+};
+
+/* parser error kinds written to fm_parse_status.error_kind; the text each one
+ * maps to is the reference's (cc/fm_parser_op.cc:70, :77/:88, :90-92, :100) */
+enum {
+  FM_PARSE_OK = 0,
+  FM_PARSE_E_LABEL = 1,    /* "Label could not be read in example: " */
+  FM_PARSE_E_FORMAT = 2,   /* "Invalid format in example: " */
+  FM_PARSE_E_RANGE = 3,    /* "Invalid feature id. Should be in range [0, vocabulary_size)." */
+  FM_PARSE_E_VALUE = 4,    /* "Invalid feature value. " */
+  FM_PARSE_E_CAPACITY = 5  /* not a reference error: feature_ids/vals capacity too small */
+};
+
+enum { FM_LOSS_LOGISTIC = 0, FM_LOSS_MSE = 1 };
+
+/* device-resident result of a parse.  first_error packs (line << 3) | kind of
+ * the FIRST failing line (the reference keeps the first status too,
+ * cc/fm_parser_op.cc:39-45); UINT64_MAX means the batch parsed cleanly. */
+typedef struct {
+  uint64_t first_error;
+  int64_t nnz;      /* total number of features = feature_poses[n_lines] (fm_parse_count) */
+  int64_t n_lines;  /* written by fm_split_lines */
+  int64_t reserved;
+} fm_parse_status;
+#define FM_PARSE_NO_ERROR UINT64_MAX
+#define FM_PARSE_ERROR_KIND(first_error) ((first_error) == UINT64_MAX ? 0 : (int)((first_error) & 7))
+#define FM_PARSE_ERROR_LINE(first_error) ((first_error) == UINT64_MAX ? (int64_t)-1 : (int64_t)((first_error) >> 3))
+
+int fm_abi_version(void);
+const char* fm_last_error(void);
+
+/* ---- P: FmParser, cc/fm_parser_op.cc:8-15 (op), :29-51 (Compute), :58-109 (ParseLine) ----
+ *
+ * Text layout: `text` holds the lines back to back; line i is
+ * text[line_offsets[i] .. line_offsets[i+1]-1), i.e. every line is followed by
+ * exactly one terminator byte ('\n' in a file) that is not part of it.
+ * A NUL inside a line ends it (std::string::c_str(), :65).
+ * `text` must be 16-byte aligned and readable up to the next multiple of 16
+ * past text_bytes (the kernels read whole 16-byte words).
+ */
+
+/* Finds the line starts of a '\n'-separated buffer (the TextLineReader's job,
+ * tffm/fm_model.py:40-43, on the device).  A last line without '\n' is NOT
+ * accepted: the caller appends one.  Writes line_offsets[0..n_lines] and
+ * status->n_lines; at most max_lines lines (more => FM_PARSE_E_CAPACITY). */
+size_t fm_split_lines_workspace(int64_t text_bytes);
+int fm_split_lines(const uint8_t* text, int64_t text_bytes, int64_t* line_offsets,
+                   int64_t max_lines, fm_parse_status* status, void* workspace,
+                   size_t workspace_bytes, void* stream);
+
+/* Pass 1: per line, the label-free feature count -> sizes[n_lines]; then
+ * feature_poses = [0, cumsum(sizes)] (this is tf.cumsum at
+ * tffm/fm_model.py:73 fused into the parser) and status->nnz.
+ * Resets status->first_error first.  Lines the fast counter cannot prove regular are
+ * parsed in full by the sequential scanner. */
+size_t fm_parse_workspace(int64_t n_lines);
+int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, int64_t n_lines,
+                   int64_t vocab_size, int hash_feature_id, int32_t* sizes,
+                   int32_t* feature_poses /* [n_lines+1] */, fm_parse_status* status,
+                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* Pass 2: labels[n_lines], feature_ids[nnz] (int64, as the op's output),
+ * feature_vals[nnz]; `capacity` = elements available in feature_ids/vals. */
+int fm_parse_fill(const uint8_t* text, const int64_t* line_offsets, int64_t n_lines,
+                  int64_t vocab_size, int hash_feature_id, const int32_t* feature_poses,
+                  float* labels, int64_t* feature_ids, float* feature_vals, int64_t capacity,
+                  fm_parse_status* status, void* stream);
+
+/* ---- U1: tf.unique, tffm/fm_model.py:72 ----
+ * ori_ids[U] = distinct ids in order of first occurrence; local_ids[n] = index
+ * of every occurrence into ori_ids; *n_unique (device int64) = U.
+ * n may come from the device: if n_dev != NULL the kernels read *n_dev (<= n)
+ * instead of n, so the parser's nnz need not visit the host. */
+size_t fm_unique_workspace(int64_t n);
+int fm_unique(const int64_t* ids, int64_t n, const int64_t* n_dev, int64_t* ori_ids,
+              int32_t* local_ids, int64_t* n_unique, void* workspace, size_t workspace_bytes,
+              void* stream);
+
+/* ---- L1: tf.nn.embedding_lookup, tffm/fm_model.py:291 ----
+ * The table lives in ONE device array [vocab_rows, table_ld] (row id = feature
+ * id; the reference's vocab_block_b[id / nb] with b = id % nb, :269-284, is a
+ * checkpoint-time relabelling).  out[u, 0..K] = table[ori_ids[u], 0..K]. */
+int fm_lookup(const float* table, int64_t table_ld, const int64_t* ori_ids, int64_t n_unique,
+              const int64_t* n_unique_dev, int64_t factor_num, float* out, int64_t out_ld,
+              void* stream);
+
+/* ---- S: FmScorer, cc/fm_scorer_op.cc:9-17 (op), cc/fm_scorer_op.h:8-140 ----
+ * pred[i] = sum_j b_j x_j + 0.5 sum_k [ (sum_j v_jk x_j)^2 - sum_j (v_jk x_j)^2 ]
+ * reg     = 0.5 lf sum_occ sum_k v^2 + 0.5 lb sum_occ b^2   (per occurrence)
+ * params is [rows, params_ld], column 0 the bias, 1..K the factors.
+ * workspace: fm_score_workspace(batch) bytes (per-block partials of reg). */
+size_t fm_score_workspace(int64_t batch);
+int fm_score(const int32_t* feature_ids, const float* params, int64_t params_ld,
+             const float* feature_vals, const int32_t* feature_poses, int64_t batch,
+             int64_t factor_num, float factor_lambda, float bias_lambda, float* pred_score,
+             float* reg_score, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- LS: loss and d loss / d pred, tffm/fm_model.py:311-316, :324-326 ----
+ * loss = mean_i w_i l(pred_i, y_i); pred_grad_i = w_i l'(pred_i, y_i) / batch.
+ * weights may be NULL (all ones, :66).  loss is a device float. */
+size_t fm_loss_workspace(int64_t batch);
+int fm_loss_grad(const float* pred, const float* labels, const float* weights, int64_t batch,
+                 int loss_kind, float* loss, float* pred_grad, void* workspace,
+                 size_t workspace_bytes, void* stream);
+
+/* ---- G: FmGrad, cc/fm_grad_op.cc:15-24 (op), cc/fm_grad_op.h:23-163 ----
+ * params_grad has the shape of params ([param_rows, params_ld], fm_grad_op.cc:67)
+ * and is zero-filled by this call (fm_grad_op.h:155) before the accumulation.
+ * reg_grad is the op's scalar input; if reg_grad_dev != NULL the kernel reads
+ * the scalar from the device instead (autograd hands it over as a tensor).
+ * If param_rows_dev != NULL only the first *param_rows_dev (<= param_rows) rows
+ * are in use and need clearing. */
+int fm_grad(const int32_t* feature_ids, const float* params, int64_t params_ld,
+            const float* feature_vals, const int32_t* feature_poses, int64_t batch,
+            int64_t factor_num, float factor_lambda, float bias_lambda, const float* pred_grad,
+            float reg_grad, const float* reg_grad_dev, int64_t param_rows,
+            const int64_t* param_rows_dev, float* params_grad, void* stream);
+
+/* ---- A1: TF1 SparseApplyAdagrad as emitted for tffm/fm_model.py:341-348 ----
+ * for u < U: row = ori_ids[u]:  acc[row] += g[u]^2 ; table[row] -= lr g[u] / sqrt(acc[row])
+ * guard (optional, device): the call is a no-op unless *guard == UINT64_MAX.  Pass
+ * &status->first_error so that a batch that failed to parse never touches the table
+ * (in the reference the failed op aborts the step, cc/fm_parser_op.cc:70). */
+int fm_sparse_adagrad(float* table, float* accum, int64_t table_ld, const int64_t* ori_ids,
+                      int64_t n_unique, const int64_t* n_unique_dev, int64_t factor_num,
+                      const float* grad, int64_t grad_ld, float learning_rate, const uint64_t* guard,
+                      void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FM_B200_H_ */

@@ -108,10 +108,23 @@ def strtof_vectors():
         cases.append("%.9g" % f)
         cases.append("%.6g" % f)
         cases.append("%.4f" % (rnd.random() * 20))
+    cases += ["0x1.400001p-148", "0x1.200001p-147", "0x1.400002p-148"]
     out = []
     for s in cases:
         v, n = O.strtof(s)
-        out.append([s, int(np.float32(v).view(np.uint32)), n])
+        bits = int(np.float32(v).view(np.uint32))
+        entry = [s, bits, n]
+        # glibc 2.39's HEX path drops the round bit of a 25-bit mantissa in the subnormal range
+        # (e.g. 0x1.000001p-150 -> 0, IEEE nearest is 2^-149).  The IEEE result is what we pin;
+        # the glibc value is kept beside it for the record.
+        if s.strip().lstrip("+-").lower().startswith("0x") and n == len(s):
+            try:
+                ieee = int(np.float32(float.fromhex(s)).view(np.uint32))
+                if ieee != bits:
+                    entry = [s, ieee, n, {"glibc_2_39_bits": bits}]
+            except (ValueError, OverflowError):
+                pass
+        out.append(entry)
     return out
 
 

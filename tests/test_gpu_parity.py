@@ -1,0 +1,436 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the
+same inputs.  Integer / index outputs are bit-exact; float outputs of the parser
+are bit-exact (they are glibc strtof's bits); scores, losses and gradients are
+held to 1e-5 relative (north_star), with an absolute floor scaled to the size of
+the terms being summed because the second-order term cancels.
+"""
+import random
+
+import numpy as np
+import pytest
+import torch
+
+import bench_data
+from fast_tffm_b200 import fm_ops
+from fast_tffm_b200.fm_model import Model
+from oracle import dense_ref, oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+RTOL = 1e-5
+
+
+def dev(a, dtype=None):
+    return torch.as_tensor(np.asarray(a), dtype=dtype).to(DEV)
+
+
+def bits(t):
+    return t.detach().cpu().numpy().view(np.uint32)
+
+
+def assert_parse_equal(lines, vocab, hashed):
+    exp = O.parse_lines(lines, vocab, hashed)
+    got = fm_ops.fm_parser(lines, vocab, hashed)
+    np.testing.assert_array_equal(bits(got[0]), exp[0].view(np.uint32))
+    np.testing.assert_array_equal(got[1].cpu().numpy(), exp[1])
+    np.testing.assert_array_equal(got[2].cpu().numpy(), exp[2])
+    np.testing.assert_array_equal(bits(got[3]), exp[3].view(np.uint32))
+    return got
+
+
+# ---------------------------------------------------------------- parser ----
+def test_parser_reference_vectors(golden_parser):
+    """port of test/fm_parser_op_test.py:17-46"""
+    g = golden_parser
+    labels, sizes, ids, vals = fm_ops.fm_parser(g["examples"], g["vocab_size"])
+    assert labels.dtype == torch.float32 and sizes.dtype == torch.int32
+    assert ids.dtype == torch.int64 and vals.dtype == torch.float32
+    np.testing.assert_allclose(labels.cpu(), g["labels"])
+    np.testing.assert_array_equal(ids.cpu(), g["feature_ids"])
+    np.testing.assert_allclose(vals.cpu(), np.float32(g["feature_vals"]))
+    np.testing.assert_array_equal(sizes.cpu(), g["sizes"])
+    labels, sizes, ids, vals = fm_ops.fm_parser(g["examples"], g["vocab_size"], True)
+    np.testing.assert_array_equal(ids.cpu(), g["hashed_ids_1_to_10_mod_10000_selfgenerated"])
+    np.testing.assert_array_equal(sizes.cpu(), g["sizes"])
+    np.testing.assert_allclose(vals.cpu(), np.float32(g["feature_vals"]))
+
+
+def test_parser_reference_errors(golden_parser):
+    """port of test/fm_parser_op_test.py:48-81: same message prefixes"""
+    for line, prefix in golden_parser["errors"]:
+        with pytest.raises(ValueError) as e:
+            fm_ops.fm_parser([line], golden_parser["vocab_size"], False)
+        assert str(e.value).startswith(prefix) and str(e.value).endswith(line)
+    with pytest.raises(ValueError, match="Invalid feature id"):
+        fm_ops.fm_parser(["1 10000:1"], 10000)
+    with pytest.raises(ValueError, match="Invalid feature id"):
+        fm_ops.fm_parser(["1 -1:1"], 10000)
+    with pytest.raises(ValueError, match="Label could not be read"):
+        fm_ops.fm_parser(["1 1:1", ""], 10000)
+
+
+def test_parser_first_failing_line_wins():
+    lines = ["1 1:1"] * 700 + ["1 1:x"] + ["1 2:2"] * 300 + ["y 1:1"] + ["1 1:1"] * 50
+    with pytest.raises(fm_ops.FmParseError) as e:
+        fm_ops.fm_parser(lines, 100)
+    assert e.value.line_no == 700 and e.value.kind == 4
+
+
+def test_parser_libc_quirks_match_oracle():
+    cases = [
+        [" 2  7: 3", "1"],                      # whitespace skipping by strtof / strtoll
+        ["1 2:3 ", "1 2:3  ".rstrip() + " "],   # trailing single space
+        ["\t1 \t2:\n3"],
+        [b"1 2:3\x00 garbage"],                 # NUL ends the line
+        ["1 +5:+.5e1 6:-0 7:1e-3 8:0x1p3 9:inf 10:nan 11:-nan(12)"],
+        ["1e2 1:1.5E+1 2:00012.5000"],
+        ["0x10 0:1"],
+        ["1 5"],
+        ["-0 99:1e-46 98:3.4028236e38 97:1.17549435e-38"],
+    ]
+    for lines in cases:
+        assert_parse_equal(lines, 100, False)
+    for lines in [["1  a", "2 a:1 :2 b", "3 a\tb:1"], ["1 ab cd:2.5 ef: 3"], ["0 :1"], ["7 x:y".replace("y", "1")]]:
+        assert_parse_equal(lines, 1000, True)
+
+
+def test_parser_error_kinds_match_oracle():
+    bad = ["", " ", "x", "1 a", "1 2:", "1 2: ", "1 2:3x", "1 2:3 4:", "1 200", "1 -3", "1 2:3\t4", "1,2", "1 2 3:",
+           "1 99999999999999999999", "1:2", "1 2:3:4", "1 2::3", "nan(", "1 0x10", "1\t2"]
+    for line in bad:
+        for hashed in (False, True):
+            try:
+                O.parse_lines([line], 100, hashed)
+                exp = None
+            except O.ParseError as e:
+                exp = e.kind
+            if exp is None:
+                assert_parse_equal([line], 100, hashed)
+            else:
+                with pytest.raises(fm_ops.FmParseError) as e:
+                    fm_ops.fm_parser([line], 100, hashed)
+                assert e.value.kind == exp, (line, hashed)
+
+
+def test_parser_number_vectors_bit_exact(golden_numbers):
+    """every strtof golden string as a label and as a feature value, against glibc's bits"""
+    ok_lines, exp_bits = [], []
+    for s, b, n, *quirk in golden_numbers["strtof"]:
+        if "\x00" in s or n != len(s) or n == 0 or s[0] in " \t\n\r\v\f":
+            continue
+        ok_lines.append("%s 3:%s" % (s, s))
+        exp_bits.append(b)
+    labels, sizes, ids, vals = fm_ops.fm_parser(ok_lines, 10)
+    np.testing.assert_array_equal(bits(labels), np.uint32(exp_bits))
+    np.testing.assert_array_equal(bits(vals), np.uint32(exp_bits))
+    assert sizes.cpu().tolist() == [1] * len(ok_lines)
+
+
+def _random_line(rnd, hashed, vocab):
+    def num():
+        r = rnd.random()
+        if r < 0.3:
+            return "%.4f" % (rnd.random() * 10)
+        if r < 0.5:
+            return "%.6g" % (rnd.gauss(0, 1) * 10 ** rnd.randint(-8, 8))
+        if r < 0.6:
+            return repr(rnd.random() * 10 ** rnd.randint(-40, 38))
+        if r < 0.7:
+            return str(rnd.randint(-5, 5))
+        if r < 0.75:
+            return "%.17g" % rnd.random()
+        if r < 0.8:
+            return rnd.choice(["1e-45", "3e-46", "1e39", "0.0", "-0", "+1", ".5", "5.", "1e+2"])
+        return "%d.%d" % (rnd.randint(0, 99), rnd.randint(0, 999999))
+    toks = []
+    for _ in range(rnd.choice([0, 1, 2, 5, 39, 39, 39, 70])):
+        fid = ("f%x" % rnd.getrandbits(rnd.choice([8, 32, 64, 100]))) if hashed else str(rnd.randrange(vocab))
+        toks.append(fid if rnd.random() < 0.4 else fid + ":" + num())
+    line = " ".join([num()] + toks)
+    if rnd.random() < 0.2:
+        line += " "
+    return line
+
+
+@pytest.mark.parametrize("hashed", [False, True])
+def test_parser_fuzz_bit_exact(hashed):
+    rnd = random.Random(1234 + hashed)
+    lines = [_random_line(rnd, hashed, 1 << 20) for _ in range(3000)]
+    # a few irregular (but valid) lines sprinkled in: they take the sequential path
+    for i in range(0, 3000, 97):
+        lines[i] = lines[i].replace(" ", "  ", 1) if not hashed else lines[i].replace(":", ": ", 1)
+    assert_parse_equal(lines, 1 << 20, hashed)
+
+
+def test_parser_long_and_ragged_lines():
+    lines, _ = bench_data.ragged_batch(64, 5, max_nnz=512)
+    lines.append(b"1 " + b" ".join(b"%d:%d" % (i, i) for i in range(5000)))   # 5000 features, ~50 KB
+    lines.append(b"0")
+    assert_parse_equal(lines, 1 << 24, False)
+    assert_parse_equal(lines, 1 << 24, True)
+
+
+def test_parser_criteo_excerpt(criteo_lines):
+    lines, _ = criteo_lines
+    assert_parse_equal(lines, 800000, False)
+
+
+def test_parser_empty_batch():
+    labels, sizes, ids, vals = fm_ops.fm_parser([], 10)
+    assert labels.numel() == 0 and sizes.numel() == 0 and ids.numel() == 0 and vals.numel() == 0
+
+
+def test_split_lines_matches_host_offsets():
+    text, off, _ = bench_data.criteo_batch(1000, 3)
+    padded = torch.from_numpy(bench_data.pad16(text)).to(DEV)
+    got = fm_ops.fm_split_lines(padded, text.size, 2000)
+    np.testing.assert_array_equal(got.cpu().numpy(), off)
+    with pytest.raises(ValueError, match="more than"):
+        fm_ops.fm_split_lines(padded, text.size, 999)
+    with pytest.raises(ValueError, match="newline"):
+        fm_ops.fm_split_lines(padded, text.size - 1, 2000)
+
+
+def test_parser_synthetic_cfg2_full_size():
+    """BASELINE config 2 shape at full batch size, bit-exact against the oracle"""
+    text, off, nnz = bench_data.criteo_batch(65536, 0)
+    exp = O.parse(text, off, 1 << 24, True)
+    packed = fm_ops.PackedLines(torch.from_numpy(bench_data.pad16(text)), torch.from_numpy(off))
+    got = fm_ops.fm_parser(packed, 1 << 24, True)
+    assert got[2].numel() == nnz
+    np.testing.assert_array_equal(got[2].cpu().numpy(), exp[2])
+    np.testing.assert_array_equal(bits(got[3]), exp[3].view(np.uint32))
+    np.testing.assert_array_equal(bits(got[0]), exp[0].view(np.uint32))
+    np.testing.assert_array_equal(got[1].cpu().numpy(), exp[1])
+
+
+# ---------------------------------------------------------------- unique ----
+@pytest.mark.parametrize("n,hi", [(0, 10), (1, 10), (1000, 50), (100000, 1 << 24), (300000, 1000), (2555904, 1 << 24)])
+def test_unique_first_occurrence_order(n, hi):
+    rng = np.random.default_rng(n + hi)
+    ids = rng.integers(0, hi, n)
+    ori, local = fm_ops.fm_unique(dev(ids, torch.int64))
+    e_ori, e_local = O.unique(ids)
+    np.testing.assert_array_equal(ori.cpu().numpy(), e_ori)
+    np.testing.assert_array_equal(local.cpu().numpy(), e_local)
+    assert local.dtype == torch.int32 and ori.dtype == torch.int64
+
+
+def test_unique_all_equal_and_large_ids():
+    ids = np.full(5000, (1 << 62) + 12345, np.int64)
+    ori, local = fm_ops.fm_unique(dev(ids))
+    assert ori.cpu().tolist() == [(1 << 62) + 12345] and not local.any()
+
+
+# ------------------------------------------------------ scorer and grad ----
+def _random_case(rng, b, rows, k, ld_pad, max_nnz):
+    sizes = rng.integers(0, max_nnz + 1, b).astype(np.int32)
+    if b > 3:
+        sizes[1] = 0
+        sizes[2] = max_nnz
+    poses = O.poses(sizes)
+    n = int(poses[-1])
+    fids = rng.integers(0, rows, n).astype(np.int32)
+    vals = rng.normal(size=n).astype(np.float32)
+    params = np.zeros((rows, k + 1 + ld_pad), np.float32)
+    params[:, :k + 1] = rng.uniform(-0.3, 0.3, (rows, k + 1))
+    return fids, params, vals, poses
+
+
+def _close(got, exp, scale):
+    """|got - exp| <= RTOL * (|exp| + scale): scale = magnitude of the terms summed"""
+    got, exp = np.asarray(got, np.float64), np.asarray(exp, np.float64)
+    err = np.abs(got - exp)
+    tol = RTOL * (np.abs(exp) + scale)
+    assert (err <= tol).all(), "max err %g, tol there %g" % (err.max(), tol[np.argmax(err - tol)])
+
+
+def test_scorer_reference_case(golden_scorer):
+    """port of test/fm_scorer_op_test.py: pred, reg and d cost / d params (autograd through fm_scorer)"""
+    g = golden_scorer
+    params = dev(np.float32(g["params"])).requires_grad_(True)
+    pred, reg = fm_ops.fm_scorer(g["feature_ids"], params, g["feature_vals"], g["feature_poses"],
+                                 g["factor_lambda"], g["bias_lambda"])
+    assert pred.shape == (2,) and reg.shape == ()
+    np.testing.assert_allclose(pred.detach().cpu(), g["pred"], rtol=RTOL, atol=1e-6)
+    np.testing.assert_allclose(reg.detach().cpu(), g["reg"], rtol=RTOL)
+    cost = ((dev(g["labels"], torch.float32) - pred) ** 2).sum() + reg
+    cost.backward()
+    np.testing.assert_allclose(params.grad.cpu(), g["grad"], rtol=RTOL, atol=1e-6)
+
+
+@pytest.mark.parametrize("k,ld_pad", [(0, 0), (1, 0), (3, 1), (4, 0), (8, 0), (16, 0), (16, 3), (17, 2), (32, 0),
+                                       (33, 0), (64, 0), (100, 0), (100, 3), (128, 0), (150, 1), (256, 0)])
+def test_scorer_and_grad_vs_oracle(k, ld_pad):
+    rng = np.random.default_rng(k * 7 + ld_pad)
+    b, rows = 257, 500
+    fids, params, vals, poses = _random_case(rng, b, rows, k, ld_pad, 70)
+    lf, lb = 0.013, 0.4
+    e_pred, e_reg = O.score(fids, params, vals, poses, lf, lb, k=k)
+    lib_params = dev(params)
+    # the op derives K from the width of params (cc/fm_scorer_op.cc:51): pass a K+1-wide view
+    view = lib_params[:, :k + 1] if ld_pad else lib_params
+    if ld_pad:
+        # a padded table row stride goes through the C ABI's params_ld; exercise it via the model-level call
+        from fast_tffm_b200 import _lib
+        lib = _lib.load()
+        pred = torch.empty(b, device=DEV)
+        reg = torch.empty((), device=DEV)
+        ws = _lib.workspace(lib.fm_score_workspace(b), lib_params.device)
+        _lib.check(lib.fm_score(_lib.ptr(dev(fids)), _lib.ptr(lib_params), lib_params.stride(0), _lib.ptr(dev(vals)),
+                                _lib.ptr(dev(poses)), b, k, lf, lb, _lib.ptr(pred), _lib.ptr(reg), _lib.ptr(ws),
+                                ws.numel(), _lib.stream()), "fm_score")
+    else:
+        pred, reg = fm_ops.fm_scorer(dev(fids), view, dev(vals), dev(poses), lf, lb)
+    # scale of the summed terms per example: sum |x| |b| + 0.5 sum_k (sum |x v|)^2
+    absx = np.abs(vals)
+    scale = np.zeros(b)
+    for i in range(b):
+        sl = slice(poses[i], poses[i + 1])
+        r = np.abs(params[fids[sl]])
+        scale[i] = (absx[sl] * r[:, 0]).sum() + 0.5 * ((absx[sl, None] * r[:, 1:k + 1]).sum(0) ** 2).sum()
+    _close(pred.cpu().numpy(), e_pred, scale)
+    np.testing.assert_allclose(reg.item(), e_reg, rtol=RTOL)
+
+    pg = rng.normal(size=b).astype(np.float32)
+    e_grad = O.grad(fids, params, vals, poses, lf, lb, pg, 0.37, k=k)
+    if ld_pad:
+        from fast_tffm_b200 import _lib
+        lib = _lib.load()
+        grad = torch.full_like(lib_params, 7.0)
+        _lib.check(lib.fm_grad(_lib.ptr(dev(fids)), _lib.ptr(lib_params), lib_params.stride(0), _lib.ptr(dev(vals)),
+                               _lib.ptr(dev(poses)), b, k, lf, lb, _lib.ptr(dev(pg)), 0.37, None, rows, None,
+                               _lib.ptr(grad), _lib.stream()), "fm_grad")
+    else:
+        grad = fm_ops.fm_grad(dev(fids), view, dev(vals), dev(poses), lf, lb, dev(pg), dev(np.float32(0.37)))
+    assert grad.shape == lib_params.shape if ld_pad else grad.shape == (rows, k + 1)
+    gscale = np.abs(e_grad).max() if e_grad.size else 0.0
+    _close(grad.cpu().numpy(), e_grad, gscale)
+
+
+def test_scorer_ragged_rows_up_to_512():
+    rng = np.random.default_rng(99)
+    fids, params, vals, poses = _random_case(rng, 64, 4000, 32, 0, 512)
+    params *= 0.1
+    e_pred, e_reg = O.score(fids, params, vals, poses, 1e-5, 1e-5)
+    pred, reg = fm_ops.fm_scorer(dev(fids), dev(params), dev(vals), dev(poses), 1e-5, 1e-5)
+    _close(pred.cpu().numpy(), e_pred, np.abs(e_pred).max() + 1.0)
+    np.testing.assert_allclose(reg.item(), e_reg, rtol=RTOL)
+
+
+def test_scorer_matches_dense_closed_form():
+    """independent second oracle (test/fm_scorer_op_test.py:49-63 in torch float64)"""
+    rng = np.random.default_rng(5)
+    fids, params, vals, poses = _random_case(rng, 40, 60, 16, 0, 12)
+    labels = rng.normal(size=40)
+    dp, dr, dg = dense_ref.dense_cost_and_grad(fids, torch.from_numpy(params), vals, poses, 0.3, 0.7, labels)
+    p = dev(params).requires_grad_(True)
+    pred, reg = fm_ops.fm_scorer(dev(fids), p, dev(vals), dev(poses), 0.3, 0.7)
+    (((dev(labels, torch.float32) - pred) ** 2).sum() + reg).backward()
+    np.testing.assert_allclose(pred.detach().cpu(), dp, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(reg.item(), float(dr), rtol=RTOL)
+    np.testing.assert_allclose(p.grad.cpu(), dg, rtol=1e-4, atol=1e-5)
+
+
+def test_scorer_gradient_only_flows_to_params():
+    p = torch.rand(5, 4, device=DEV, requires_grad=True)
+    vals = torch.rand(3, device=DEV, requires_grad=True)
+    pred, reg = fm_ops.fm_scorer([0, 1, 2], p, vals, [0, 2, 3], 0.1, 0.1)
+    (pred.sum() + reg).backward()
+    assert p.grad is not None and vals.grad is None            # tffm/fm_ops.py:19-27
+
+
+# ------------------------------------------------- loss, lookup, adagrad ----
+@pytest.mark.parametrize("loss_type", ["logistic", "mse"])
+def test_loss_and_pred_grad(loss_type):
+    rng = np.random.default_rng(8)
+    b = 10007
+    pred = (rng.normal(size=b) * 4).astype(np.float32)
+    y = rng.integers(0, 2, b).astype(np.float32)
+    w = rng.uniform(0.5, 2, b).astype(np.float32)
+    for weights in (w, None):
+        e_loss, e_pg = O.loss(pred, y, weights, loss_type)
+        loss, pg = fm_ops.fm_loss_grad(dev(pred), dev(y), None if weights is None else dev(weights), loss_type)
+        np.testing.assert_allclose(loss.item(), e_loss, rtol=RTOL)
+        np.testing.assert_allclose(pg.cpu().numpy(), e_pg, rtol=RTOL, atol=1e-9)
+
+
+def test_lookup_and_adagrad_vs_oracle():
+    rng = np.random.default_rng(11)
+    vocab, nb, k = 20011, 10, 16
+    flat = rng.uniform(-0.01, 0.01, (vocab, k + 1)).astype(np.float32)
+    ref = O.RefModel(vocab, nb, k, flat, batch_size=8)
+    m = Model(vocabulary_size=vocab, vocabulary_block_num=nb, factor_num=k).build(DEV, init_table=flat)
+    ids = rng.permutation(vocab)[:5000]
+    rows = fm_ops.fm_lookup(m.table, dev(ids), k)
+    np.testing.assert_array_equal(rows.cpu().numpy(), O.lookup_mod(ref.blocks, vocab, nb, ids))
+    g = rng.normal(size=(5000, k + 1)).astype(np.float32) * 0.1
+    g[7] = 0.0   # a zero gradient row is still "touched": acc unchanged, w unchanged
+    O.adagrad_mod(ref.blocks, ref.acc, vocab, nb, ids, g, 0.01)
+    fm_ops.fm_sparse_adagrad(m.table, m.accum, dev(ids), dev(g), k, 0.01)
+    np.testing.assert_allclose(m.table[:, :k + 1].cpu().numpy(), ref.flat_table(), rtol=RTOL, atol=1e-8)
+    np.testing.assert_allclose(m.accum[:, :k + 1].cpu().numpy(), ref.flat_acc(), rtol=RTOL)
+    # checkpoint relabelling: vocab_block_i[id // nb] for id % nb == i
+    st = m.blocks_state()
+    assert st["vocab_block_3"].shape == (vocab // nb + 1, k + 1)
+    np.testing.assert_allclose(st["vocab_block_3"].numpy(), ref.blocks[3], rtol=RTOL, atol=1e-8)
+    m2 = Model(vocabulary_size=vocab, vocabulary_block_num=nb, factor_num=k).build(DEV, seed=1)
+    m2.load_blocks_state(st)
+    assert torch.equal(m2.table[:, :k + 1], m.table[:, :k + 1]) and torch.equal(m2.accum[:, :k + 1], m.accum[:, :k + 1])
+
+
+# ------------------------------------------------------------ whole step ----
+@pytest.mark.parametrize("loss_type,hashed", [("mse", False), ("logistic", False), ("logistic", True)])
+def test_train_steps_match_reference_model(criteo_lines, loss_type, hashed):
+    """cfg1 shape in small: sample.cfg's pipeline on the Criteo excerpt, explicit initial table,
+    fixed batch order; loss per step and the trained table against the oracle model"""
+    lines, weights = criteo_lines
+    rng = np.random.default_rng(21)
+    vocab, nb, k, bs = 200003, 10, 12, 500
+    flat = rng.uniform(-0.01, 0.01, (vocab, k + 1)).astype(np.float32)
+    kw = dict(factor_lambda=2e-3, bias_lambda=1e-3, loss_type=loss_type)
+    ref = O.RefModel(vocab, nb, k, flat, batch_size=bs, hash_feature_id=hashed, lr=0.05, init_acc=0.1, **kw)
+    m = Model(vocabulary_size=vocab, vocabulary_block_num=nb, factor_num=k, batch_size=bs, hash_feature_id=hashed,
+              learning_rate=0.05, adagrad_init_accumulator=0.1, **kw).build(DEV, init_table=flat)
+    for step in range(4):
+        sl = slice(step * bs, (step + 1) * bs)
+        w = np.float32(weights[sl]) if step % 2 == 0 else None
+        e = ref.train_step(lines[sl], w)
+        got = m.train_step(lines[sl], w)
+        np.testing.assert_allclose(got, e["loss"], rtol=RTOL)
+    np.testing.assert_allclose(m.table[:, :k + 1].cpu().numpy(), ref.flat_table(), rtol=1e-4, atol=1e-7)
+    np.testing.assert_allclose(m.accum[:, :k + 1].cpu().numpy(), ref.flat_acc(), rtol=1e-4, atol=1e-9)
+    pred = m.predict(lines[1000:1300])
+    np.testing.assert_allclose(pred.cpu().numpy(), ref.predict(lines[1000:1300]), rtol=1e-4, atol=1e-6)
+
+
+def test_failed_parse_leaves_the_table_untouched():
+    m = Model(vocabulary_size=100, factor_num=4, batch_size=2).build(DEV, seed=0)
+    before = m.table.clone()
+    with pytest.raises(fm_ops.FmParseError, match="Invalid feature value"):
+        m.train_step(["1 2:3", "0 4:x"])
+    assert torch.equal(m.table, before)
+    m.train_step(["1 2:3", "0 4:1"])
+    assert not torch.equal(m.table, before)
+
+
+def test_full_size_step_properties():
+    """cfg2 at BASELINE size: size-independent properties of one step"""
+    text, off, nnz = bench_data.criteo_batch(65536, 7)
+    m = Model(vocabulary_size=1 << 24, factor_num=16, batch_size=65536, hash_feature_id=True, loss_type="logistic",
+              factor_lambda=1e-5, bias_lambda=1e-5).build(DEV, seed=3, max_nnz_per_line=39)
+    packed = fm_ops.PackedLines(torch.from_numpy(bench_data.pad16(text)), torch.from_numpy(off)).to(DEV, False)
+    table0 = m.table.clone()
+    b = m.train_step_async(packed)
+    st = b["status"].cpu()
+    assert int(st[0]) == -1 and int(st[1]) == nnz
+    u = int(st[4])
+    ids, ori, local = b["ids"][:nnz], b["ori"][:u], b["local"][:nnz]
+    assert torch.equal(ori[local.long()], ids)                        # tf.unique invariant
+    assert u == torch.unique(ids).numel()
+    poses = b["poses"][:65537]
+    assert int(poses[0]) == 0 and int(poses[-1]) == nnz and bool((poses[1:] - poses[:-1] == 39).all())
+    changed = (m.table != table0).any(1).nonzero().flatten()
+    assert torch.equal(changed, torch.sort(ori).values)                # exactly the batch's rows were updated
+    loss = float(st[6:8].view(torch.float32)[0])
+    assert 0.6 < loss < 0.8                                            # ~log 2 for a fresh model

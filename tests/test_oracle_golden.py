@@ -67,8 +67,10 @@ def test_hash64_known_answers(golden_parser):
 
 
 def test_number_vectors_match_glibc(golden_numbers):
-    for s, bits, n in golden_numbers["strtof"]:
+    for s, bits, n, *quirk in golden_numbers["strtof"]:
         v, consumed = O.strtof(s)
+        if quirk:  # glibc hex-subnormal rounding bug: the fixture pins the IEEE value instead
+            bits = quirk[0]["glibc_2_39_bits"]
         assert (int(np.float32(v).view(np.uint32)), consumed) == (bits, n), s
     for s, val, n in golden_numbers["strtoll"]:
         assert O.strtoll(s) == (val, n), s
