@@ -178,7 +178,15 @@ def run_ours(args):
     m = Model(vocabulary_size=CFG["vocab"], factor_num=k, batch_size=b, hash_feature_id=True,
               loss_type=CFG["loss_type"], learning_rate=CFG["learning_rate"],
               adagrad_init_accumulator=CFG["init_acc"], factor_lambda=CFG["factor_lambda"],
-              bias_lambda=CFG["bias_lambda"]).build(dev, seed=0, max_nnz_per_line=CFG["nnz_per_line"])
+              bias_lambda=CFG["bias_lambda"]).build(dev, seed=0, max_nnz_per_line=CFG["nnz_per_line"], ld=args.ld)
+    if args.l2_fetch:
+        # experiment knob: cudaLimitMaxL2FetchGranularity (0x05)
+        import ctypes
+        rt = ctypes.CDLL("libcudart.so.12")
+        rc = rt.cudaDeviceSetLimit(5, ctypes.c_size_t(args.l2_fetch))
+        got = ctypes.c_size_t(0)
+        rt.cudaDeviceGetLimit(ctypes.byref(got), 5)
+        print("l2 fetch granularity ->", args.l2_fetch, "rc", rc, "now", got.value, file=sys.stderr)
 
     host, devb = [], []
     for i in range(args.batches):
@@ -295,6 +303,8 @@ def main():
     ap.add_argument("--dist", default="uniform", choices=["uniform", "zipf"])
     ap.add_argument("--batches", type=int, default=8, help="distinct synthetic batches cycled through")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ld", type=int, default=None, help="experiment: table row stride in floats")
+    ap.add_argument("--l2-fetch", type=int, default=0, help="experiment: cudaLimitMaxL2FetchGranularity")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3

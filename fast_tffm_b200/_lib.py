@@ -35,7 +35,7 @@ _SIGNATURES = {
     "fm_parse_fill": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _i64, _vp, _vp]),
     "fm_unique_workspace": (_sz, [_i64]),
     "fm_unique": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
-    "fm_lookup": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp]),
+    "fm_lookup": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp]),
     "fm_score_workspace": (_sz, [_i64]),
     "fm_score": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _i64, _f32, _f32, _vp, _vp, _vp, _sz, _vp]),
     "fm_loss_workspace": (_sz, [_i64]),

@@ -17,7 +17,8 @@ template <int LPR>
 __global__ void __launch_bounds__(256)
 lookup_kernel(const float* __restrict__ table, int64_t table_ld, const int64_t* __restrict__ ori_ids,
               int64_t n_max, const int64_t* __restrict__ n_dev, int width, float* __restrict__ out,
-              int64_t out_ld) {
+              int64_t out_ld, const unsigned long long* __restrict__ guard) {
+  if (guard && *guard != 0xffffffffffffffffull) return;  // ids of a failed parse are not to be trusted
   const int64_t n = dev_count(n_max, n_dev);
   const int c = threadIdx.x % LPR;
   const int64_t rows_per_block = blockDim.x / LPR;
@@ -72,8 +73,9 @@ static inline unsigned row_blocks(int64_t n, int lpr) {
 template <int LPR>
 struct LookupLaunch {
   static void run(const float* table, int64_t table_ld, const int64_t* ori_ids, int64_t n, const int64_t* n_dev,
-                  int width, float* out, int64_t out_ld, cudaStream_t stream) {
-    lookup_kernel<LPR><<<row_blocks(n, LPR), 256, 0, stream>>>(table, table_ld, ori_ids, n, n_dev, width, out, out_ld);
+                  int width, float* out, int64_t out_ld, const unsigned long long* guard, cudaStream_t stream) {
+    lookup_kernel<LPR><<<row_blocks(n, LPR), 256, 0, stream>>>(table, table_ld, ori_ids, n, n_dev, width, out, out_ld,
+                                                               guard);
   }
 };
 template <int LPR>
@@ -125,14 +127,14 @@ using namespace fm;
 
 FM_EXPORT int fm_lookup(const float* table, int64_t table_ld, const int64_t* ori_ids, int64_t n_unique,
                         const int64_t* n_unique_dev, int64_t factor_num, float* out, int64_t out_ld,
-                        void* stream_) {
+                        const uint64_t* guard, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   const int64_t width = factor_num + 1;
   FM_REQUIRE(n_unique >= 0 && factor_num >= 0 && table_ld >= width && out_ld >= width, "fm_lookup: bad shape");
   if (n_unique == 0) return FM_OK;
   FM_REQUIRE(table && ori_ids && out, "fm_lookup: null pointer");
   dispatch_width<LookupLaunch>((int)width, table, table_ld, ori_ids, n_unique, n_unique_dev, (int)width, out,
-                               out_ld, stream);
+                               out_ld, reinterpret_cast<const unsigned long long*>(guard), stream);
   FM_LAUNCH_CHECK();
   return FM_OK;
 }

@@ -140,7 +140,7 @@ class Model(object):
         self.predict_files = expand(pfiles) if pfiles is not None else []
 
     # ---- the vocabulary table ------------------------------------------------------
-    def build(self, device=None, init_table=None, seed=None, max_nnz_per_line=None):
+    def build(self, device=None, init_table=None, seed=None, max_nnz_per_line=None, ld=None):
         """Allocates table + Adagrad accumulator in HBM.  The table is ONE array
         [vocabulary_size, ld] (row = feature id, ld = K+1 rounded up to 4 floats); the
         reference's vocabulary_block_num blocks (fm_model.py:269-284) are a relabelling
@@ -152,7 +152,8 @@ class Model(object):
             device = torch.device("cuda", torch.cuda.current_device())
         self.device = torch.device(device)
         k, v = self.factor_num, self.vocabulary_size
-        self.ld = _ld_for(k)
+        self.ld = _ld_for(k) if ld is None else int(ld)
+        assert self.ld >= k + 1
         self.table = torch.zeros(v, self.ld, dtype=torch.float32, device=self.device)
         if init_table is not None:
             self.table[:, :k + 1] = torch.as_tensor(init_table, dtype=torch.float32)[:, :k + 1].to(self.device)
@@ -217,7 +218,7 @@ class Model(object):
                             ptr(b["ws_unique"]), b["ws_unique"].numel(), st), "fm_unique")
         mark("unique")
         check(lib.fm_lookup(ptr(self.table), self.ld, ptr(b["ori"]), b["cap"], nuniq_dev, k, ptr(b["rows"]), self.ld,
-                            st), "fm_lookup")
+                            status, st), "fm_lookup")
         mark("lookup")
         check(lib.fm_score(ptr(b["local"]), ptr(b["rows"]), self.ld, ptr(b["vals"]), ptr(b["poses"]), n_lines, k,
                            self.factor_lambda, self.bias_lambda, ptr(b["pred"]), _off(b["status"], 7),

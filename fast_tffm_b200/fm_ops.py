@@ -293,7 +293,7 @@ def fm_lookup(table: Tensor, ori_ids: Tensor, factor_num: int):
     u = ori_ids.numel()
     out = torch.empty(u, factor_num + 1, dtype=torch.float32, device=table.device)
     check(lib.fm_lookup(ptr(table), table.stride(0), ptr(ori_ids), u, None, factor_num, ptr(out), out.stride(0),
-                        stream()), "fm_lookup")
+                        None, stream()), "fm_lookup")
     return out
 
 

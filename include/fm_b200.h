@@ -114,10 +114,13 @@ int fm_unique(const int64_t* ids, int64_t n, const int64_t* n_dev, int64_t* ori_
 /* ---- L1: tf.nn.embedding_lookup, tffm/fm_model.py:291 ----
  * The table lives in ONE device array [vocab_rows, table_ld] (row id = feature
  * id; the reference's vocab_block_b[id / nb] with b = id % nb, :269-284, is a
- * checkpoint-time relabelling).  out[u, 0..K] = table[ori_ids[u], 0..K]. */
+ * checkpoint-time relabelling).  out[u, 0..K] = table[ori_ids[u], 0..K].
+ * ori_ids are NOT range-checked (neither are the reference op's inputs).  guard
+ * (optional, device): the call is a no-op unless *guard == UINT64_MAX; pass
+ * &status->first_error so the ids of a batch that failed to parse are never used. */
 int fm_lookup(const float* table, int64_t table_ld, const int64_t* ori_ids, int64_t n_unique,
               const int64_t* n_unique_dev, int64_t factor_num, float* out, int64_t out_ld,
-              void* stream);
+              const uint64_t* guard, void* stream);
 
 /* ---- S: FmScorer, cc/fm_scorer_op.cc:9-17 (op), cc/fm_scorer_op.h:8-140 ----
  * pred[i] = sum_j b_j x_j + 0.5 sum_k [ (sum_j v_jk x_j)^2 - sum_j (v_jk x_j)^2 ]

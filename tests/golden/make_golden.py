@@ -118,14 +118,44 @@ def strtof_vectors():
         # (e.g. 0x1.000001p-150 -> 0, IEEE nearest is 2^-149).  The IEEE result is what we pin;
         # the glibc value is kept beside it for the record.
         if s.strip().lstrip("+-").lower().startswith("0x") and n == len(s):
-            try:
-                ieee = int(np.float32(float.fromhex(s)).view(np.uint32))
-                if ieee != bits:
-                    entry = [s, ieee, n, {"glibc_2_39_bits": bits}]
-            except (ValueError, OverflowError):
-                pass
+            ieee = hex_to_f32_bits(s)
+            if ieee is not None and ieee != bits:
+                entry = [s, ieee, n, {"glibc_2_39_bits": bits}]
         out.append(entry)
     return out
+
+
+def hex_to_f32_bits(s):
+    """exact IEEE round-to-nearest-even of a C hex-float string, by rational arithmetic"""
+    import re
+    from fractions import Fraction
+    m = re.fullmatch(r"\s*([+-]?)0[xX]([0-9a-fA-F]*)\.?([0-9a-fA-F]*)(?:[pP]([+-]?\d+))?", s)
+    if not m or not (m.group(2) or m.group(3)):
+        return None
+    sign, ip, fp, ex = m.groups()
+    v = Fraction(int((ip or "0") + (fp or ""), 16), 16 ** len(fp or "")) * Fraction(2) ** int(ex or 0)
+    sbit = 0x80000000 if sign == "-" else 0
+    if v == 0:
+        return sbit
+    e = 0
+    while v >= 2 ** (e + 1):
+        e += 1
+    while v < Fraction(2) ** e:
+        e -= 1
+    e = max(e, -126)
+    q = v / Fraction(2) ** (e - 23)            # in units of the ulp at this exponent
+    n = q.numerator // q.denominator
+    r = q - n
+    if r > Fraction(1, 2) or (r == Fraction(1, 2) and n % 2 == 1):
+        n += 1
+    if n >= 1 << 24:
+        n >>= 1
+        e += 1
+    if e > 127:
+        return sbit | 0x7f800000
+    if n < 1 << 23:                              # subnormal (e == -126)
+        return sbit | n
+    return sbit | ((e + 127) << 23) | (n - (1 << 23))
 
 
 def strtoll_vectors():

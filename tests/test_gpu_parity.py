@@ -158,7 +158,12 @@ def test_parser_fuzz_bit_exact(hashed):
     lines = [_random_line(rnd, hashed, 1 << 20) for _ in range(3000)]
     # a few irregular (but valid) lines sprinkled in: they take the sequential path
     for i in range(0, 3000, 97):
-        lines[i] = lines[i].replace(" ", "  ", 1) if not hashed else lines[i].replace(":", ": ", 1)
+        cand = lines[i].replace(" ", "  ", 1) if not hashed else lines[i].replace(":", ": ", 1)
+        try:
+            O.parse_lines([cand], 1 << 20, hashed)
+            lines[i] = cand
+        except O.ParseError:
+            pass
     assert_parse_equal(lines, 1 << 20, hashed)
 
 
@@ -267,7 +272,7 @@ def test_scorer_and_grad_vs_oracle(k, ld_pad):
     fids, params, vals, poses = _random_case(rng, b, rows, k, ld_pad, 70)
     lf, lb = 0.013, 0.4
     e_pred, e_reg = O.score(fids, params, vals, poses, lf, lb, k=k)
-    lib_params = dev(params)
+    lib_params, d_fids, d_vals, d_poses = dev(params), dev(fids), dev(vals), dev(poses)
     # the op derives K from the width of params (cc/fm_scorer_op.cc:51): pass a K+1-wide view
     view = lib_params[:, :k + 1] if ld_pad else lib_params
     if ld_pad:
@@ -277,11 +282,11 @@ def test_scorer_and_grad_vs_oracle(k, ld_pad):
         pred = torch.empty(b, device=DEV)
         reg = torch.empty((), device=DEV)
         ws = _lib.workspace(lib.fm_score_workspace(b), lib_params.device)
-        _lib.check(lib.fm_score(_lib.ptr(dev(fids)), _lib.ptr(lib_params), lib_params.stride(0), _lib.ptr(dev(vals)),
-                                _lib.ptr(dev(poses)), b, k, lf, lb, _lib.ptr(pred), _lib.ptr(reg), _lib.ptr(ws),
+        _lib.check(lib.fm_score(_lib.ptr(d_fids), _lib.ptr(lib_params), lib_params.stride(0), _lib.ptr(d_vals),
+                                _lib.ptr(d_poses), b, k, lf, lb, _lib.ptr(pred), _lib.ptr(reg), _lib.ptr(ws),
                                 ws.numel(), _lib.stream()), "fm_score")
     else:
-        pred, reg = fm_ops.fm_scorer(dev(fids), view, dev(vals), dev(poses), lf, lb)
+        pred, reg = fm_ops.fm_scorer(d_fids, view, d_vals, d_poses, lf, lb)
     # scale of the summed terms per example: sum |x| |b| + 0.5 sum_k (sum |x v|)^2
     absx = np.abs(vals)
     scale = np.zeros(b)
@@ -293,16 +298,17 @@ def test_scorer_and_grad_vs_oracle(k, ld_pad):
     np.testing.assert_allclose(reg.item(), e_reg, rtol=RTOL)
 
     pg = rng.normal(size=b).astype(np.float32)
+    d_pg = dev(pg)
     e_grad = O.grad(fids, params, vals, poses, lf, lb, pg, 0.37, k=k)
     if ld_pad:
         from fast_tffm_b200 import _lib
         lib = _lib.load()
         grad = torch.full_like(lib_params, 7.0)
-        _lib.check(lib.fm_grad(_lib.ptr(dev(fids)), _lib.ptr(lib_params), lib_params.stride(0), _lib.ptr(dev(vals)),
-                               _lib.ptr(dev(poses)), b, k, lf, lb, _lib.ptr(dev(pg)), 0.37, None, rows, None,
+        _lib.check(lib.fm_grad(_lib.ptr(d_fids), _lib.ptr(lib_params), lib_params.stride(0), _lib.ptr(d_vals),
+                               _lib.ptr(d_poses), b, k, lf, lb, _lib.ptr(d_pg), 0.37, None, rows, None,
                                _lib.ptr(grad), _lib.stream()), "fm_grad")
     else:
-        grad = fm_ops.fm_grad(dev(fids), view, dev(vals), dev(poses), lf, lb, dev(pg), dev(np.float32(0.37)))
+        grad = fm_ops.fm_grad(d_fids, view, d_vals, d_poses, lf, lb, d_pg, dev(np.float32(0.37)))
     assert grad.shape == lib_params.shape if ld_pad else grad.shape == (rows, k + 1)
     gscale = np.abs(e_grad).max() if e_grad.size else 0.0
     _close(grad.cpu().numpy(), e_grad, gscale)
