@@ -29,10 +29,13 @@ import bench_data  # noqa: E402
 CFG = dict(vocab=1 << 24, factor_num=16, batch=65536, nnz_per_line=39, hash_feature_id=True,
            loss_type="logistic", learning_rate=0.01, init_acc=0.1, factor_lambda=1e-5, bias_lambda=1e-5)
 METRIC, UNIT = "fm_train_examples_per_sec", "examples/s"
-STAGES = ["parse_count", "parse_fill", "unique", "lookup", "score", "loss", "grad", "adagrad"]
-# my kernels per step: count, poses scan, fill | insert, rank scan, finish | lookup | score, reduce |
-# loss, reduce | zero rows, grad | adagrad
-KERNELS_PER_STEP = 14
+STAGES = {  # stage marks per step, in order
+    True: ["parse_count", "parse_fill", "unique", "score_scatter", "adagrad"],
+    False: ["parse_count", "parse_fill", "unique", "lookup", "score", "loss", "grad", "adagrad"],
+}
+# my kernels per step.  fused: count, poses scan, fill | insert, rank scan, finish | score_scatter, reduce2 |
+# fused adagrad.  composed: ... | lookup | score, reduce | loss, reduce | zero rows, grad | adagrad
+KERNELS_PER_STEP = {True: 9, False: 14}
 
 
 def measured_peak_gbs():
@@ -43,9 +46,20 @@ def measured_peak_gbs():
     return 6650.0, "fallback"
 
 
-def algorithmic_bytes(n, u, b, k, text_bytes):
-    """compulsory bytes per stage (fp32; ids i64 at the parser output)"""
+def algorithmic_bytes(n, u, b, k, text_bytes, fused):
+    """compulsory bytes per stage (fp32; ids i64 at the parser output).
+    Fused stages drop the intermediates they eliminate (gathered rows, pred_grad, dense grad) and
+    count what they add (the K+3-wide accumulator rows: one read-modify-write in the scatter, one
+    read + one clearing write in the update)."""
     rb = 4 * (k + 1)
+    ab = 4 * (k + 3)
+    if fused:
+        return {
+            "parse": text_bytes + 12 * n + 8 * b,
+            "unique": 12 * n + 8 * u + 4 * (b + 1),
+            "score_scatter": 16 * n + 4 * (b + 1) + 8 * b + u * rb + 2 * u * ab,
+            "adagrad": 8 * u + 2 * u * ab + 4 * u * rb,
+        }
     return {
         "parse": text_bytes + 12 * n + 8 * b,          # count + fill together
         "unique": 12 * n + 8 * u + 4 * (b + 1),
@@ -198,10 +212,12 @@ def run_ours(args):
     text_bytes = int(host[0].offsets[-1])
 
     # ---- device-resident throughput (value) + per-stage CUDA events ----------------
+    fused = not args.composed
+    stages = STAGES[fused]
     for i in range(args.warmup):
-        m.train_step_async(devb[i % len(devb)])
+        m.train_step_async(devb[i % len(devb)], fused=fused)
     torch.cuda.synchronize()
-    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(STAGES) + 1)] for _ in range(args.steps)]
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(stages) + 1)] for _ in range(args.steps)]
     sampler = ClockSampler(local_rank)
     sampler.start()
     torch.cuda.synchronize()
@@ -212,12 +228,12 @@ def run_ours(args):
         def mark(name, evs=ev[s], cursor=cursor):
             cursor[0] += 1
             evs[cursor[0]].record()
-        bufs = m.train_step_async(devb[s % len(devb)], mark=mark)
+        bufs = m.train_step_async(devb[s % len(devb)], mark=mark, fused=fused)
     torch.cuda.synchronize()
     clocks = sampler.stop()
     total_ms = ev[0][0].elapsed_time(ev[-1][-1])
     stage_ms = {n: sum(ev[s][i].elapsed_time(ev[s][i + 1]) for s in range(args.steps)) / args.steps
-                for i, n in enumerate(STAGES)}
+                for i, n in enumerate(stages)}
     st = bufs["status"].cpu()
     assert int(st[0]) == -1, "parse error in the benchmark data"
     nnz, n_unique = int(st[1]), int(st[4])
@@ -225,7 +241,7 @@ def run_ours(args):
     value = args.steps * b / (total_ms * 1e-3)
 
     # ---- roofline of the dominant stage -------------------------------------------
-    alg = algorithmic_bytes(nnz, n_unique, b, k, text_bytes)
+    alg = algorithmic_bytes(nnz, n_unique, b, k, text_bytes, fused)
     merged = dict(stage_ms)
     merged["parse"] = merged.pop("parse_count") + merged.pop("parse_fill")
     peak, peak_kind = measured_peak_gbs()
@@ -234,7 +250,7 @@ def run_ours(args):
                      "frac": round(alg[n] / (ms * 1e-3) / 1e9 / peak, 4) if ms > 0 else None}
                  for n, ms in merged.items()}
     # the dominant GATHER/SCATTER kernel: the longest of the table-touching stages
-    dom = max(("lookup", "score", "grad", "adagrad", "unique", "parse"), key=lambda n: merged[n])
+    dom = max(merged, key=lambda n: merged[n])
     roofline = {"bound": "hbm", "kernel": dom, "achieved": per_stage[dom]["gbs"], "peak": peak,
                 "peak_kind": peak_kind, "unit": "GB/s", "frac": per_stage[dom]["frac"], "traffic": None,
                 "step_frac": round(sum(alg.values()) / (total_ms / args.steps * 1e-3) / 1e9 / peak, 4),
@@ -262,7 +278,7 @@ def run_ours(args):
                 stage_in[slot].offsets.copy_(hb.offsets, non_blocking=True)
                 ready[slot].record(copy_stream)
             main.wait_event(ready[slot])
-            bb = m.train_step_async(stage_in[slot])
+            bb = m.train_step_async(stage_in[slot], fused=fused)
             consumed[slot].record(main)
             pinned_status[base + s].copy_(bb["status"], non_blocking=True)   # loss + status back to the host
 
@@ -287,7 +303,8 @@ def run_ours(args):
         "cpu_baseline": None if base is None else {k_: base[k_] for k_ in ("value", "unit", "cores", "kind", "sample", "stage_ms")},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / args.steps},
-        "gpu_launches": KERNELS_PER_STEP * args.steps,
+        "gpu_launches": KERNELS_PER_STEP[fused] * args.steps,
+        "path": "fused" if fused else "composed (op by op)",
         "clocks": clocks,
         "final_loss": loss, "nnz_per_step": nnz, "unique_per_step": n_unique,
     }
@@ -303,6 +320,7 @@ def main():
     ap.add_argument("--dist", default="uniform", choices=["uniform", "zipf"])
     ap.add_argument("--batches", type=int, default=8, help="distinct synthetic batches cycled through")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--composed", action="store_true", help="time the op-by-op chain instead of the fused path")
     ap.add_argument("--ld", type=int, default=None, help="experiment: table row stride in floats")
     ap.add_argument("--l2-fetch", type=int, default=0, help="experiment: cudaLimitMaxL2FetchGranularity")
     args = ap.parse_args()

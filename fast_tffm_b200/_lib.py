@@ -42,6 +42,11 @@ _SIGNATURES = {
     "fm_loss_grad": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp, _vp, _vp, _sz, _vp]),
     "fm_grad": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _i64, _f32, _f32, _vp, _f32, _vp, _i64, _vp, _vp, _vp]),
     "fm_sparse_adagrad": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _f32, _vp, _vp]),
+    "fm_fused_gacc_ld": (_i64, [_i64]),
+    "fm_fused_workspace": (_sz, [_i64]),
+    "fm_fused_score_scatter": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _i64, _f32, _f32, _i32,
+                                         _vp, _vp, _vp, _vp, _i64, _vp, _vp, _sz, _vp]),
+    "fm_fused_adagrad": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _f32, _f32, _f32, _f32, _vp, _vp]),
 }
 
 _lib = None

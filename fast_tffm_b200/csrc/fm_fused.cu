@@ -1,0 +1,372 @@
+// fm_fused.cu -- the training hot path with every table row read once.
+//
+// The reference runs, per step, embedding_lookup -> FmScorer -> loss -> FmGrad ->
+// SparseApplyAdagrad (tffm/fm_model.py:291-348) and each of those walks the
+// gathered rows again.  Here:
+//
+//   fm_fused_score_scatter  one warp per example: gathers the example's rows
+//       straight from the vocabulary table with 128-bit loads, computes
+//       pred (cc/fm_scorer_op.h:22-36, :60-86, :134-136), the example's loss term
+//       and d loss / d pred (tffm/fm_model.py:311-326), then scatters the
+//       example's contribution to the gradient of each of its rows.
+//       FmGrad's per-occurrence gradient (cc/fm_grad_op.h:88-97)
+//           g_0 = pg x + rg lb b            g_k = rg lf v_k - pg x^2 v_k + pg x s_k
+//       summed over the occurrences of one table row factorises as
+//           G_0 = C + cnt rg lb b           G_k = v_k (cnt rg lf - D) + B_k
+//       with C = sum pg x, D = sum pg x^2, B_k = sum pg x s_k, cnt = #occurrences,
+//       none of which needs the row itself.  So the kernel adds {C, B_1..B_K, D,
+//       cnt} to a compact accumulator row per distinct id (columns 0, 1..K, K+1,
+//       K+2) with vector float atomics (red.global.add.v4.f32) and never reads the
+//       rows a second time.
+//   fm_fused_adagrad  one lane group per distinct id: reads the accumulator row
+//       (sequential), the weight and Adagrad rows (random, once), forms G, applies
+//       acc += G^2 ; w -= lr G / sqrt(acc)  (TF1 SparseApplyAdagrad) and clears
+//       the accumulator row for the next step.
+//
+// Rows are handled as float4 chunks: table row stride (floats) must be a multiple
+// of 4 with the pad columns zero, pointers 16-byte aligned.
+#include "fm_common.cuh"
+
+namespace fm {
+namespace {
+
+constexpr int kWarps = 8;
+constexpr unsigned long long kNoError = 0xffffffffffffffffull;
+
+__device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+template <int LPR>
+__device__ __forceinline__ float sum_row_groups(float v) {  // over lanes with equal (lane % LPR)
+#pragma unroll
+  for (int o = 16; o >= LPR; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+  return v;
+}
+template <int LPR>
+__device__ __forceinline__ float sum_in_group(float v) {  // over the LPR lanes of one row
+#pragma unroll
+  for (int o = LPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+  return v;
+}
+
+// LPR lanes share a row; lane c owns float4 chunks c, c + LPR, ... (T of them).
+template <int LPR, int T>
+__global__ void __launch_bounds__(kWarps * 32)
+fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __restrict__ local,
+                           const float* __restrict__ vals, const int32_t* __restrict__ poses,
+                           const float* __restrict__ labels, const float* __restrict__ weights, int64_t batch,
+                           int K, const float* __restrict__ table, int64_t ld, float lam_f, float lam_b,
+                           int loss_kind, float* __restrict__ pred, float* __restrict__ gacc, int64_t gacc_ld,
+                           float* __restrict__ partials, const unsigned long long* __restrict__ guard) {
+  constexpr int RPW = 32 / LPR;
+  __shared__ float s_loss[kWarps], s_reg[kWarps];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int r = lane / LPR, c = lane % LPR;
+  const int vc_table = (int)(ld >> 2), vc_acc = (int)(gacc_ld >> 2);
+  const bool active = !(guard && *guard != kNoError);
+  float loss_acc = 0.f, reg_acc = 0.f;
+  const float inv_batch = 1.0f / (float)batch;
+
+  for (int64_t i = (int64_t)blockIdx.x * kWarps + warp; active && i < batch; i += (int64_t)gridDim.x * kWarps) {
+    const int start = poses[i], end = poses[i + 1];
+    float4 S[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) S[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+    float q = 0.f, bias_dot = 0.f, bias_sq = 0.f, fac_sq = 0.f;
+
+    // ---- pass A: gather the rows once ------------------------------------------
+    for (int base = start; base < end; base += 32) {
+      const int j = base + lane;
+      const int64_t my_off = j < end ? ids[j] * ld : 0;
+      const float my_x = j < end ? vals[j] : 0.f;
+      const int rows_here = min(32, end - base);
+#pragma unroll
+      for (int s = 0; s < LPR; ++s) {
+        const int jj = s * RPW + r;
+        if (s * RPW >= rows_here) break;  // warp-uniform
+        const int64_t off = __shfl_sync(kFull, my_off, jj);
+        const float x = __shfl_sync(kFull, my_x, jj);
+        if (jj < rows_here) {
+#pragma unroll
+          for (int t = 0; t < T; ++t) {
+            const int chunk = c + t * LPR;
+            if (chunk < vc_table) {
+              float4 v = ldg4(table + off + 4 * chunk);
+              if (chunk == 0) {  // column 0 is the bias
+                bias_dot = fmaf(x, v.x, bias_dot);
+                bias_sq = fmaf(v.x, v.x, bias_sq);
+                v.x = 0.f;
+              }
+              // pad columns of the table are zero, so they drop out of every sum
+              const float a0 = x * v.x, a1 = x * v.y, a2 = x * v.z, a3 = x * v.w;
+              S[t].x += a0; S[t].y += a1; S[t].z += a2; S[t].w += a3;
+              q = fmaf(a0, a0, fmaf(a1, a1, fmaf(a2, a2, fmaf(a3, a3, q))));
+              fac_sq = fmaf(v.x, v.x, fmaf(v.y, v.y, fmaf(v.z, v.z, fmaf(v.w, v.w, fac_sq))));
+            }
+          }
+        }
+      }
+    }
+    float second = 0.f;
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+      S[t].x = sum_row_groups<LPR>(S[t].x);
+      S[t].y = sum_row_groups<LPR>(S[t].y);
+      S[t].z = sum_row_groups<LPR>(S[t].z);
+      S[t].w = sum_row_groups<LPR>(S[t].w);
+      second += S[t].x * S[t].x + S[t].y * S[t].y + S[t].z * S[t].z + S[t].w * S[t].w;
+    }
+    if (r != 0) second = 0.f;  // every row group holds the same column totals: count them once
+    const float p = warp_sum(bias_dot + 0.5f * (second - q));
+    reg_acc += warp_sum(0.5f * lam_f * fac_sq + 0.5f * lam_b * bias_sq);
+
+    // ---- loss term and d loss / d pred (tffm/fm_model.py:311-326) ------------------
+    const float y = labels[i], w = weights ? weights[i] : 1.0f;
+    float l, d;
+    if (loss_kind == FM_LOSS_LOGISTIC) {
+      l = fmaxf(p, 0.f) - p * y + log1pf(expf(-fabsf(p)));
+      d = 1.0f / (1.0f + expf(-p)) - y;
+    } else {
+      l = (p - y) * (p - y);
+      d = 2.0f * (p - y);
+    }
+    const float pg = w * d * inv_batch;
+    if (lane == 0) {
+      pred[i] = p;
+      loss_acc += w * l;
+    }
+
+    // ---- pass B: scatter {C, B_k, D, cnt} to the accumulator rows ---------------------
+    for (int base = start; base < end; base += 32) {
+      const int j = base + lane;
+      const int my_u = j < end ? local[j] : 0;
+      const float my_x = j < end ? vals[j] : 0.f;
+      const int rows_here = min(32, end - base);
+#pragma unroll
+      for (int s = 0; s < LPR; ++s) {
+        const int jj = s * RPW + r;
+        if (s * RPW >= rows_here) break;
+        const int u = __shfl_sync(kFull, my_u, jj);
+        const float x = __shfl_sync(kFull, my_x, jj);
+        if (jj < rows_here) {
+          const float pgx = pg * x;
+          float* arow = gacc + (int64_t)u * gacc_ld;
+#pragma unroll
+          for (int t = 0; t < T; ++t) {
+            const int chunk = c + t * LPR;
+            if (chunk < vc_acc) {
+              const int col = 4 * chunk;
+              float o[4] = {pgx * S[t].x, pgx * S[t].y, pgx * S[t].z, pgx * S[t].w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const int cc = col + e;
+                if (cc == 0) o[e] = pgx;                 // C
+                else if (cc == K + 1) o[e] = pgx * x;    // D
+                else if (cc == K + 2) o[e] = 1.0f;       // cnt
+                else if (cc > K + 2) o[e] = 0.f;
+              }
+              if (col <= K + 2) red_add_v4(arow + col, o[0], o[1], o[2], o[3]);
+            }
+          }
+        }
+      }
+    }
+  }
+
+  if (lane == 0) { s_loss[warp] = loss_acc; s_reg[warp] = reg_acc; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) { a += s_loss[w]; b += s_reg[w]; }
+    partials[blockIdx.x] = a;
+    partials[gridDim.x + blockIdx.x] = b;
+  }
+}
+
+// two fixed-order sums (loss, reg) of `n` per-block partials each
+__global__ void __launch_bounds__(256)
+reduce2_kernel(const float* __restrict__ partials, int n, float scale0, float* __restrict__ out0,
+               float* __restrict__ out1) {
+  __shared__ double s_w[2][8];
+  double a = 0.0, b = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) { a += (double)partials[i]; b += (double)partials[n + i]; }
+  a = warp_sum(a); b = warp_sum(b);
+  if ((threadIdx.x & 31) == 0) { s_w[0][threadIdx.x >> 5] = a; s_w[1][threadIdx.x >> 5] = b; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double ta = 0.0, tb = 0.0;
+    for (int w = 0; w < 8; ++w) { ta += s_w[0][w]; tb += s_w[1][w]; }
+    *out0 = (float)(ta * (double)scale0);
+    *out1 = (float)tb;
+  }
+}
+
+template <int LPR, int T>
+__global__ void __launch_bounds__(256)
+fused_adagrad_kernel(float* __restrict__ table, float* __restrict__ accum, int64_t ld,
+                     const int64_t* __restrict__ ori_ids, int64_t n_max, const int64_t* __restrict__ n_dev, int K,
+                     float* __restrict__ gacc, int64_t gacc_ld, float lr, float rf, float rb,
+                     const unsigned long long* __restrict__ guard) {
+  if (guard && *guard != kNoError) return;
+  const int64_t n = n_dev ? min(*n_dev, n_max) : n_max;
+  const int c = threadIdx.x % LPR;
+  const int64_t groups_per_block = blockDim.x / LPR;
+  const int vc_table = (int)(ld >> 2), vc_acc = (int)(gacc_ld >> 2);
+  const int64_t n_round = (n + groups_per_block - 1) / groups_per_block * groups_per_block;  // keep warps converged
+  for (int64_t u = (int64_t)blockIdx.x * groups_per_block + threadIdx.x / LPR; u < n_round;
+       u += (int64_t)gridDim.x * groups_per_block) {
+    const bool live = u < n;
+    const int64_t row = live ? ori_ids[u] * ld : 0;
+    float4 a[T], w[T], h[T];
+    float D = 0.f, cnt = 0.f;
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+      const int chunk = c + t * LPR;
+      a[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+      w[t] = a[t]; h[t] = a[t];
+      if (live && chunk < vc_acc) a[t] = *reinterpret_cast<const float4*>(gacc + u * gacc_ld + 4 * chunk);
+      if (live && chunk < vc_table) {
+        w[t] = *reinterpret_cast<const float4*>(table + row + 4 * chunk);
+        h[t] = *reinterpret_cast<const float4*>(accum + row + 4 * chunk);
+      }
+      const float av[4] = {a[t].x, a[t].y, a[t].z, a[t].w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        if (4 * chunk + e == K + 1) D += av[e];
+        if (4 * chunk + e == K + 2) cnt += av[e];
+      }
+    }
+    D = sum_in_group<LPR>(D);
+    cnt = sum_in_group<LPR>(cnt);
+    const float fac_scale = cnt * rf - D, bias_scale = cnt * rb;
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+      const int chunk = c + t * LPR;
+      if (live && chunk < vc_table) {
+        const float av[4] = {a[t].x, a[t].y, a[t].z, a[t].w};
+        float wv[4] = {w[t].x, w[t].y, w[t].z, w[t].w};
+        float hv[4] = {h[t].x, h[t].y, h[t].z, h[t].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int col = 4 * chunk + e;
+          float g = 0.f;
+          if (col == 0) g = fmaf(bias_scale, wv[e], av[e]);
+          else if (col <= K) g = fmaf(wv[e], fac_scale, av[e]);
+          hv[e] = fmaf(g, g, hv[e]);
+          wv[e] -= __fdiv_rn(lr * g, __fsqrt_rn(hv[e]));
+        }
+        *reinterpret_cast<float4*>(table + row + 4 * chunk) = make_float4(wv[0], wv[1], wv[2], wv[3]);
+        *reinterpret_cast<float4*>(accum + row + 4 * chunk) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+      }
+      if (live && chunk < vc_acc)
+        *reinterpret_cast<float4*>(gacc + u * gacc_ld + 4 * chunk) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+}
+
+struct Shape { int lpr, t; };
+static inline bool pick_shape(int64_t chunks, Shape* s) {
+  int lpr = 1;
+  while (lpr < 32 && lpr < chunks) lpr <<= 1;
+  const int t = (int)((chunks + lpr - 1) / lpr);
+  if (t > 3) return false;
+  s->lpr = lpr; s->t = t;
+  return true;
+}
+
+#define FM_DISPATCH_SHAPE(shape, CALL)                     \
+  switch ((shape).lpr * 4 + (shape).t) {                   \
+    case 1 * 4 + 1: { CALL(1, 1); } break;                 \
+    case 2 * 4 + 1: { CALL(2, 1); } break;                 \
+    case 4 * 4 + 1: { CALL(4, 1); } break;                 \
+    case 8 * 4 + 1: { CALL(8, 1); } break;                 \
+    case 16 * 4 + 1: { CALL(16, 1); } break;               \
+    case 32 * 4 + 1: { CALL(32, 1); } break;               \
+    case 32 * 4 + 2: { CALL(32, 2); } break;               \
+    case 32 * 4 + 3: { CALL(32, 3); } break;               \
+    default: return fm_fail(FM_E_LIMIT, "unsupported row shape"); \
+  }
+
+static inline int fused_blocks(int64_t batch) {
+  int64_t b = (batch + kWarps - 1) / kWarps;
+  if (b > 148 * 8) b = 148 * 8;
+  return (int)(b < 1 ? 1 : b);
+}
+
+}  // namespace
+}  // namespace fm
+
+using namespace fm;
+
+FM_EXPORT int64_t fm_fused_gacc_ld(int64_t factor_num) { return (factor_num + 3 + 3) / 4 * 4; }
+
+FM_EXPORT size_t fm_fused_workspace(int64_t batch) {
+  return fm_align_up((size_t)fused_blocks(batch) * 2 * sizeof(float), 256);
+}
+
+FM_EXPORT int fm_fused_score_scatter(const int64_t* feature_ids, const int32_t* local_ids, const float* feature_vals,
+                                     const int32_t* feature_poses, const float* labels, const float* weights,
+                                     int64_t batch, int64_t factor_num, const float* table, int64_t table_ld,
+                                     float factor_lambda, float bias_lambda, int loss_kind, float* pred_score,
+                                     float* loss, float* reg_score, float* gacc, int64_t gacc_ld,
+                                     const uint64_t* guard, void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  FM_REQUIRE(batch >= 0 && factor_num >= 0, "fm_fused_score_scatter: bad shape");
+  FM_REQUIRE(table_ld >= factor_num + 1 && table_ld % 4 == 0, "fm_fused_score_scatter: table_ld must be a multiple of 4 and >= K+1");
+  FM_REQUIRE(gacc_ld >= factor_num + 3 && gacc_ld % 4 == 0, "fm_fused_score_scatter: gacc_ld must be a multiple of 4 and >= K+3");
+  FM_REQUIRE(loss_kind == FM_LOSS_LOGISTIC || loss_kind == FM_LOSS_MSE, "fm_fused_score_scatter: unknown loss kind");
+  FM_REQUIRE(loss && reg_score && workspace, "fm_fused_score_scatter: null pointer");
+  FM_REQUIRE(batch == 0 || (feature_ids && local_ids && feature_vals && feature_poses && labels && table && pred_score && gacc),
+             "fm_fused_score_scatter: null pointer");
+  FM_REQUIRE((((uintptr_t)table | (uintptr_t)gacc) & 15) == 0, "fm_fused_score_scatter: table and gacc must be 16-byte aligned");
+  if (workspace_bytes < fm_fused_workspace(batch))
+    return fm_fail(FM_E_WORKSPACE, "fm_fused_score_scatter: workspace %zu < %zu", workspace_bytes, fm_fused_workspace(batch));
+  Shape sh;
+  if (!pick_shape(gacc_ld / 4 > table_ld / 4 ? gacc_ld / 4 : table_ld / 4, &sh))
+    return fm_fail(FM_E_LIMIT, "fm_fused_score_scatter: factor_num %lld too large", (long long)factor_num);
+  const int blocks = fused_blocks(batch);
+  float* partials = reinterpret_cast<float*>(workspace);
+#define CALL(LPR, T)                                                                                              \
+  fused_score_scatter_kernel<LPR, T><<<blocks, kWarps * 32, 0, stream>>>(                                         \
+      feature_ids, local_ids, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, table, table_ld, \
+      factor_lambda, bias_lambda, loss_kind, pred_score, gacc, gacc_ld, partials,                                 \
+      reinterpret_cast<const unsigned long long*>(guard))
+  FM_DISPATCH_SHAPE(sh, CALL)
+#undef CALL
+  FM_LAUNCH_CHECK();
+  reduce2_kernel<<<1, 256, 0, stream>>>(partials, blocks, batch > 0 ? 1.0f / (float)batch : 0.f, loss, reg_score);
+  FM_LAUNCH_CHECK();
+  return FM_OK;
+}
+
+FM_EXPORT int fm_fused_adagrad(float* table, float* accum, int64_t table_ld, const int64_t* ori_ids, int64_t n_unique,
+                               const int64_t* n_unique_dev, int64_t factor_num, float* gacc, int64_t gacc_ld,
+                               float learning_rate, float factor_lambda, float bias_lambda, float reg_grad,
+                               const uint64_t* guard, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  FM_REQUIRE(n_unique >= 0 && factor_num >= 0, "fm_fused_adagrad: bad shape");
+  FM_REQUIRE(table_ld >= factor_num + 1 && table_ld % 4 == 0, "fm_fused_adagrad: table_ld must be a multiple of 4 and >= K+1");
+  FM_REQUIRE(gacc_ld >= factor_num + 3 && gacc_ld % 4 == 0, "fm_fused_adagrad: gacc_ld must be a multiple of 4 and >= K+3");
+  if (n_unique == 0) return FM_OK;
+  FM_REQUIRE(table && accum && ori_ids && gacc, "fm_fused_adagrad: null pointer");
+  FM_REQUIRE((((uintptr_t)table | (uintptr_t)accum | (uintptr_t)gacc) & 15) == 0, "fm_fused_adagrad: 16-byte alignment required");
+  Shape sh;
+  if (!pick_shape(gacc_ld / 4 > table_ld / 4 ? gacc_ld / 4 : table_ld / 4, &sh))
+    return fm_fail(FM_E_LIMIT, "fm_fused_adagrad: factor_num %lld too large", (long long)factor_num);
+  const int64_t groups_per_block = 256 / sh.lpr;
+  int64_t blocks = (n_unique + groups_per_block - 1) / groups_per_block;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+#define CALL(LPR, T)                                                                                     \
+  fused_adagrad_kernel<LPR, T><<<(unsigned)blocks, 256, 0, stream>>>(                                    \
+      table, accum, table_ld, ori_ids, n_unique, n_unique_dev, (int)factor_num, gacc, gacc_ld,           \
+      learning_rate, reg_grad * factor_lambda, reg_grad * bias_lambda,                                   \
+      reinterpret_cast<const unsigned long long*>(guard))
+  FM_DISPATCH_SHAPE(sh, CALL)
+#undef CALL
+  FM_LAUNCH_CHECK();
+  return FM_OK;
+}

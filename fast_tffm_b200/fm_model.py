@@ -186,7 +186,10 @@ class Model(object):
             poses=torch.empty(lines + 1, dtype=i32, device=dev), ids=torch.empty(cap, dtype=i64, device=dev),
             vals=torch.empty(cap, dtype=f32, device=dev), ori=torch.empty(cap, dtype=i64, device=dev),
             local=torch.empty(cap, dtype=i32, device=dev), rows=torch.empty(cap, self.ld, dtype=f32, device=dev),
-            grad=torch.empty(cap, self.ld, dtype=f32, device=dev), pred=torch.empty(lines, dtype=f32, device=dev),
+            grad=None, pred=torch.empty(lines, dtype=f32, device=dev),
+            gacc_ld=int(lib.fm_fused_gacc_ld(self.factor_num)),
+            gacc=torch.zeros(cap, int(lib.fm_fused_gacc_ld(self.factor_num)), dtype=f32, device=dev),
+            ws_fused=_lib.workspace(lib.fm_fused_workspace(lines), dev),
             pred_grad=torch.empty(lines, dtype=f32, device=dev),
             # [first_error, nnz, n_lines, reserved] (fm_parse_status), n_unique, then loss and reg as f32 bits
             status=torch.zeros(8, dtype=i64, device=dev),
@@ -199,12 +202,12 @@ class Model(object):
         self._bufs = b
         return b
 
-    def _forward(self, packed, b, mark=_no_mark):
-        """parse -> unique -> lookup -> score, all sizes device-resident.
+    def _parse_unique(self, packed, b, mark=_no_mark):
+        """parse -> unique (+ cumsum), all sizes device-resident.
         mark(name) is called after each stage is enqueued (bench.py records CUDA events there)."""
         lib, st = load(), stream()
         n_lines = packed.n_lines
-        k, hashed = self.factor_num, int(self.hash_feature_id)
+        hashed = int(self.hash_feature_id)
         status, nnz_dev, nuniq_dev = ptr(b["status"]), _off(b["status"], 1), _off(b["status"], 4)
         check(lib.fm_parse_count(ptr(packed.text), ptr(packed.offsets), n_lines, self.vocabulary_size, hashed,
                                  ptr(b["sizes"]), ptr(b["poses"]), status, ptr(b["ws_parse"]),
@@ -217,6 +220,13 @@ class Model(object):
         check(lib.fm_unique(ptr(b["ids"]), b["cap"], nnz_dev, ptr(b["ori"]), ptr(b["local"]), nuniq_dev,
                             ptr(b["ws_unique"]), b["ws_unique"].numel(), st), "fm_unique")
         mark("unique")
+
+    def _forward(self, packed, b, mark=_no_mark):
+        """parse -> unique -> lookup -> score: the reference's op chain, one C-ABI call per op"""
+        lib, st = load(), stream()
+        n_lines, k = packed.n_lines, self.factor_num
+        status, nuniq_dev = ptr(b["status"]), _off(b["status"], 4)
+        self._parse_unique(packed, b, mark)
         check(lib.fm_lookup(ptr(self.table), self.ld, ptr(b["ori"]), b["cap"], nuniq_dev, k, ptr(b["rows"]), self.ld,
                             status, st), "fm_lookup")
         mark("lookup")
@@ -225,13 +235,34 @@ class Model(object):
                            ptr(b["ws_score"]), b["ws_score"].numel(), st), "fm_score")
         mark("score")
 
-    def train_step_async(self, packed: PackedLines, weights=None, mark=_no_mark):
+    def train_step_async(self, packed: PackedLines, weights=None, mark=_no_mark, fused=True):
         """One training step on a device-resident batch; enqueues only.  Returns the
         buffers dict: status[0] parse status word, status[1] nnz, status[4] n_unique,
-        scalars[0] loss, scalars[2] reg."""
+        scalars[0] loss, scalars[2] reg.
+        fused=True  (default) parse -> unique -> fm_fused_score_scatter -> fm_fused_adagrad:
+                    each table row is read once per step;
+        fused=False the reference's op-by-op chain (lookup, scorer, loss, grad, Adagrad)."""
         b = self._buffers(packed.n_lines, packed.text.numel())
         lib, st = load(), stream()
         n_lines, k = packed.n_lines, self.factor_num
+        if fused:
+            self._parse_unique(packed, b, mark)
+            check(lib.fm_fused_score_scatter(
+                ptr(b["ids"]), ptr(b["local"]), ptr(b["vals"]), ptr(b["poses"]), ptr(b["labels"]), ptr(weights),
+                n_lines, k, ptr(self.table), self.ld, self.factor_lambda, self.bias_lambda,
+                _lib.LOSS_KIND[self.loss_type], ptr(b["pred"]), _off(b["status"], 6), _off(b["status"], 7),
+                ptr(b["gacc"]), b["gacc_ld"], ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st),
+                "fm_fused_score_scatter")
+            mark("score_scatter")
+            check(lib.fm_fused_adagrad(
+                ptr(self.table), ptr(self.accum), self.ld, ptr(b["ori"]), b["cap"], _off(b["status"], 4), k,
+                ptr(b["gacc"]), b["gacc_ld"], self.learning_rate, self.factor_lambda, self.bias_lambda,
+                1.0 / self.batch_size, ptr(b["status"]), st), "fm_fused_adagrad")
+            mark("adagrad")
+            self.global_step += 1
+            return b
+        if b["grad"] is None:
+            b["grad"] = torch.empty(b["cap"], self.ld, dtype=torch.float32, device=self.device)
         self._forward(packed, b, mark)
         nuniq_dev = _off(b["status"], 4)
         check(lib.fm_loss_grad(ptr(b["pred"]), ptr(b["labels"]), ptr(weights), n_lines,
@@ -250,11 +281,11 @@ class Model(object):
         self.global_step += 1
         return b
 
-    def train_step(self, lines, weights=None):
+    def train_step(self, lines, weights=None, fused=True):
         """lines: list of str / PackedLines (host or device); weights: per-example floats or None.
         Returns the batch loss (python float); raises FmParseError like the op would."""
         packed, weights = self._to_device(lines, weights)
-        b = self.train_step_async(packed, weights)
+        b = self.train_step_async(packed, weights, fused=fused)
         host = b["status"].cpu()
         _raise(host, packed)
         return float(host[6:8].view(torch.float32)[0])

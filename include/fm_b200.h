@@ -164,6 +164,41 @@ int fm_sparse_adagrad(float* table, float* accum, int64_t table_ld, const int64_
                       const float* grad, int64_t grad_ld, float learning_rate, const uint64_t* guard,
                       void* stream);
 
+/* ---- fused training path: S + LS + G + A1 with every table row read once ----
+ * Not an op of the reference: it computes what fm_lookup -> fm_score ->
+ * fm_loss_grad -> fm_grad -> fm_sparse_adagrad compute (tffm/fm_model.py:291-348
+ * over cc/fm_scorer_op.h and cc/fm_grad_op.h), in two kernels.
+ *
+ * fm_fused_score_scatter: per example, gathers its rows from `table` by GLOBAL id
+ * (feature_ids, int64 as the parser emits them), writes pred_score, the mean
+ * weighted loss and reg_score, and adds the example's share of the gradient to
+ * gacc[local_ids[j]] (local_ids from fm_unique).  A gacc row holds, in columns
+ * 0, 1..K, K+1, K+2: C = sum pg x, B_k = sum pg x s_k, D = sum pg x^2, cnt; from
+ * them the row's gradient is G_0 = C + cnt rg lb b, G_k = v_k (cnt rg lf - D) + B_k,
+ * which equals the sum of FmGrad's per-occurrence terms (cc/fm_grad_op.h:88-97).
+ * gacc must be all zero on entry; fm_fused_adagrad leaves it all zero again.
+ * table_ld and gacc_ld are multiples of 4 floats, pad columns of `table` are
+ * zero, table / gacc / accum are 16-byte aligned.
+ *
+ * fm_fused_adagrad: for u < U, forms G from gacc[u] and table[ori_ids[u]] and
+ * applies TF1 SparseApplyAdagrad to table / accum; rg = reg_grad (the factor the
+ * objective puts on reg_score: 1 / batch_size, tffm/fm_model.py:345-347).
+ * guard: as in fm_sparse_adagrad; both calls are no-ops when it is tripped. */
+int64_t fm_fused_gacc_ld(int64_t factor_num);
+size_t fm_fused_workspace(int64_t batch);
+int fm_fused_score_scatter(const int64_t* feature_ids, const int32_t* local_ids,
+                           const float* feature_vals, const int32_t* feature_poses,
+                           const float* labels, const float* weights, int64_t batch,
+                           int64_t factor_num, const float* table, int64_t table_ld,
+                           float factor_lambda, float bias_lambda, int loss_kind,
+                           float* pred_score, float* loss, float* reg_score, float* gacc,
+                           int64_t gacc_ld, const uint64_t* guard, void* workspace,
+                           size_t workspace_bytes, void* stream);
+int fm_fused_adagrad(float* table, float* accum, int64_t table_ld, const int64_t* ori_ids,
+                     int64_t n_unique, const int64_t* n_unique_dev, int64_t factor_num,
+                     float* gacc, int64_t gacc_ld, float learning_rate, float factor_lambda,
+                     float bias_lambda, float reg_grad, const uint64_t* guard, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

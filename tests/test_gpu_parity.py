@@ -386,8 +386,9 @@ def test_lookup_and_adagrad_vs_oracle():
 
 
 # ------------------------------------------------------------ whole step ----
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("loss_type,hashed", [("mse", False), ("logistic", False), ("logistic", True)])
-def test_train_steps_match_reference_model(criteo_lines, loss_type, hashed):
+def test_train_steps_match_reference_model(criteo_lines, loss_type, hashed, fused):
     """cfg1 shape in small: sample.cfg's pipeline on the Criteo excerpt, explicit initial table,
     fixed batch order; loss per step and the trained table against the oracle model"""
     lines, weights = criteo_lines
@@ -402,8 +403,10 @@ def test_train_steps_match_reference_model(criteo_lines, loss_type, hashed):
         sl = slice(step * bs, (step + 1) * bs)
         w = np.float32(weights[sl]) if step % 2 == 0 else None
         e = ref.train_step(lines[sl], w)
-        got = m.train_step(lines[sl], w)
+        got = m.train_step(lines[sl], w, fused=fused)
         np.testing.assert_allclose(got, e["loss"], rtol=RTOL)
+        np.testing.assert_allclose(m._bufs["pred"][:bs].cpu().numpy(), e["pred"], rtol=1e-4, atol=1e-6)
+        np.testing.assert_allclose(float(m._bufs["scalars"][2]), e["reg"], rtol=RTOL)
     np.testing.assert_allclose(m.table[:, :k + 1].cpu().numpy(), ref.flat_table(), rtol=1e-4, atol=1e-7)
     np.testing.assert_allclose(m.accum[:, :k + 1].cpu().numpy(), ref.flat_acc(), rtol=1e-4, atol=1e-9)
     pred = m.predict(lines[1000:1300])
@@ -437,6 +440,9 @@ def test_full_size_step_properties():
     poses = b["poses"][:65537]
     assert int(poses[0]) == 0 and int(poses[-1]) == nnz and bool((poses[1:] - poses[:-1] == 39).all())
     changed = (m.table != table0).any(1).nonzero().flatten()
-    assert torch.equal(changed, torch.sort(ori).values)                # exactly the batch's rows were updated
+    touched = torch.zeros(1 << 24, dtype=torch.bool, device=DEV)
+    touched[ori] = True
+    assert bool(touched[changed].all())                                # only the batch's rows were updated
+    assert changed.numel() > 0.9 * u                                   # (rows whose x == 0 move by less than an ulp)
     loss = float(st[6:8].view(torch.float32)[0])
     assert 0.6 < loss < 0.8                                            # ~log 2 for a fresh model
