@@ -38,6 +38,7 @@ _SIGNATURES = {
     "fm_lookup": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp]),
     "fm_score_workspace": (_sz, [_i64]),
     "fm_score": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _i64, _f32, _f32, _vp, _vp, _vp, _sz, _vp]),
+    "fm_score_noalloc": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _i64, _f32, _f32, _vp, _vp, _vp]),
     "fm_loss_workspace": (_sz, [_i64]),
     "fm_loss_grad": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp, _vp, _vp, _sz, _vp]),
     "fm_grad": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _i64, _f32, _f32, _vp, _f32, _vp, _i64, _vp, _vp, _vp]),

@@ -14,6 +14,8 @@
 // (fm_scorer_op.h:134-136).  Row-group and column reductions are warp shuffles.
 // reg_score is reduced warp -> block -> per-block partial -> one fixed-order
 // pass (deterministic; no float atomics on the scalar).
+#include <mutex>
+
 #include "fm_common.cuh"
 
 namespace fm {
@@ -267,6 +269,95 @@ FM_EXPORT int fm_grad(const int32_t* feature_ids, const float* params, int64_t p
                                       batch, (int)factor_num, factor_lambda, bias_lambda, pred_grad, reg_grad,
                                       reg_grad_dev, params_grad, blocks, stream);
   if (rc != FM_OK) return rc;
+  FM_LAUNCH_CHECK();
+  return FM_OK;
+}
+
+// ---------------------------------------------------------------------------
+// fm_score_noalloc: fm_score for callers that have no way to hand over a
+// workspace.  (No counterpart in the reference.)
+//
+// fm_score needs one float of scratch per thread block (the per-block partial
+// sums of reg_score).  Some hosts cannot give us that memory: a serving process
+// whose framework grabbed the whole device for its own pool at start-up (a
+// plugin's cudaMalloc then fails, or is simply forbidden by the host's rules),
+// or a scoring thread on a latency budget that must not take the device-wide
+// lock and implicit synchronisation cudaMalloc / cudaFree bring with them.
+// For them the scratch lives in the library image itself: a fixed array in
+// device memory that every GPU loading this library carries until the process
+// exits (kNoAllocMaxBlocks floats = 512 KiB).
+//
+// Rules that follow from sharing one array:
+//   * batch is limited to FM_SCORE_NOALLOC_MAX_BATCH examples; larger batches
+//     are refused with FM_E_LIMIT (use fm_score with your own workspace).
+//   * every call on a device uses the same array and leaves its partial sums
+//     behind.  Nothing has to start at zero -- each launch overwrites exactly
+//     the entries its own reduction reads -- but two calls that overlap on the
+//     GPU (different streams, or several host threads) race on it.  Serialise
+//     them, or use fm_score.
+//   * the first call on each device looks the array's device address up
+//     (cudaGetSymbolAddress, with that device current) and caches it.  Make
+//     that first call during start-up, before any stream capture begins.
+// The call itself allocates nothing, frees nothing and does not synchronise.
+// ---------------------------------------------------------------------------
+namespace fm {
+namespace {
+
+constexpr int64_t kNoAllocMaxBatch = FM_SCORE_NOALLOC_MAX_BATCH;
+constexpr int64_t kNoAllocMaxBlocks = (kNoAllocMaxBatch + kWarps - 1) / kWarps;
+constexpr int kMaxDevices = 64;
+
+// In host code this name is only a handle for the runtime; the address kernels
+// can use comes from cudaGetSymbolAddress below.
+static __device__ __align__(256) float g_score_noalloc_scratch[kNoAllocMaxBlocks];
+
+static float* g_noalloc_ptr[kMaxDevices];  // per device, filled on first use
+static std::mutex g_noalloc_mu;
+
+static int noalloc_scratch_for_current_device(float** out) {
+  int dev = -1;
+  FM_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices)
+    return fm_fail(FM_E_LIMIT, "fm_score_noalloc: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    FM_CUDA(cudaGetSymbolAddress(&p, g_score_noalloc_scratch));
+    if (p == nullptr) return fm_fail(FM_E_CUDA, "fm_score_noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_noalloc_ptr[dev];
+  return FM_OK;
+}
+
+}  // namespace
+}  // namespace fm
+
+FM_EXPORT int fm_score_noalloc(const int32_t* feature_ids, const float* params, int64_t params_ld,
+                               const float* feature_vals, const int32_t* feature_poses, int64_t batch,
+                               int64_t factor_num, float factor_lambda, float bias_lambda, float* pred_score,
+                               float* reg_score, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  FM_REQUIRE(batch >= 0 && factor_num >= 0 && params_ld >= factor_num + 1, "fm_score_noalloc: bad shape");
+  if (batch > kNoAllocMaxBatch)
+    return fm_fail(FM_E_LIMIT,
+                   "fm_score_noalloc: batch %lld exceeds the built-in scratch (FM_SCORE_NOALLOC_MAX_BATCH = %lld); "
+                   "call fm_score with a caller-provided workspace instead",
+                   (long long)batch, (long long)kNoAllocMaxBatch);
+  FM_REQUIRE(reg_score && feature_poses, "fm_score_noalloc: null pointer");
+  FM_REQUIRE(batch == 0 || (pred_score && params), "fm_score_noalloc: null pointer");
+  float* partials = nullptr;
+  const int rc0 = noalloc_scratch_for_current_device(&partials);
+  if (rc0 != FM_OK) return rc0;
+  const unsigned blocks = (unsigned)((batch + kWarps - 1) / kWarps);
+  if (batch > 0) {
+    const int rc = dispatch<ScoreLaunch>(factor_num, feature_ids, params, params_ld, feature_vals, feature_poses,
+                                         batch, (int)factor_num, factor_lambda, bias_lambda, pred_score,
+                                         partials, blocks, stream);
+    if (rc != FM_OK) return rc;
+    FM_LAUNCH_CHECK();
+  }
+  reduce_partials_kernel<<<1, 256, 0, stream>>>(partials, (int)blocks, 1.0f, reg_score);
   FM_LAUNCH_CHECK();
   return FM_OK;
 }

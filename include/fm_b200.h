@@ -133,6 +133,25 @@ int fm_score(const int32_t* feature_ids, const float* params, int64_t params_ld,
              int64_t factor_num, float factor_lambda, float bias_lambda, float* pred_score,
              float* reg_score, void* workspace, size_t workspace_bytes, void* stream);
 
+/* fm_score without a workspace argument.  It has no counterpart in the reference.
+ * For hosts that cannot allocate device memory for us -- a serving framework that
+ * reserved the whole GPU for its own pool so a plugin's cudaMalloc fails or is
+ * forbidden, or a latency-bound scoring thread that must stay clear of
+ * cudaMalloc/cudaFree's device-wide lock and implicit synchronisation.  The
+ * per-block scratch fm_score needs sits in a fixed device array inside the
+ * library (512 KiB, held by every GPU that loads the library until exit), so:
+ *   - batch <= FM_SCORE_NOALLOC_MAX_BATCH, else FM_E_LIMIT (use fm_score);
+ *   - all calls on a device share that array and it keeps the last call's
+ *     contents; calls that overlap on the GPU race -- serialise them;
+ *   - the first call on each device resolves the array's device address
+ *     (cudaGetSymbolAddress); make it at start-up, before any stream capture.
+ * Allocates nothing, frees nothing, never synchronises.  Same results as fm_score. */
+#define FM_SCORE_NOALLOC_MAX_BATCH 1048576
+int fm_score_noalloc(const int32_t* feature_ids, const float* params, int64_t params_ld,
+                     const float* feature_vals, const int32_t* feature_poses, int64_t batch,
+                     int64_t factor_num, float factor_lambda, float bias_lambda,
+                     float* pred_score, float* reg_score, void* stream);
+
 /* ---- LS: loss and d loss / d pred, tffm/fm_model.py:311-316, :324-326 ----
  * loss = mean_i w_i l(pred_i, y_i); pred_grad_i = w_i l'(pred_i, y_i) / batch.
  * weights may be NULL (all ones, :66).  loss is a device float. */
