@@ -1,0 +1,49 @@
+"""run_tffm.py train / predict driven by a sample.cfg-shaped config (configs[0] in small)."""
+import os
+import re
+import shutil
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("loss_type", ["mse", "logistic"])
+def test_train_then_predict_cli(tmp_path, loss_type):
+    for f in ("train_0", "train_1", "weight_0", "weight_1", "test_0"):
+        shutil.copy(os.path.join(ROOT, "data", f), tmp_path / f)
+    cfg = open(os.path.join(ROOT, "sample.cfg")).read()
+    cfg = cfg.replace("./data/", str(tmp_path) + "/").replace("./log", str(tmp_path / "log"))
+    cfg = cfg.replace("batch_size = 50000", "batch_size = 400").replace("epoch_num = 20", "epoch_num = 3")
+    cfg = cfg.replace("factor_num = 100", "factor_num = 20").replace("loss_type = mse", "loss_type = " + loss_type)
+    cfg = cfg.replace("learning_rate = 0.01", "learning_rate = 0.05")
+    (tmp_path / "t.cfg").write_text(cfg)
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "run_tffm.py"), "train", str(tmp_path / "t.cfg"), "-m",
+                          "-t", str(tmp_path / "trace")], capture_output=True, text=True, env=env, cwd=ROOT)
+    assert out.returncode == 0, out.stdout + out.stderr
+    losses = [float(x) for x in re.findall(r"-- Global Step: \d+; Avg loss: ([0-9.]+);", out.stdout)]
+    assert len(losses) == 15                                   # 3 epochs x 2000 lines / 400
+    assert np.mean(losses[-3:]) < np.mean(losses[:3])
+    assert "Average speed:" in out.stdout and "Model saved to" in out.stdout and "speed:" in out.stdout
+    assert (tmp_path / "log" / "model.ckpt.pt").exists() and (tmp_path / "trace.json").exists()
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "run_tffm.py"), "predict", str(tmp_path / "t.cfg")],
+                         capture_output=True, text=True, env=env, cwd=ROOT)
+    assert out.returncode == 0, out.stdout + out.stderr
+    scores = [float(x) for x in open(tmp_path / "test_0_score")]
+    assert len(scores) == 500 and np.isfinite(scores).all()
+    # the restored model scores the same lines identically through the Python API
+    import torch
+    from tffm.fm_model import Model
+    m = Model(str(tmp_path / "t.cfg")).build(seed=0)
+    m.restore(str(tmp_path / "log" / "model.ckpt.pt"))
+    lines = open(tmp_path / "test_0").read().splitlines()
+    np.testing.assert_allclose(m.predict(lines).cpu().numpy(), np.float32(scores), rtol=1e-6)
+    # unsupported tasks say so
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "run_tffm.py"), "generate", str(tmp_path / "t.cfg")],
+                         capture_output=True, text=True, env=env, cwd=ROOT)
+    assert out.returncode == 2
