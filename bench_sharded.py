@@ -1,0 +1,97 @@
+"""bench.py's multi-GPU leg: vocab-sharded FM training, one process per GPU (torchrun).
+
+Weak scaling: every rank parses its own 65 536-line cfg2 batch per step (global batch =
+65 536 x N); the 2^24-row table and its Adagrad accumulator are row-partitioned id % N.
+Timing: CUDA events on each rank around the K timed steps, barrier + synchronize on both
+sides, MAX over ranks.
+"""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+import bench_data
+
+
+def run_sharded(args, cfg, workload_config):
+    from bench import METRIC, UNIT, ClockSampler, algorithmic_bytes, measured_peak_gbs
+    from fast_tffm_b200.fm_model import Model
+    from fast_tffm_b200.fm_ops import PackedLines
+    from fast_tffm_b200.sharded import ShardedModel
+
+    world, rank = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"])
+    local_rank = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist.init_process_group("nccl", device_id=dev)
+    b, k = cfg["batch"], cfg["factor_num"]
+    model = Model(vocabulary_size=cfg["vocab"], factor_num=k, batch_size=b * world, hash_feature_id=True,
+                  loss_type=cfg["loss_type"], learning_rate=cfg["learning_rate"],
+                  adagrad_init_accumulator=cfg["init_acc"], factor_lambda=cfg["factor_lambda"],
+                  bias_lambda=cfg["bias_lambda"])
+    m = ShardedModel(model, device=dev).build(seed=0)
+    host, devb = [], []
+    for i in range(args.batches):
+        text, off, _ = bench_data.criteo_batch(b, 1000 * (rank + 1) + i, args.dist)
+        ht, ho = torch.from_numpy(bench_data.pad16(text)).pin_memory(), torch.from_numpy(off).pin_memory()
+        host.append(PackedLines(ht, ho))
+        devb.append(PackedLines(ht.to(dev), ho.to(dev)))
+
+    def timed(batches, steps, base):
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        loss = None
+        for s in range(steps):
+            loss = m.train_step(batches[(base + s) % len(batches)], global_batch=b * world)
+        t1.record()
+        torch.cuda.synchronize()
+        dist.barrier()
+        ms = torch.tensor([t0.elapsed_time(t1)], device=dev)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), loss
+
+    for s in range(args.warmup):
+        m.train_step(devb[s % len(devb)], global_batch=b * world)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    total_ms, loss = timed(devb, args.steps, args.warmup)
+    clocks = sampler.stop()
+    e2e_ms, _ = timed(host, args.steps, args.warmup)            # host buffers: H2D of the text inside the region
+
+    stats = torch.tensor([m.last["nnz"], m.last["n_unique"], m.last["sent_rows"]], dtype=torch.float64, device=dev)
+    dist.all_reduce(stats)
+    if rank == 0:
+        nnz, nuniq, sent = (float(x) / world for x in stats.tolist())
+        text_bytes = int(host[0].offsets[-1])
+        alg = algorithmic_bytes(nnz, nuniq, b, k, text_bytes, True)
+        peak, peak_kind = measured_peak_gbs()
+        step_s = total_ms / args.steps * 1e-3
+        gld = (k + 3 + 3) // 4 * 4
+        ld = (k + 1 + 3) // 4 * 4
+        xbytes = sent * (8 + 4 * ld + 4 * gld)                  # per rank per direction per step
+        line = {
+            "metric": METRIC, "value": args.steps * b * world / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, world, b),
+            "roofline": {"bound": "hbm", "kernel": "whole step (per rank)", "achieved": round(sum(alg.values()) / step_s / 1e9, 1),
+                         "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
+                         "frac": round(sum(alg.values()) / step_s / 1e9 / peak, 4), "traffic": None,
+                         "exchange": {"bytes_per_rank_per_direction": int(xbytes),
+                                      "gbs_if_exchange_were_the_whole_step": round(xbytes / step_s / 1e9, 1),
+                                      "nvlink_peer_copy_gbs_measured_reference": 770}},
+            "cpu_baseline": None,
+            "e2e": {"value": args.steps * b * world / (e2e_ms * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": int(host[0].text.numel() + host[0].offsets.numel() * 8) * world,
+                    "d2h_bytes_per_step": 8 * world, "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": 20 * args.steps,
+            "clocks": clocks, "final_loss": loss, "nnz_per_rank": nnz, "unique_per_rank": nuniq,
+        }
+        print(json.dumps(line))
+    dist.barrier()
+    dist.destroy_process_group()

@@ -59,7 +59,7 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
                            const float* __restrict__ vals, const int32_t* __restrict__ poses,
                            const float* __restrict__ labels, const float* __restrict__ weights, int64_t batch,
                            int K, const float* __restrict__ table, int64_t ld, float lam_f, float lam_b,
-                           int loss_kind, float* __restrict__ pred, float* __restrict__ gacc, int64_t gacc_ld,
+                           int loss_kind, float inv_batch, float* __restrict__ pred, float* __restrict__ gacc, int64_t gacc_ld,
                            float* __restrict__ partials, const unsigned long long* __restrict__ guard) {
   constexpr int RPW = 32 / LPR;
   __shared__ float s_loss[kWarps], s_reg[kWarps];
@@ -68,7 +68,6 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
   const int vc_table = (int)(ld >> 2), vc_acc = (int)(gacc_ld >> 2);
   const bool active = !(guard && *guard != kNoError);
   float loss_acc = 0.f, reg_acc = 0.f;
-  const float inv_batch = 1.0f / (float)batch;
 
   for (int64_t i = (int64_t)blockIdx.x * kWarps + warp; active && i < batch; i += (int64_t)gridDim.x * kWarps) {
     const int start = poses[i], end = poses[i + 1];
@@ -311,7 +310,8 @@ FM_EXPORT size_t fm_fused_workspace(int64_t batch) {
 FM_EXPORT int fm_fused_score_scatter(const int64_t* feature_ids, const int32_t* local_ids, const float* feature_vals,
                                      const int32_t* feature_poses, const float* labels, const float* weights,
                                      int64_t batch, int64_t factor_num, const float* table, int64_t table_ld,
-                                     float factor_lambda, float bias_lambda, int loss_kind, float* pred_score,
+                                     float factor_lambda, float bias_lambda, int loss_kind, int64_t loss_batch,
+                                     float* pred_score,
                                      float* loss, float* reg_score, float* gacc, int64_t gacc_ld,
                                      const uint64_t* guard, void* workspace, size_t workspace_bytes, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
@@ -330,15 +330,17 @@ FM_EXPORT int fm_fused_score_scatter(const int64_t* feature_ids, const int32_t* 
     return fm_fail(FM_E_LIMIT, "fm_fused_score_scatter: factor_num %lld too large", (long long)factor_num);
   const int blocks = fused_blocks(batch);
   float* partials = reinterpret_cast<float*>(workspace);
+  const int64_t denom = loss_batch > 0 ? loss_batch : batch;
+  const float inv_batch = denom > 0 ? 1.0f / (float)denom : 0.f;
 #define CALL(LPR, T)                                                                                              \
   fused_score_scatter_kernel<LPR, T><<<blocks, kWarps * 32, 0, stream>>>(                                         \
       feature_ids, local_ids, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, table, table_ld, \
-      factor_lambda, bias_lambda, loss_kind, pred_score, gacc, gacc_ld, partials,                                 \
+      factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, gacc, gacc_ld, partials,                                 \
       reinterpret_cast<const unsigned long long*>(guard))
   FM_DISPATCH_SHAPE(sh, CALL)
 #undef CALL
   FM_LAUNCH_CHECK();
-  reduce2_kernel<<<1, 256, 0, stream>>>(partials, blocks, batch > 0 ? 1.0f / (float)batch : 0.f, loss, reg_score);
+  reduce2_kernel<<<1, 256, 0, stream>>>(partials, blocks, inv_batch, loss, reg_score);
   FM_LAUNCH_CHECK();
   return FM_OK;
 }

@@ -1,0 +1,210 @@
+// fm_shard.cu -- kernels around the all-to-all exchange of the vocab-sharded table.
+//
+// The reference shards the table over TF parameter servers: vocab_block_i lives on
+// ps task i % n_ps, embedding_lookup's "mod" strategy routes id -> block id % nb,
+// row id // nb, and sparse gradients travel back the same way
+// (tffm/fm_model.py:269-291, run_tffm.py:181-206).  Here rank id % G owns row id // G
+// and the routing is explicit:
+//   fm_shard_bucket      stable counting sort of the batch's distinct ids by owner:
+//                        send_ids (grouped by owner), pos[u] = slot of distinct id u
+//                        in that order, counts[G]
+//   fm_shard_remap       per occurrence: slot = pos[local_id]   (index into the rows
+//                        that come back from the owners, and into the gradient
+//                        accumulator rows that go out to them)
+//   fm_shard_local_rows  owner side: row = id / G
+//   fm_shard_combine     owner side: accumulator rows received from several ranks for
+//                        the same id are summed BEFORE Adagrad squares the gradient, so
+//                        the update equals the single-process one
+#include "fm_common.cuh"
+
+namespace fm {
+namespace {
+
+constexpr int kBThreads = 256, kBItems = 4, kBTile = kBThreads * kBItems, kMaxRanks = 64;
+
+__device__ __forceinline__ int owner_of(int64_t id, int g) { return (int)((uint64_t)id % (uint64_t)g); }
+
+__global__ void __launch_bounds__(kBThreads)
+bucket_hist_kernel(const int64_t* __restrict__ ids, int64_t n, int g, int* __restrict__ block_counts) {
+  __shared__ int s_cnt[kMaxRanks];
+  if (threadIdx.x < kMaxRanks) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const int64_t base = (int64_t)blockIdx.x * kBTile + threadIdx.x * kBItems;
+#pragma unroll
+  for (int k = 0; k < kBItems; ++k)
+    if (base + k < n) atomicAdd(&s_cnt[owner_of(ids[base + k], g)], 1);
+  __syncthreads();
+  if (threadIdx.x < g) block_counts[(int64_t)blockIdx.x * g + threadIdx.x] = s_cnt[threadIdx.x];
+}
+
+// exclusive scan of block_counts in owner-major order: base[blk][o] = sum of counts of
+// all smaller owners + same owner in earlier blocks.  One block.
+__global__ void __launch_bounds__(256)
+bucket_offsets_kernel(const int* __restrict__ block_counts, int64_t n_blocks, int g, int64_t* __restrict__ block_base,
+                      int64_t* __restrict__ counts) {
+  __shared__ long long s_part[256];
+  __shared__ long long s_owner_base[kMaxRanks + 1];
+  const int tid = threadIdx.x;
+  if (tid == 0) s_owner_base[0] = 0;
+  for (int o = 0; o < g; ++o) {
+    // per-thread contiguous segment of blocks
+    const int64_t per = (n_blocks + 255) / 256, lo = tid * per, hi = min(lo + per, n_blocks);
+    long long sum = 0;
+    for (int64_t b = lo; b < hi; ++b) sum += block_counts[b * g + o];
+    s_part[tid] = sum;
+    __syncthreads();
+    if (tid == 0) {
+      long long run = 0;
+      for (int t = 0; t < 256; ++t) { const long long v = s_part[t]; s_part[t] = run; run += v; }
+      counts[o] = run;
+      s_owner_base[o + 1] = s_owner_base[o] + run;
+    }
+    __syncthreads();
+    long long run = s_owner_base[o] + s_part[tid];
+    for (int64_t b = lo; b < hi; ++b) { block_base[b * g + o] = run; run += block_counts[b * g + o]; }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(kBThreads)
+bucket_scatter_kernel(const int64_t* __restrict__ ids, int64_t n, int g, const int64_t* __restrict__ block_base,
+                      int64_t* __restrict__ send_ids, int32_t* __restrict__ pos) {
+  __shared__ int s_warp[kBThreads / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t base = (int64_t)blockIdx.x * kBTile + tid * kBItems;
+  int64_t id[kBItems];
+  int own[kBItems];
+#pragma unroll
+  for (int k = 0; k < kBItems; ++k) {
+    id[k] = base + k < n ? ids[base + k] : 0;
+    own[k] = base + k < n ? owner_of(id[k], g) : -1;
+  }
+  for (int o = 0; o < g; ++o) {
+    int mine = 0;
+#pragma unroll
+    for (int k = 0; k < kBItems; ++k) mine += own[k] == o;
+    int incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int v = __shfl_up_sync(kFull, incl, d);
+      if (lane >= d) incl += v;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    int before = incl - mine;
+    for (int w = 0; w < warp; ++w) before += s_warp[w];
+    int64_t slot = block_base[(int64_t)blockIdx.x * g + o] + before;
+#pragma unroll
+    for (int k = 0; k < kBItems; ++k)
+      if (own[k] == o) {
+        send_ids[slot] = id[k];
+        pos[base + k] = (int32_t)slot;
+        ++slot;
+      }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(256)
+remap_kernel(const int32_t* __restrict__ local, int64_t n_max, const int64_t* __restrict__ n_dev,
+             const int32_t* __restrict__ pos, int64_t* __restrict__ slot64, int32_t* __restrict__ slot32) {
+  const int64_t n = n_dev ? min(*n_dev, n_max) : n_max;
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t s = pos[local[j]];
+    slot64[j] = s;
+    slot32[j] = s;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+local_rows_kernel(const int64_t* __restrict__ ids, int64_t n, int g, int64_t* __restrict__ rows) {
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x)
+    rows[j] = (int64_t)((uint64_t)ids[j] / (uint64_t)g);
+}
+
+// dst[index[i], :] += src[i, :]  as float4 vector atomics; ld multiple of 4
+__global__ void __launch_bounds__(256)
+combine_rows_kernel(const float* __restrict__ src, const int32_t* __restrict__ index, int64_t n, int vec_per_row,
+                    float* __restrict__ dst) {
+  const int64_t total = n * vec_per_row;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = t / vec_per_row;
+    const int v = (int)(t - i * vec_per_row);
+    const float4 x = __ldg(reinterpret_cast<const float4*>(src) + t);
+    float* d = dst + ((int64_t)index[i] * vec_per_row + v) * 4;
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d), "f"(x.x), "f"(x.y), "f"(x.z), "f"(x.w)
+                 : "memory");
+  }
+}
+
+static inline unsigned grid_for(int64_t n, int per_block) {
+  int64_t b = (n + per_block - 1) / per_block;
+  if (b > 148 * 16) b = 148 * 16;
+  return (unsigned)(b < 1 ? 1 : b);
+}
+
+}  // namespace
+}  // namespace fm
+
+using namespace fm;
+
+FM_EXPORT size_t fm_shard_bucket_workspace(int64_t n, int64_t n_ranks) {
+  const int64_t blocks = n <= 0 ? 1 : (n + kBTile - 1) / kBTile;
+  return fm_align_up((size_t)blocks * (size_t)n_ranks * (sizeof(int) + sizeof(int64_t)) + 256, 256);
+}
+
+FM_EXPORT int fm_shard_bucket(const int64_t* ids, int64_t n, int64_t n_ranks, int64_t* send_ids, int32_t* pos,
+                              int64_t* counts, void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  FM_REQUIRE(n >= 0 && n_ranks >= 1, "fm_shard_bucket: bad size");
+  if (n_ranks > kMaxRanks) return fm_fail(FM_E_LIMIT, "fm_shard_bucket: more than %d ranks", kMaxRanks);
+  FM_REQUIRE(counts && workspace, "fm_shard_bucket: null pointer");
+  FM_REQUIRE(n == 0 || (ids && send_ids && pos), "fm_shard_bucket: null pointer");
+  if (workspace_bytes < fm_shard_bucket_workspace(n, n_ranks))
+    return fm_fail(FM_E_WORKSPACE, "fm_shard_bucket: workspace too small");
+  const int64_t blocks = n <= 0 ? 1 : (n + kBTile - 1) / kBTile;
+  int64_t* block_base = reinterpret_cast<int64_t*>(workspace);
+  int* block_counts = reinterpret_cast<int*>(block_base + blocks * n_ranks);
+  bucket_hist_kernel<<<(unsigned)blocks, kBThreads, 0, stream>>>(ids, n, (int)n_ranks, block_counts);
+  FM_LAUNCH_CHECK();
+  bucket_offsets_kernel<<<1, 256, 0, stream>>>(block_counts, blocks, (int)n_ranks, block_base, counts);
+  FM_LAUNCH_CHECK();
+  if (n > 0) {
+    bucket_scatter_kernel<<<(unsigned)blocks, kBThreads, 0, stream>>>(ids, n, (int)n_ranks, block_base, send_ids, pos);
+    FM_LAUNCH_CHECK();
+  }
+  return FM_OK;
+}
+
+FM_EXPORT int fm_shard_remap(const int32_t* local_ids, int64_t n, const int64_t* n_dev, const int32_t* pos,
+                             int64_t* slot64, int32_t* slot32, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  FM_REQUIRE(n >= 0, "fm_shard_remap: negative n");
+  if (n == 0) return FM_OK;
+  FM_REQUIRE(local_ids && pos && slot64 && slot32, "fm_shard_remap: null pointer");
+  remap_kernel<<<grid_for(n, 256), 256, 0, stream>>>(local_ids, n, n_dev, pos, slot64, slot32);
+  FM_LAUNCH_CHECK();
+  return FM_OK;
+}
+
+FM_EXPORT int fm_shard_local_rows(const int64_t* ids, int64_t n, int64_t n_ranks, int64_t* rows, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  FM_REQUIRE(n >= 0 && n_ranks >= 1, "fm_shard_local_rows: bad size");
+  if (n == 0) return FM_OK;
+  FM_REQUIRE(ids && rows, "fm_shard_local_rows: null pointer");
+  local_rows_kernel<<<grid_for(n, 256), 256, 0, stream>>>(ids, n, (int)n_ranks, rows);
+  FM_LAUNCH_CHECK();
+  return FM_OK;
+}
+
+FM_EXPORT int fm_shard_combine(const float* src_rows, const int32_t* index, int64_t n, int64_t ld, float* dst_rows,
+                               void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  FM_REQUIRE(n >= 0 && ld > 0 && ld % 4 == 0, "fm_shard_combine: ld must be a positive multiple of 4");
+  if (n == 0) return FM_OK;
+  FM_REQUIRE(src_rows && index && dst_rows, "fm_shard_combine: null pointer");
+  FM_REQUIRE((((uintptr_t)src_rows | (uintptr_t)dst_rows) & 15) == 0, "fm_shard_combine: 16-byte alignment required");
+  combine_rows_kernel<<<grid_for(n * (ld / 4), 256), 256, 0, stream>>>(src_rows, index, n, (int)(ld / 4), dst_rows);
+  FM_LAUNCH_CHECK();
+  return FM_OK;
+}

@@ -250,7 +250,7 @@ class Model(object):
             check(lib.fm_fused_score_scatter(
                 ptr(b["ids"]), ptr(b["local"]), ptr(b["vals"]), ptr(b["poses"]), ptr(b["labels"]), ptr(weights),
                 n_lines, k, ptr(self.table), self.ld, self.factor_lambda, self.bias_lambda,
-                _lib.LOSS_KIND[self.loss_type], ptr(b["pred"]), _off(b["status"], 6), _off(b["status"], 7),
+                _lib.LOSS_KIND[self.loss_type], 0, ptr(b["pred"]), _off(b["status"], 6), _off(b["status"], 7),
                 ptr(b["gacc"]), b["gacc_ld"], ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st),
                 "fm_fused_score_scatter")
             mark("score_scatter")

@@ -202,14 +202,17 @@ int fm_sparse_adagrad(float* table, float* accum, int64_t table_ld, const int64_
  * fm_fused_adagrad: for u < U, forms G from gacc[u] and table[ori_ids[u]] and
  * applies TF1 SparseApplyAdagrad to table / accum; rg = reg_grad (the factor the
  * objective puts on reg_score: 1 / batch_size, tffm/fm_model.py:345-347).
- * guard: as in fm_sparse_adagrad; both calls are no-ops when it is tripped. */
+ * guard: as in fm_sparse_adagrad; both calls are no-ops when it is tripped.
+ * loss_batch: denominator of the mean loss and of d loss / d pred; 0 = batch.  A rank
+ * that holds a slice of a global batch passes the global size and sums the per-rank
+ * losses afterwards. */
 int64_t fm_fused_gacc_ld(int64_t factor_num);
 size_t fm_fused_workspace(int64_t batch);
 int fm_fused_score_scatter(const int64_t* feature_ids, const int32_t* local_ids,
                            const float* feature_vals, const int32_t* feature_poses,
                            const float* labels, const float* weights, int64_t batch,
                            int64_t factor_num, const float* table, int64_t table_ld,
-                           float factor_lambda, float bias_lambda, int loss_kind,
+                           float factor_lambda, float bias_lambda, int loss_kind, int64_t loss_batch,
                            float* pred_score, float* loss, float* reg_score, float* gacc,
                            int64_t gacc_ld, const uint64_t* guard, void* workspace,
                            size_t workspace_bytes, void* stream);
@@ -217,6 +220,24 @@ int fm_fused_adagrad(float* table, float* accum, int64_t table_ld, const int64_t
                      int64_t n_unique, const int64_t* n_unique_dev, int64_t factor_num,
                      float* gacc, int64_t gacc_ld, float learning_rate, float factor_lambda,
                      float bias_lambda, float reg_grad, const uint64_t* guard, void* stream);
+
+/* ---- D1: the parameter-server sharding of tffm/fm_model.py:269-291 + run_tffm.py:181-206,
+ * as explicit routing around an all-to-all: rank id % n_ranks owns table row id / n_ranks ----
+ * fm_shard_bucket: stable counting sort of `ids` (the batch's distinct ids) by owner:
+ *   send_ids[n] grouped by owner, pos[u] = position of ids[u] in send_ids, counts[n_ranks].
+ * fm_shard_remap: slot64[j] = slot32[j] = pos[local_ids[j]] (row index of occurrence j in
+ *   the rows received back / the accumulator rows sent out).
+ * fm_shard_local_rows: rows[j] = ids[j] / n_ranks (owner side).
+ * fm_shard_combine: dst_rows[index[i], :] += src_rows[i, :] (owner side: accumulator rows
+ *   from several ranks for one id are summed before the Adagrad square); ld % 4 == 0. */
+size_t fm_shard_bucket_workspace(int64_t n, int64_t n_ranks);
+int fm_shard_bucket(const int64_t* ids, int64_t n, int64_t n_ranks, int64_t* send_ids, int32_t* pos,
+                    int64_t* counts, void* workspace, size_t workspace_bytes, void* stream);
+int fm_shard_remap(const int32_t* local_ids, int64_t n, const int64_t* n_dev, const int32_t* pos,
+                   int64_t* slot64, int32_t* slot32, void* stream);
+int fm_shard_local_rows(const int64_t* ids, int64_t n, int64_t n_ranks, int64_t* rows, void* stream);
+int fm_shard_combine(const float* src_rows, const int32_t* index, int64_t n, int64_t ld,
+                     float* dst_rows, void* stream);
 
 #ifdef __cplusplus
 }

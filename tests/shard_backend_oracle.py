@@ -1,0 +1,96 @@
+"""CPU stand-in for CudaShardKernels, for tests only: numpy + the oracle on CPU tensors.
+
+Lets the host-side orchestration of fast_tffm_b200.sharded.ShardedModel (routing,
+all-to-all split sizes, owner-side combine order) run under gloo with world_size 2 on a box
+without GPUs.  It is also an independent (numpy, float64) statement of the fused path's
+factorised gradient sums.  Never imported by the product package.
+"""
+import numpy as np
+import torch
+
+from oracle import oracle as O
+
+
+def _t(a, dtype=None):
+    return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype)
+
+
+class OracleShardKernels:
+    def parse_unique(self, packed, vocab, hashed):
+        text, off = packed.text.numpy(), packed.offsets.numpy()
+        labels, sizes, ids, vals = O.parse(text, off, vocab, hashed)
+        ori, local = O.unique(ids)
+        return dict(labels=_t(labels), poses=_t(O.poses(sizes)), ids=_t(ids), vals=_t(vals), ori=_t(ori),
+                    local=_t(local))
+
+    def unique(self, ids):
+        ori, local = O.unique(ids.numpy())
+        return _t(ori), _t(local)
+
+    def bucket(self, ori, n_ranks):
+        ids = ori.numpy()
+        owner = (ids % n_ranks).astype(np.int64)
+        perm = np.argsort(owner, kind="stable")
+        pos = np.empty(ids.size, np.int32)
+        pos[perm] = np.arange(ids.size, dtype=np.int32)
+        return _t(ids[perm]), _t(pos), _t(np.bincount(owner, minlength=n_ranks).astype(np.int64))
+
+    def remap(self, local, pos):
+        s = pos.numpy()[local.numpy()]
+        return _t(s.astype(np.int64)), _t(s.astype(np.int32))
+
+    def score_scatter(self, slot64, slot32, vals, poses, labels, weights, k, rows, lf, lb, loss_type, global_batch,
+                      gacc):
+        fids, x, ps = slot32.numpy(), vals.numpy().astype(np.float64), poses.numpy()
+        params = rows.numpy()
+        b = labels.numel()
+        pred, reg = O.score(fids, params, vals.numpy(), ps, lf, lb, k=k)
+        w = None if weights is None else weights.numpy()
+        loss, pg = O.loss(pred, labels.numpy(), w, loss_type)
+        scale = b / float(global_batch)
+        loss, pg = loss * scale, pg.astype(np.float64) * scale
+        ex = np.repeat(np.arange(b), np.diff(ps))
+        v = params[fids, 1:k + 1].astype(np.float64)
+        s = np.zeros((b, k))
+        np.add.at(s, ex, x[:, None] * v)
+        pgx = pg[ex] * x
+        acc = np.zeros((gacc.shape[0], gacc.shape[1]))
+        np.add.at(acc[:, 0], fids, pgx)
+        np.add.at(acc[:, 1:k + 1], fids, pgx[:, None] * s[ex])
+        np.add.at(acc[:, k + 1], fids, pgx * x)
+        np.add.at(acc[:, k + 2], fids, 1.0)
+        gacc += _t(acc, torch.float32)
+        return _t(pred), _t(np.float32([loss, reg]))
+
+    def score(self, slot32, rows, vals, poses, k):
+        pred, _ = O.score(slot32.numpy(), rows.numpy(), vals.numpy(), poses.numpy(), 0.0, 0.0, k=k)
+        return _t(pred)
+
+    def local_rows(self, ids, n_ranks):
+        return ids // n_ranks
+
+    def lookup(self, table, rows, k):
+        out = torch.zeros(rows.numel(), table.shape[1])
+        out[:, :k + 1] = table[rows, :k + 1]
+        return out
+
+    def combine(self, src, index, dst):
+        acc = dst.numpy().astype(np.float64)
+        np.add.at(acc, index.numpy(), src.numpy().astype(np.float64))
+        dst.copy_(_t(acc, torch.float32))
+
+    def adagrad(self, table, accum, rows, k, gacc, lr, lf, lb, reg_grad):
+        r = rows.numpy()
+        a = gacc.numpy().astype(np.float64)
+        w = table.numpy()[r, :k + 1].astype(np.float64)
+        cnt, d = a[:, k + 2], a[:, k + 1]
+        g = np.empty_like(w)
+        g[:, 0] = a[:, 0] + cnt * reg_grad * lb * w[:, 0]
+        g[:, 1:] = w[:, 1:] * (cnt * reg_grad * lf - d)[:, None] + a[:, 1:k + 1]
+        h = accum.numpy()[r, :k + 1].astype(np.float64) + g * g
+        accum[rows, :k + 1] = _t(h, torch.float32)
+        table[rows, :k + 1] = _t(w - lr * g / np.sqrt(h.astype(np.float32)), torch.float32)
+        gacc.zero_()
+
+    def gacc_ld(self, k):
+        return (k + 3 + 3) // 4 * 4

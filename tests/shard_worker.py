@@ -1,0 +1,35 @@
+"""worker for the world_size-2 tests of the sharded path (spawned processes import this)"""
+import os
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def run(rank, world, port, backend, lines, weights, cfg_kw, init, steps, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    if backend == "nccl":
+        torch.cuda.set_device(rank)
+        device, kernels = torch.device("cuda", rank), None
+    else:
+        from shard_backend_oracle import OracleShardKernels
+        device, kernels = torch.device("cpu"), OracleShardKernels()
+    dist.init_process_group(backend, rank=rank, world_size=world)
+    from fast_tffm_b200.fm_model import Model
+    from fast_tffm_b200.sharded import ShardedModel
+    m = ShardedModel(Model(**cfg_kw), kernels=kernels, device=device).build(init_table=init)
+    bs = cfg_kw["batch_size"]
+    per = bs // world
+    losses = []
+    for s in range(steps):
+        lo = s * bs + rank * per
+        w = None if weights is None or s % 2 else np.float32(weights[lo:lo + per])
+        losses.append(m.train_step(lines[lo:lo + per], w))
+    pred = m.predict(lines[rank * per:(rank + 1) * per]).cpu().numpy()
+    full = m.gather_full_table().cpu().numpy()
+    if rank == 0:
+        np.save(os.path.join(out_dir, "table.npy"), full)
+        np.save(os.path.join(out_dir, "losses.npy"), np.float64(losses))
+    np.save(os.path.join(out_dir, "pred%d.npy" % rank), pred)
+    dist.barrier()
+    dist.destroy_process_group()
