@@ -95,14 +95,29 @@ FMNP_HD inline uint32_t round_pack(uint64_t q, int64_t lsb_exp, bool sticky) {
 }
 
 // ---- tiers 1 and 2 ---------------------------------------------------------
+#define FMNP_P10F {1e0f, 1e1f, 1e2f, 1e3f, 1e4f, 1e5f, 1e6f, 1e7f, 1e8f, 1e9f, 1e10f}
+#define FMNP_P10D {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11, \
+                   1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22}
+#if defined(__CUDACC__)
+static __device__ __constant__ float kDevP10F[11] = FMNP_P10F;
+static __device__ __constant__ double kDevP10D[23] = FMNP_P10D;
+#endif
+static const float kHostP10F[11] = FMNP_P10F;
+static const double kHostP10D[23] = FMNP_P10D;
+
 FMNP_HD inline float pow10_f32(int i) {
-  const float t[11] = {1e0f, 1e1f, 1e2f, 1e3f, 1e4f, 1e5f, 1e6f, 1e7f, 1e8f, 1e9f, 1e10f};
-  return t[i];
+#if defined(__CUDA_ARCH__)
+  return kDevP10F[i];
+#else
+  return kHostP10F[i];
+#endif
 }
 FMNP_HD inline double pow10_f64(int i) {
-  const double t[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
-                        1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
-  return t[i];
+#if defined(__CUDA_ARCH__)
+  return kDevP10D[i];
+#else
+  return kHostP10D[i];
+#endif
 }
 
 // w * 10^q -> binary32 bits when one of the cheap exact tiers applies

@@ -3,20 +3,21 @@
 // Replaces cc/fm_parser_op.cc:29-51 (Compute: a serial loop over the batch) and
 // :58-109 (ParseLine) plus the tf.cumsum at tffm/fm_model.py:73.
 //
-// Structure (one warp per line, text read as 16-byte words, 512 bytes per
-// warp iteration):
+// Structure (8 lanes per line, 4 lines per warp; text read as 16-byte words):
 //   pass 1 (count): count the ' ' bytes of a line and prove it "regular"
-//       (no NUL / \t\n\v\f\r, no space at the start, after ':' or after a
-//       space).  In a regular line every loop iteration of ParseLine eats
-//       exactly one space, so sizes[i] = spaces - (trailing space ? 1 : 0).
-//       Any other line is counted by the sequential scanner, which follows
-//       ParseLine statement by statement.
+//       (no control bytes, no space at the start, after ':' or after a space)
+//       with word-wide byte flags.  In a regular line every loop iteration of
+//       ParseLine eats exactly one space, so sizes[i] = spaces - (trailing
+//       space ? 1 : 0).  Any other line goes on a list and is counted by a
+//       second, tiny kernel that follows ParseLine statement by statement.
 //   scan: feature_poses = [0, cumsum(sizes)], single pass.
-//   pass 2 (fill): the spaces of a 512-byte chunk are compacted to token
-//       starts in shared memory; each lane parses whole tokens (id[:val]).  A
-//       lane that meets anything but the plain grammar raises a flag and lane 0
-//       re-parses the line sequentially: error reporting and every libc quirk
-//       (whitespace skipping, "inf", hex floats ...) live in that one place.
+//   pass 2 (fill): the token starts of a 128-byte chunk are compacted into
+//       shared memory; each lane parses whole tokens (label, id[:val]) with
+//       the cheap exact number tiers.  A line in which any lane meets anything
+//       else goes on a second list; a tiny kernel re-parses those lines
+//       sequentially: error reporting and every libc quirk (whitespace
+//       skipping, "inf", hex floats, long mantissas ...) live in that one place,
+//       out of the hot kernels' register budget.
 // Numbers are converted by fm_numparse.cuh (bit-exact with glibc).
 #include "fm_common.cuh"
 #include "fm_numparse.cuh"
@@ -26,7 +27,32 @@ namespace fm {
 namespace {
 
 constexpr int kWarpsPerBlock = 8;
-constexpr int kChunk = 512;  // bytes per warp iteration
+constexpr int kLPL = 8;                    // lanes per line
+constexpr int kLinesPerWarp = 32 / kLPL;
+constexpr int kLinesPerBlock = kWarpsPerBlock * kLinesPerWarp;
+constexpr int kChunk = kLPL * 16;          // bytes per group iteration
+constexpr int kSlowThreads = 128, kSlowBlocks = 148;
+
+struct ParseWs {
+  void* scan;        // scan scratch (zeroed per call)
+  int* slow_count;   // [2]: lines queued for the sequential count / fill kernels (zeroed per call)
+  int32_t* slow_a;   // [n_lines] count pass
+  int32_t* slow_b;   // [n_lines] fill pass
+  size_t scan_bytes, zero_bytes, total;
+};
+static inline ParseWs parse_ws(void* base, int64_t n_lines) {
+  ParseWs w;
+  const size_t n = (size_t)(n_lines > 0 ? n_lines : 1);
+  w.scan_bytes = scan_scratch_bytes(n_lines, 4);
+  char* p = reinterpret_cast<char*>(base);
+  w.scan = p;
+  w.slow_count = reinterpret_cast<int*>(p + w.scan_bytes);
+  w.zero_bytes = w.scan_bytes + 256;
+  w.slow_a = reinterpret_cast<int32_t*>(p + w.zero_bytes);
+  w.slow_b = w.slow_a + n;
+  w.total = w.zero_bytes + fm_align_up(2 * n * sizeof(int32_t), 256);
+  return w;
+}
 
 __device__ __forceinline__ void report_error(fm_parse_status* st, int64_t line, int kind) {
   atomicMin(reinterpret_cast<unsigned long long*>(&st->first_error),
@@ -82,77 +108,101 @@ __device__ __forceinline__ uint4 load16(const uint8_t* p) {
   return __ldg(reinterpret_cast<const uint4*>(p));
 }
 
-// 16-bit masks over the 16 bytes of v: bytes equal to `c`
-__device__ __forceinline__ uint32_t eq_mask(const uint4& v, uint32_t c) {
-  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-  uint32_t m = 0;
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    // per-byte equality via the XOR + "has zero byte" trick, exact variant
-    const uint32_t x = w[k] ^ (c * 0x01010101u);
-    const uint32_t z = ~(((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x | 0x7f7f7f7fu);  // 0x80 where byte == 0
-    m |= (((z >> 7) & 1u) | ((z >> 14) & 2u) | ((z >> 21) & 4u) | ((z >> 28) & 8u)) << (4 * k);
-  }
-  return m;
+// ---- byte flags on 32-bit words: bit 7 of byte k set <=> byte k has the property --------
+__device__ __forceinline__ uint32_t flag_eq(uint32_t w, uint32_t c) {   // byte == c (exact)
+  const uint32_t x = w ^ (c * 0x01010101u);
+  return ~(((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x | 0x7f7f7f7fu);
 }
-// bytes in [lo, hi], hi < 128
-__device__ __forceinline__ uint32_t range_mask(const uint4& v, uint32_t lo, uint32_t hi) {
-  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-  uint32_t m = 0;
+__device__ __forceinline__ uint32_t flag_ctrl(uint32_t w) {             // byte < 0x20
+  return ~(((w & 0x7f7f7f7fu) + 0x60606060u) | w | 0x7f7f7f7fu);
+}
+__device__ __forceinline__ uint32_t flag_first_bytes(int n) {           // bytes 0..n-1 (n clipped to 0..4)
+  return n <= 0 ? 0u : n >= 4 ? 0x80808080u : (0x80808080u >> (8 * (4 - n)));
+}
+// flags of the bytes of word k (bytes 4k..4k+3 of a 16-byte group) that lie in [lo, hi)
+__device__ __forceinline__ uint32_t flag_valid(int k, int lo, int hi) {
+  return flag_first_bytes(hi - 4 * k) & ~flag_first_bytes(lo - 4 * k);
+}
+
+__device__ __forceinline__ unsigned group_mask(int lane) {
+  return kLPL == 32 ? kFull : (((1u << kLPL) - 1u) << ((lane / kLPL) * kLPL));
+}
+template <class T>
+__device__ __forceinline__ T group_sum(T v, unsigned gm) {
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      const uint32_t byte = (w[k] >> (8 * b)) & 0xffu;
-      m |= (uint32_t)(byte - lo <= hi - lo) << (4 * k + b);
-    }
-  }
-  return m;
+  for (int o = kLPL / 2; o > 0; o >>= 1) v += __shfl_xor_sync(gm, v, o);
+  return v;
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 parse_count_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ off, int64_t n_lines,
-                   int64_t vocab, int hash, int32_t* __restrict__ sizes, fm_parse_status* st) {
-  const int lane = threadIdx.x & 31;
-  const int64_t line = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-  if (line >= n_lines) return;
+                   int32_t* __restrict__ sizes, int32_t* __restrict__ slow_list, int* __restrict__ slow_count) {
+  const int lane = threadIdx.x & 31, c = lane % kLPL;
+  const unsigned gm = group_mask(lane);
+  const int64_t line = ((int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * kLinesPerWarp + lane / kLPL;
+  if (line >= n_lines) return;  // the whole lane group leaves together
   const int64_t s = off[line], e = off[line + 1] - 1;
   int spaces = 0;
-  bool irregular = false, trail = false;
-  // carry: was the byte just before this lane's first byte a space / ':' (or the line start)?
-  uint32_t carry_iter = 1;  // virtual byte before the line start counts as a space
+  uint32_t irregular = 0, trail = 0;
+  uint32_t carry = 0x80u;  // "the byte before the line start is a space": a leading space is irregular
   for (int64_t pos = s & ~(int64_t)15; pos < e; pos += kChunk) {
-    const int64_t p = pos + lane * 16;
-    uint32_t valid = 0;
-    uint4 v = make_uint4(0, 0, 0, 0);
-    if (p < e) {
-      v = load16(text + p);
-      const int64_t lo = s > p ? s - p : 0, hi = e - p < 16 ? e - p : 16;  // valid bytes [lo, hi)
-      valid = lo < 16 ? ((0xffffu >> (16 - hi)) & (0xffffu << lo)) & 0xffffu : 0;
+    const int64_t p = pos + c * 16;
+    uint32_t w[4] = {0, 0, 0, 0};
+    if (p < e) { const uint4 v = load16(text + p); w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w; }
+    const int lo = s > p ? (int)(s - p) : 0;
+    const int hi = e - p >= 16 ? 16 : (e - p > 0 ? (int)(e - p) : 0);
+    const bool full = lo == 0 && hi == 16;
+    uint32_t sp[4], sc[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      sp[k] = flag_eq(w[k], ' ');
+      sc[k] = sp[k] | flag_eq(w[k], ':');
+      uint32_t bad = flag_ctrl(w[k]);
+      if (!full) {
+        const uint32_t v = flag_valid(k, lo, hi);
+        sp[k] &= v; sc[k] &= v; bad &= v;
+      }
+      irregular |= bad;
+      spaces += __popc(sp[k]);
     }
-    const uint32_t sp = eq_mask(v, ' ') & valid;
-    const uint32_t sc = (sp | eq_mask(v, ':')) & valid;
-    const uint32_t bad = (eq_mask(v, 0) | range_mask(v, 9, 13)) & valid;
-    // previous-byte mask: bit t set when byte t-1 is a space / ':' / the line start
-    uint32_t prev_last = __shfl_up_sync(kFull, (sc >> 15) & 1u, 1);
-    if (lane == 0) prev_last = carry_iter;
-    uint32_t prevm = ((sc << 1) | prev_last) & 0xffffu;
-    if (s > p) prevm |= 1u << (s - p);  // line starts inside this word (lane 0 of the first chunk only)
-    irregular |= (sp & prevm) != 0 || bad != 0;
-    spaces += __popc(sp);
-    if (p <= e - 1 && e - 1 < p + 16) trail = (sp >> (e - 1 - p)) & 1u;
-    carry_iter = __shfl_sync(kFull, (sc >> 15) & 1u, 31);
+    // previous-byte flags: byte t inherits the space/colon flag of byte t-1
+    uint32_t prev_in = __shfl_up_sync(gm, sc[3] >> 24, 1, kLPL);
+    if (c == 0) prev_in = carry;
+    uint32_t pv[4];
+    pv[0] = (sc[0] << 8) | prev_in;
+#pragma unroll
+    for (int k = 1; k < 4; ++k) pv[k] = (sc[k] << 8) | (sc[k - 1] >> 24);
+    if (s > p) pv[(s - p) >> 2] |= 0x80u << (8 * ((s - p) & 3));  // the line starts inside this word
+#pragma unroll
+    for (int k = 0; k < 4; ++k) irregular |= sp[k] & pv[k];
+    if (p <= e - 1 && e - 1 < p + 16) trail = (sp[(e - 1 - p) >> 2] >> (8 * ((e - 1 - p) & 3) + 7)) & 1u;
+    carry = __shfl_sync(gm, sc[3] >> 24, kLPL - 1, kLPL);
   }
-  spaces = warp_sum(spaces);
-  irregular = __any_sync(kFull, irregular);
-  trail = __any_sync(kFull, trail);
-  if (lane == 0) {
-    int32_t cnt = spaces - (trail ? 1 : 0);
+  spaces = group_sum(spaces, gm);
+  irregular = group_sum(irregular != 0 ? 1u : 0u, gm);
+  trail = group_sum(trail, gm);
+  if (c == 0) {
     if (irregular) {
-      cnt = 0;
-      const int rc = parse_line_seq(text + s, e - s, hash, vocab, nullptr, nullptr, nullptr, 0, &cnt);
-      if (rc != FM_PARSE_OK) { report_error(st, line, rc); cnt = 0; }
+      slow_list[atomicAdd(slow_count, 1)] = (int32_t)line;
+      sizes[line] = 0;
+    } else {
+      sizes[line] = spaces - (trail ? 1 : 0);
     }
+  }
+}
+
+// the lines the fast counter could not prove regular: sequential ParseLine, count only
+__global__ void __launch_bounds__(kSlowThreads)
+parse_count_slow_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ off, int64_t vocab, int hash,
+                        int32_t* __restrict__ sizes, const int32_t* __restrict__ slow_list,
+                        const int* __restrict__ slow_count, fm_parse_status* st) {
+  const int n = *slow_count;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+    const int64_t line = slow_list[t];
+    const int64_t s = off[line], e = off[line + 1] - 1;
+    int32_t cnt = 0;
+    const int rc = parse_line_seq(text + s, e - s, hash, vocab, nullptr, nullptr, nullptr, 0, &cnt);
+    if (rc != FM_PARSE_OK) { report_error(st, line, rc); cnt = 0; }
     sizes[line] = cnt;
   }
 }
@@ -170,91 +220,101 @@ struct PosesOut {
 
 // ---- pass 2 ---------------------------------------------------------------
 
-// [+-]digits[.digits][e[+-]digits] through the cheap exact tiers; anything else
-// (or a tier miss) goes through the full glibc-compatible scanner.  Returns the
-// bytes consumed (0 = no conversion).  Leading whitespace is NOT accepted here:
-// strtof would skip it, which breaks the one-space-per-token invariant.
-__device__ __forceinline__ int64_t scan_value(const uint8_t* __restrict__ p, int64_t n, uint32_t* bits) {
-  int64_t i = 0;
-  uint8_t c = fmnp::at(p, n, 0);
-  if (fmnp::is_space(c)) return 0;
+// [+-]digits[.digits][e[+-]digits] through the cheap exact tiers only.  Returns the bytes
+// consumed, or 0 when the text is anything else (leading whitespace, inf/nan, hex, a
+// mantissa or exponent beyond the tiers): the caller then sends the line to the
+// sequential kernel, which knows the whole of strtof.
+__device__ __forceinline__ int scan_value_fast(const uint8_t* __restrict__ p, int n, uint32_t* bits) {
+  int i = 0;
+  uint8_t c = n > 0 ? p[0] : (uint8_t)0;
   uint32_t sign = 0;
-  if (c == '-') { sign = 0x80000000u; c = fmnp::at(p, n, ++i); } else if (c == '+') { c = fmnp::at(p, n, ++i); }
+  if (c == '-') { sign = 0x80000000u; ++i; c = i < n ? p[i] : (uint8_t)0; }
+  else if (c == '+') { ++i; c = i < n ? p[i] : (uint8_t)0; }
   uint64_t w = 0;
   int nd = 0, frac = 0;
-  bool any = false, simple = true;
-  for (; fmnp::is_digit(c); c = fmnp::at(p, n, ++i)) { w = w * 10 + (c - '0'); nd += (w != 0); any = true; }
+  bool any = false;
+  for (; fmnp::is_digit(c); c = ++i < n ? p[i] : (uint8_t)0) { w = w * 10 + (c - '0'); nd += (w != 0); any = true; }
   if (c == '.') {
-    c = fmnp::at(p, n, ++i);
-    for (; fmnp::is_digit(c); c = fmnp::at(p, n, ++i)) { w = w * 10 + (c - '0'); nd += (w != 0); ++frac; any = true; }
+    c = ++i < n ? p[i] : (uint8_t)0;
+    for (; fmnp::is_digit(c); c = ++i < n ? p[i] : (uint8_t)0) { w = w * 10 + (c - '0'); nd += (w != 0); ++frac; any = true; }
   }
-  if (!any || nd > 19) simple = false;
-  int64_t ex = 0;
-  if (simple && (c | 0x20) == 'e') {
-    int64_t k = i + 1;
-    uint8_t d = fmnp::at(p, n, k);
+  if (!any || nd > 19) return 0;
+  int ex = 0;
+  if ((c | 0x20) == 'e') {
+    int k = i + 1;
+    uint8_t d = k < n ? p[k] : (uint8_t)0;
     bool eneg = false;
-    if (d == '-') { eneg = true; d = fmnp::at(p, n, ++k); } else if (d == '+') { d = fmnp::at(p, n, ++k); }
+    if (d == '-') { eneg = true; d = ++k < n ? p[k] : (uint8_t)0; } else if (d == '+') { d = ++k < n ? p[k] : (uint8_t)0; }
     if (fmnp::is_digit(d)) {
-      for (; fmnp::is_digit(d); d = fmnp::at(p, n, ++k)) if (ex < 100000) ex = ex * 10 + (d - '0');
+      for (; fmnp::is_digit(d); d = ++k < n ? p[k] : (uint8_t)0) if (ex < 10000) ex = ex * 10 + (d - '0');
       if (eneg) ex = -ex;
       i = k;
     }
   }
   uint32_t r;
-  if (simple && fmnp::dec_to_f32_fast(w, ex - frac, &r)) { *bits = sign | r; return i; }
-  return fmnp::strtof_bits(p, n, bits);
+  if (!fmnp::dec_to_f32_fast(w, (int64_t)ex - frac, &r)) return 0;
+  *bits = sign | r;
+  return i;
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 parse_fill_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ off, int64_t n_lines,
                   int64_t vocab, int hash, const int32_t* __restrict__ poses, float* __restrict__ labels,
-                  int64_t* __restrict__ ids, float* __restrict__ vals, int64_t capacity, fm_parse_status* st) {
-  __shared__ uint16_t s_tok[kWarpsPerBlock][kChunk];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t line = (int64_t)blockIdx.x * kWarpsPerBlock + warp;
+                  int64_t* __restrict__ ids, float* __restrict__ vals, int64_t capacity,
+                  int32_t* __restrict__ slow_list, int* __restrict__ slow_count) {
+  __shared__ uint8_t s_tok[kWarpsPerBlock][kLinesPerWarp][kChunk + 4];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane / kLPL, c = lane % kLPL;
+  const unsigned gm = group_mask(lane);
+  const int64_t line = ((int64_t)blockIdx.x * kWarpsPerBlock + warp) * kLinesPerWarp + g;
   if (line >= n_lines) return;
   const int64_t s = off[line], e = off[line + 1] - 1;
   const int64_t out_base = poses[line];
   const int32_t cnt = poses[line + 1] - poses[line];
-  bool fail = out_base + cnt > capacity;
-  const bool over_capacity = fail;
-
-  if (lane == 0 && !fail) {  // the label: everything up to the first space
-    uint32_t bits = 0;
-    const int64_t c = scan_value(text + s, e - s, &bits);
-    if (c == 0 || !(s + c == e || text[s + c] == ' ')) fail = true;
-    else labels[line] = __uint_as_float(bits);
-  }
-  fail = __any_sync(kFull, fail);
-
-  int32_t ord_base = 0;
-  for (int64_t pos = s & ~(int64_t)15; pos < e && !fail; pos += kChunk) {
-    const int64_t p = pos + lane * 16;
-    uint32_t sp = 0, nul = 0;
-    if (p < e) {
-      const uint4 v = load16(text + p);
-      const int64_t lo = s > p ? s - p : 0, hi = e - p < 16 ? e - p : 16;
-      const uint32_t valid = lo < 16 ? ((0xffffu >> (16 - hi)) & (0xffffu << lo)) & 0xffffu : 0;
-      sp = eq_mask(v, ' ') & valid;
-      nul = eq_mask(v, 0) & valid;
-    }
-    // compact the token starts (byte after each space) of this chunk
-    const int c = __popc(sp);
-    int incl = c;
+  uint8_t* tok = s_tok[warp][g];
+  bool bad = out_base + cnt > capacity || e <= s;
+  int32_t ord_base = -1;  // token -1 is the label
+  for (int64_t pos = s & ~(int64_t)15; pos < e && !bad; pos += kChunk) {
+    const int64_t p = pos + c * 16;
+    uint32_t w[4] = {0, 0, 0, 0};
+    if (p < e) { const uint4 v = load16(text + p); w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w; }
+    const int lo = s > p ? (int)(s - p) : 0;
+    const int hi = e - p >= 16 ? 16 : (e - p > 0 ? (int)(e - p) : 0);
+    uint32_t sp[4];
+    int n_here = 0;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(kFull, incl, o);
-      if (lane >= o) incl += t;
+    for (int k = 0; k < 4; ++k) {
+      const uint32_t v = flag_valid(k, lo, hi);
+      sp[k] = flag_eq(w[k], ' ') & v;
+      bad |= (flag_eq(w[k], 0) & v) != 0;  // a NUL ends the line early: sequential path
+      n_here += __popc(sp[k]);
     }
-    const int tot = __shfl_sync(kFull, incl, 31);
-    int w = incl - c;
-    for (uint32_t m = sp; m; m &= m - 1) s_tok[warp][w++] = (uint16_t)(lane * 16 + __ffs(m));
-    __syncwarp();
-    bool bad = nul != 0;
-    for (int t = lane; t < tot; t += 32) {
-      int64_t q = pos + s_tok[warp][t];
+    const bool first = pos <= s;                  // the chunk that holds the line start also lists the label
+    if (first && c == 0) n_here += 1;
+    int incl = n_here;
+#pragma unroll
+    for (int o = 1; o < kLPL; o <<= 1) {
+      const int t = __shfl_up_sync(gm, incl, o, kLPL);
+      if (c >= o) incl += t;
+    }
+    const int tot = __shfl_sync(gm, incl, kLPL - 1, kLPL);
+    int wpos = incl - n_here;
+    if (first && c == 0) tok[wpos++] = (uint8_t)(s - pos);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      for (uint32_t f = sp[k]; f; f &= f - 1) tok[wpos++] = (uint8_t)(c * 16 + 4 * k + (__ffs(f) >> 3));
+    __syncwarp(gm);
+    for (int t = c; t < tot; t += kLPL) {
+      // tok[] holds 0..128; 128 (the byte after a space that ends the chunk) does not fit a signed char but fits u8
+      int64_t q = pos + tok[t];
       const int32_t ordinal = ord_base + t;
+      uint32_t bits = 0x3f800000u;  // 1.0f
+      if (ordinal < 0) {            // label: everything up to the first space
+        const int used = scan_value_fast(text + q, (int)min((int64_t)64, e - q), &bits);
+        q += used;
+        if (used == 0 || !(q == e || text[q] == ' ')) { bad = true; continue; }
+        labels[line] = __uint_as_float(bits);
+        continue;
+      }
       if (q >= e) { bad |= ordinal != cnt; continue; }  // trailing space: breaks without counting (:79-81)
       if (ordinal >= cnt) { bad = true; continue; }
       int64_t id = 0;
@@ -271,34 +331,44 @@ parse_fill_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ 
         if (nd == 0 || (q < e && fmnp::is_digit(text[q])) || (int64_t)acc >= vocab) { bad = true; continue; }
         id = (int64_t)acc;
       }
-      uint32_t bits = 0x3f800000u;  // 1.0f
       if (q < e && text[q] == ':') {
         ++q;
-        const int64_t c2 = scan_value(text + q, e - q, &bits);
-        if (c2 == 0) { bad = true; continue; }
-        q += c2;
+        const int used = scan_value_fast(text + q, (int)min((int64_t)64, e - q), &bits);
+        if (used == 0) { bad = true; continue; }
+        q += used;
       }
       if (!(q == e || text[q] == ' ')) { bad = true; continue; }
       ids[out_base + ordinal] = id;
       vals[out_base + ordinal] = __uint_as_float(bits);
     }
     ord_base += tot;
-    fail = __any_sync(kFull, bad);
-    __syncwarp();
+    bad = __any_sync(gm, bad);
+    __syncwarp(gm);
   }
+  bad = __any_sync(gm, bad);
   // a line that ended short of its count (cannot happen for a regular line)
-  if (!fail && ord_base != cnt && ord_base != cnt + 1) fail = true;
+  if (!bad && ord_base != cnt && ord_base != cnt + 1) bad = true;
+  if (bad && c == 0) slow_list[atomicAdd(slow_count, 1)] = (int32_t)line;
+}
 
-  if (fail && lane == 0) {
-    if (over_capacity) {
-      report_error(st, line, FM_PARSE_E_CAPACITY);
-    } else {
-      int32_t got = 0;
-      const int rc = parse_line_seq(text + s, e - s, hash, vocab, labels + line, ids + out_base,
-                                    vals + out_base, cnt, &got);
-      if (rc != FM_PARSE_OK) report_error(st, line, rc);
-      else if (got != cnt) report_error(st, line, FM_PARSE_E_FORMAT);
-    }
+// the lines the fast path gave up on: sequential ParseLine with outputs and error reporting
+__global__ void __launch_bounds__(kSlowThreads)
+parse_fill_slow_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ off, int64_t vocab, int hash,
+                       const int32_t* __restrict__ poses, float* __restrict__ labels, int64_t* __restrict__ ids,
+                       float* __restrict__ vals, int64_t capacity, const int32_t* __restrict__ slow_list,
+                       const int* __restrict__ slow_count, fm_parse_status* st) {
+  const int n = *slow_count;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+    const int64_t line = slow_list[t];
+    const int64_t s = off[line], e = off[line + 1] - 1;
+    const int64_t out_base = poses[line];
+    const int32_t cnt = poses[line + 1] - poses[line];
+    if (out_base + cnt > capacity) { report_error(st, line, FM_PARSE_E_CAPACITY); continue; }
+    int32_t got = 0;
+    const int rc = parse_line_seq(text + s, e - s, hash, vocab, labels + line, ids + out_base, vals + out_base, cnt,
+                                  &got);
+    if (rc != FM_PARSE_OK) report_error(st, line, rc);
+    else if (got != cnt) report_error(st, line, FM_PARSE_E_FORMAT);
   }
 }
 
@@ -306,21 +376,33 @@ parse_fill_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ 
 struct NewlineIn {
   const uint8_t* text; int64_t nbytes;
   __device__ int64_t count() const { return (nbytes + 15) / 16; }
-  __device__ uint32_t mask(int64_t g) const {
+  __device__ void flags(int64_t g, uint32_t (&f)[4]) const {
     const uint4 v = load16(text + g * 16);
     const int64_t left = nbytes - g * 16;
-    return eq_mask(v, '\n') & (left >= 16 ? 0xffffu : (0xffffu >> (16 - left)));
+    const int hi = left >= 16 ? 16 : (int)left;
+    f[0] = flag_eq(v.x, '\n') & flag_valid(0, 0, hi);
+    f[1] = flag_eq(v.y, '\n') & flag_valid(1, 0, hi);
+    f[2] = flag_eq(v.z, '\n') & flag_valid(2, 0, hi);
+    f[3] = flag_eq(v.w, '\n') & flag_valid(3, 0, hi);
   }
-  __device__ long long operator()(int64_t g) const { return __popc(mask(g)); }
+  __device__ long long operator()(int64_t g) const {
+    uint32_t f[4];
+    flags(g, f);
+    return __popc(f[0]) + __popc(f[1]) + __popc(f[2]) + __popc(f[3]);
+  }
 };
 struct LineStartsOut {
   NewlineIn in; int64_t* offsets; int64_t max_lines; fm_parse_status* st;
   __device__ void operator()(int64_t g, long long excl, long long cnt) const {
     if (g == 0) offsets[0] = 0;
     if (cnt == 0) return;
+    uint32_t f[4];
+    in.flags(g, f);
     long long r = excl;
-    for (uint32_t m = in.mask(g); m; m &= m - 1, ++r)
-      if (r + 1 <= max_lines) offsets[r + 1] = g * 16 + __ffs(m);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      for (uint32_t m = f[k]; m; m &= m - 1, ++r)
+        if (r + 1 <= max_lines) offsets[r + 1] = g * 16 + 4 * k + (__ffs(m) >> 3);
   }
   __device__ void total(long long t) const {
     st->n_lines = t;
@@ -358,7 +440,7 @@ FM_EXPORT int fm_split_lines(const uint8_t* text, int64_t text_bytes, int64_t* l
   return FM_OK;
 }
 
-FM_EXPORT size_t fm_parse_workspace(int64_t n_lines) { return scan_scratch_bytes(n_lines, 4); }
+FM_EXPORT size_t fm_parse_workspace(int64_t n_lines) { return parse_ws(nullptr, n_lines < 0 ? 0 : n_lines).total; }
 
 FM_EXPORT int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, int64_t n_lines,
                              int64_t vocab_size, int hash_feature_id, int32_t* sizes,
@@ -366,23 +448,28 @@ FM_EXPORT int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, i
                              size_t workspace_bytes, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   FM_REQUIRE(n_lines >= 0 && vocab_size > 0, "fm_parse_count: n_lines must be >= 0 and vocab_size > 0");
+  if (n_lines >= (1ll << 31)) return fm_fail(FM_E_LIMIT, "fm_parse_count: n_lines >= 2^31");
   FM_REQUIRE(feature_poses && status && workspace, "fm_parse_count: null pointer");
   FM_REQUIRE(n_lines == 0 || (text && line_offsets && sizes), "fm_parse_count: null pointer");
   FM_REQUIRE(((uintptr_t)text & 15) == 0, "fm_parse_count: text must be 16-byte aligned");
-  if (workspace_bytes < scan_scratch_bytes(n_lines, 4))
-    return fm_fail(FM_E_WORKSPACE, "fm_parse_count: workspace %zu < %zu", workspace_bytes, scan_scratch_bytes(n_lines, 4));
-  FM_CUDA(cudaMemsetAsync(workspace, 0, scan_scratch_bytes(n_lines, 4), stream));
+  const ParseWs ws = parse_ws(workspace, n_lines);
+  if (workspace_bytes < ws.total)
+    return fm_fail(FM_E_WORKSPACE, "fm_parse_count: workspace %zu < %zu", workspace_bytes, ws.total);
+  FM_CUDA(cudaMemsetAsync(workspace, 0, ws.zero_bytes, stream));
   FM_CUDA(cudaMemsetAsync(&status->first_error, 0xff, sizeof(uint64_t), stream));
   if (n_lines > 0) {
-    const unsigned blocks = (unsigned)((n_lines + kWarpsPerBlock - 1) / kWarpsPerBlock);
-    parse_count_kernel<<<blocks, kWarpsPerBlock * 32, 0, stream>>>(text, line_offsets, n_lines, vocab_size,
-                                                                   hash_feature_id, sizes, status);
+    const unsigned blocks = (unsigned)((n_lines + kLinesPerBlock - 1) / kLinesPerBlock);
+    parse_count_kernel<<<blocks, kWarpsPerBlock * 32, 0, stream>>>(text, line_offsets, n_lines, sizes, ws.slow_a,
+                                                                   ws.slow_count);
+    FM_LAUNCH_CHECK();
+    parse_count_slow_kernel<<<kSlowBlocks, kSlowThreads, 0, stream>>>(text, line_offsets, vocab_size, hash_feature_id,
+                                                                      sizes, ws.slow_a, ws.slow_count, status);
     FM_LAUNCH_CHECK();
   }
   SizesIn in{sizes, n_lines};
   PosesOut out{feature_poses, n_lines, status};
   const int64_t tiles = scan_tiles(n_lines, 4);
-  scan_kernel<4><<<(unsigned)tiles, kScanThreads, 0, stream>>>(in, out, scan_scratch_at(workspace, n_lines, 4), tiles);
+  scan_kernel<4><<<(unsigned)tiles, kScanThreads, 0, stream>>>(in, out, scan_scratch_at(ws.scan, n_lines, 4), tiles);
   FM_LAUNCH_CHECK();
   return FM_OK;
 }
@@ -390,17 +477,24 @@ FM_EXPORT int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, i
 FM_EXPORT int fm_parse_fill(const uint8_t* text, const int64_t* line_offsets, int64_t n_lines,
                             int64_t vocab_size, int hash_feature_id, const int32_t* feature_poses,
                             float* labels, int64_t* feature_ids, float* feature_vals, int64_t capacity,
-                            fm_parse_status* status, void* stream_) {
+                            fm_parse_status* status, void* workspace, size_t workspace_bytes, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   FM_REQUIRE(n_lines >= 0 && vocab_size > 0 && capacity >= 0, "fm_parse_fill: bad size");
   if (n_lines == 0) return FM_OK;
-  FM_REQUIRE(text && line_offsets && feature_poses && labels && status, "fm_parse_fill: null pointer");
+  FM_REQUIRE(text && line_offsets && feature_poses && labels && status && workspace, "fm_parse_fill: null pointer");
   FM_REQUIRE(capacity == 0 || (feature_ids && feature_vals), "fm_parse_fill: null output");
   FM_REQUIRE(((uintptr_t)text & 15) == 0, "fm_parse_fill: text must be 16-byte aligned");
-  const unsigned blocks = (unsigned)((n_lines + kWarpsPerBlock - 1) / kWarpsPerBlock);
+  const ParseWs ws = parse_ws(workspace, n_lines);
+  if (workspace_bytes < ws.total)
+    return fm_fail(FM_E_WORKSPACE, "fm_parse_fill: workspace %zu < %zu", workspace_bytes, ws.total);
+  const unsigned blocks = (unsigned)((n_lines + kLinesPerBlock - 1) / kLinesPerBlock);
   parse_fill_kernel<<<blocks, kWarpsPerBlock * 32, 0, stream>>>(text, line_offsets, n_lines, vocab_size,
-                                                                hash_feature_id, feature_poses, labels,
-                                                                feature_ids, feature_vals, capacity, status);
+                                                                hash_feature_id, feature_poses, labels, feature_ids,
+                                                                feature_vals, capacity, ws.slow_b, ws.slow_count + 1);
+  FM_LAUNCH_CHECK();
+  parse_fill_slow_kernel<<<kSlowBlocks, kSlowThreads, 0, stream>>>(text, line_offsets, vocab_size, hash_feature_id,
+                                                                   feature_poses, labels, feature_ids, feature_vals,
+                                                                   capacity, ws.slow_b, ws.slow_count + 1, status);
   FM_LAUNCH_CHECK();
   return FM_OK;
 }

@@ -215,7 +215,7 @@ class Model(object):
         mark("parse_count")
         check(lib.fm_parse_fill(ptr(packed.text), ptr(packed.offsets), n_lines, self.vocabulary_size, hashed,
                                 ptr(b["poses"]), ptr(b["labels"]), ptr(b["ids"]), ptr(b["vals"]), b["cap"], status,
-                                st), "fm_parse_fill")
+                                ptr(b["ws_parse"]), b["ws_parse"].numel(), st), "fm_parse_fill")
         mark("parse_fill")
         check(lib.fm_unique(ptr(b["ids"]), b["cap"], nnz_dev, ptr(b["ori"]), ptr(b["local"]), nuniq_dev,
                             ptr(b["ws_unique"]), b["ws_unique"].numel(), st), "fm_unique")

@@ -56,7 +56,8 @@ class CudaShardKernels:
         ids = torch.empty(nnz, dtype=i64, device=dev)
         vals = torch.empty(nnz, dtype=f32, device=dev)
         check(lib.fm_parse_fill(ptr(packed.text), ptr(packed.offsets), n_lines, vocab, int(hashed), ptr(poses),
-                                ptr(labels), ptr(ids), ptr(vals), nnz, ptr(status), stream()), "fm_parse_fill")
+                                ptr(labels), ptr(ids), ptr(vals), nnz, ptr(status), ptr(ws), ws.numel(), stream()),
+              "fm_parse_fill")
         ori, local = self.unique(ids)
         first = int(status[0].item()) & 0xFFFFFFFFFFFFFFFF
         if first != _lib.NO_ERROR:

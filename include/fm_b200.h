@@ -87,7 +87,7 @@ int fm_split_lines(const uint8_t* text, int64_t text_bytes, int64_t* line_offset
  * feature_poses = [0, cumsum(sizes)] (this is tf.cumsum at
  * tffm/fm_model.py:73 fused into the parser) and status->nnz.
  * Resets status->first_error first.  Lines the fast counter cannot prove regular are
- * parsed in full by the sequential scanner. */
+ * counted by a sequential kernel that follows ParseLine statement by statement. */
 size_t fm_parse_workspace(int64_t n_lines);
 int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, int64_t n_lines,
                    int64_t vocab_size, int hash_feature_id, int32_t* sizes,
@@ -95,11 +95,13 @@ int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, int64_t n_l
                    void* workspace, size_t workspace_bytes, void* stream);
 
 /* Pass 2: labels[n_lines], feature_ids[nnz] (int64, as the op's output),
- * feature_vals[nnz]; `capacity` = elements available in feature_ids/vals. */
+ * feature_vals[nnz]; `capacity` = elements available in feature_ids/vals.
+ * `workspace` is the one given to fm_parse_count for this batch (its contents are
+ * still needed: the two passes share their bookkeeping). */
 int fm_parse_fill(const uint8_t* text, const int64_t* line_offsets, int64_t n_lines,
                   int64_t vocab_size, int hash_feature_id, const int32_t* feature_poses,
                   float* labels, int64_t* feature_ids, float* feature_vals, int64_t capacity,
-                  fm_parse_status* status, void* stream);
+                  fm_parse_status* status, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- U1: tf.unique, tffm/fm_model.py:72 ----
  * ori_ids[U] = distinct ids in order of first occurrence; local_ids[n] = index
