@@ -30,12 +30,14 @@ CFG = dict(vocab=1 << 24, factor_num=16, batch=65536, nnz_per_line=39, hash_feat
            loss_type="logistic", learning_rate=0.01, init_acc=0.1, factor_lambda=1e-5, bias_lambda=1e-5)
 METRIC, UNIT = "fm_train_examples_per_sec", "examples/s"
 STAGES = {  # stage marks per step, in order
-    True: ["parse_count", "parse_fill", "unique", "score_scatter", "adagrad"],
-    False: ["parse_count", "parse_fill", "unique", "lookup", "score", "loss", "grad", "adagrad"],
+    "claim": ["parse_count", "parse_fill", "score_scatter", "adagrad"],
+    "fused": ["parse_count", "parse_fill", "unique", "score_scatter", "adagrad"],
+    "composed": ["parse_count", "parse_fill", "unique", "lookup", "score", "loss", "grad", "adagrad"],
 }
-# my kernels per step.  fused: count, poses scan, fill | insert, rank scan, finish | score_scatter, reduce2 |
-# fused adagrad.  composed: ... | lookup | score, reduce | loss, reduce | zero rows, grad | adagrad
-KERNELS_PER_STEP = {True: 9, False: 14}
+# my kernels per step.  parse: count, count-slow, poses scan, fill, fill-slow (5); unique: insert, rank
+# scan, finish (3); claim: + score_scatter, reduce2, adagrad_claim; fused: + unique + score_scatter,
+# reduce2, adagrad; composed: + unique + lookup | score, reduce | loss, reduce | zero rows, grad | adagrad
+KERNELS_PER_STEP = {"claim": 8, "fused": 11, "composed": 16}
 
 
 def measured_peak_gbs():
@@ -53,7 +55,13 @@ def algorithmic_bytes(n, u, b, k, text_bytes, fused):
     read + one clearing write in the update)."""
     rb = 4 * (k + 1)
     ab = 4 * (k + 3)
-    if fused:
+    if fused == "claim":   # no unique; the update walks the N occurrences' ids
+        return {
+            "parse": text_bytes + 12 * n + 8 * b,
+            "score_scatter": 12 * n + 4 * (b + 1) + 8 * b + u * rb + 2 * u * ab,
+            "adagrad": 8 * n + 2 * u * ab + 4 * u * rb,
+        }
+    if fused == "fused":
         return {
             "parse": text_bytes + 12 * n + 8 * b,
             "unique": 12 * n + 8 * u + 4 * (b + 1),
@@ -192,7 +200,8 @@ def run_ours(args):
     m = Model(vocabulary_size=CFG["vocab"], factor_num=k, batch_size=b, hash_feature_id=True,
               loss_type=CFG["loss_type"], learning_rate=CFG["learning_rate"],
               adagrad_init_accumulator=CFG["init_acc"], factor_lambda=CFG["factor_lambda"],
-              bias_lambda=CFG["bias_lambda"]).build(dev, seed=0, max_nnz_per_line=CFG["nnz_per_line"], ld=args.ld)
+              bias_lambda=CFG["bias_lambda"]).build(dev, seed=0, max_nnz_per_line=CFG["nnz_per_line"], ld=args.ld,
+                                                     layout=args.layout)
     if args.l2_fetch:
         # experiment knob: cudaLimitMaxL2FetchGranularity (0x05)
         import ctypes
@@ -212,10 +221,10 @@ def run_ours(args):
     text_bytes = int(host[0].offsets[-1])
 
     # ---- device-resident throughput (value) + per-stage CUDA events ----------------
-    fused = not args.composed
+    fused = args.path
     stages = STAGES[fused]
     for i in range(args.warmup):
-        m.train_step_async(devb[i % len(devb)], fused=fused)
+        m.train_step_async(devb[i % len(devb)], path=fused)
     torch.cuda.synchronize()
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(stages) + 1)] for _ in range(args.steps)]
     sampler = ClockSampler(local_rank)
@@ -228,7 +237,7 @@ def run_ours(args):
         def mark(name, evs=ev[s], cursor=cursor):
             cursor[0] += 1
             evs[cursor[0]].record()
-        bufs = m.train_step_async(devb[s % len(devb)], mark=mark, fused=fused)
+        bufs = m.train_step_async(devb[s % len(devb)], mark=mark, path=fused)
     torch.cuda.synchronize()
     clocks = sampler.stop()
     total_ms = ev[0][0].elapsed_time(ev[-1][-1])
@@ -236,7 +245,8 @@ def run_ours(args):
                 for i, n in enumerate(stages)}
     st = bufs["status"].cpu()
     assert int(st[0]) == -1, "parse error in the benchmark data"
-    nnz, n_unique = int(st[1]), int(st[4])
+    nnz = int(st[1])
+    n_unique = int(st[4]) if fused != "claim" else int(torch.unique(bufs["ids"][:nnz]).numel())
     loss = float(st[6:8].view(torch.float32)[0])
     value = args.steps * b / (total_ms * 1e-3)
 
@@ -278,7 +288,7 @@ def run_ours(args):
                 stage_in[slot].offsets.copy_(hb.offsets, non_blocking=True)
                 ready[slot].record(copy_stream)
             main.wait_event(ready[slot])
-            bb = m.train_step_async(stage_in[slot], fused=fused)
+            bb = m.train_step_async(stage_in[slot], path=fused)
             consumed[slot].record(main)
             pinned_status[base + s].copy_(bb["status"], non_blocking=True)   # loss + status back to the host
 
@@ -304,9 +314,9 @@ def run_ours(args):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": KERNELS_PER_STEP[fused] * args.steps,
-        "path": "fused" if fused else "composed (op by op)",
+        "path": fused, "layout": args.layout, "unique_per_step": n_unique,
         "clocks": clocks,
-        "final_loss": loss, "nnz_per_step": nnz, "unique_per_step": n_unique,
+        "final_loss": loss, "nnz_per_step": nnz,
     }
     print(json.dumps(line))
 
@@ -320,7 +330,10 @@ def main():
     ap.add_argument("--dist", default="uniform", choices=["uniform", "zipf"])
     ap.add_argument("--batches", type=int, default=8, help="distinct synthetic batches cycled through")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--composed", action="store_true", help="time the op-by-op chain instead of the fused path")
+    ap.add_argument("--path", default="claim", choices=["claim", "fused", "composed"],
+                    help="claim: no unique, table-shaped accumulators (default); fused: unique + compact "
+                         "accumulators; composed: the reference's op-by-op chain")
+    ap.add_argument("--layout", default="split", choices=["split", "interleaved"])
     ap.add_argument("--ld", type=int, default=None, help="experiment: table row stride in floats")
     ap.add_argument("--l2-fetch", type=int, default=0, help="experiment: cudaLimitMaxL2FetchGranularity")
     args = ap.parse_args()

@@ -68,7 +68,7 @@ def run_sharded(args, cfg, workload_config):
     if rank == 0:
         nnz, nuniq, sent = (float(x) / world for x in stats.tolist())
         text_bytes = int(host[0].offsets[-1])
-        alg = algorithmic_bytes(nnz, nuniq, b, k, text_bytes, True)
+        alg = algorithmic_bytes(nnz, nuniq, b, k, text_bytes, "fused")
         peak, peak_kind = measured_peak_gbs()
         step_s = total_ms / args.steps * 1e-3
         gld = (k + 3 + 3) // 4 * 4

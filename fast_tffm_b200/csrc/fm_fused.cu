@@ -23,8 +23,10 @@
 //       acc += G^2 ; w -= lr G / sqrt(acc)  (TF1 SparseApplyAdagrad) and clears
 //       the accumulator row for the next step.
 //
-// Rows are handled as float4 chunks: table row stride (floats) must be a multiple
-// of 4 with the pad columns zero, pointers 16-byte aligned.
+// Rows are handled as float4 chunks: row strides (floats) are multiples of 4,
+// pointers 16-byte aligned, and the columns K+1 .. 4*ceil((K+1)/4)-1 of a table row
+// are zero.  Strides may be larger than the rows (e.g. weight, Adagrad and gradient
+// accumulator rows of one id interleaved in one allocation).
 #include "fm_common.cuh"
 
 namespace fm {
@@ -65,7 +67,7 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
   __shared__ float s_loss[kWarps], s_reg[kWarps];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int r = lane / LPR, c = lane % LPR;
-  const int vc_table = (int)(ld >> 2), vc_acc = (int)(gacc_ld >> 2);
+  const int vc_table = (K + 4) >> 2, vc_acc = (K + 6) >> 2;  // float4 chunks of a K+1 / K+3 wide row
   const bool active = !(guard && *guard != kNoError);
   float loss_acc = 0.f, reg_acc = 0.f;
 
@@ -122,6 +124,10 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
     const float p = warp_sum(bias_dot + 0.5f * (second - q));
     reg_acc += warp_sum(0.5f * lam_f * fac_sq + 0.5f * lam_b * bias_sq);
 
+    if (labels == nullptr) {  // scoring only: no loss, no scatter
+      if (lane == 0) pred[i] = p;
+      continue;
+    }
     // ---- loss term and d loss / d pred (tffm/fm_model.py:311-326) ------------------
     const float y = labels[i], w = weights ? weights[i] : 1.0f;
     float l, d;
@@ -141,18 +147,18 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
     // ---- pass B: scatter {C, B_k, D, cnt} to the accumulator rows ---------------------
     for (int base = start; base < end; base += 32) {
       const int j = base + lane;
-      const int my_u = j < end ? local[j] : 0;
+      const int64_t my_u = j < end ? (local ? (int64_t)local[j] : ids[j]) : 0;
       const float my_x = j < end ? vals[j] : 0.f;
       const int rows_here = min(32, end - base);
 #pragma unroll
       for (int s = 0; s < LPR; ++s) {
         const int jj = s * RPW + r;
         if (s * RPW >= rows_here) break;
-        const int u = __shfl_sync(kFull, my_u, jj);
+        const int64_t u = __shfl_sync(kFull, my_u, jj);
         const float x = __shfl_sync(kFull, my_x, jj);
         if (jj < rows_here) {
           const float pgx = pg * x;
-          float* arow = gacc + (int64_t)u * gacc_ld;
+          float* arow = gacc + u * gacc_ld;
 #pragma unroll
           for (int t = 0; t < T; ++t) {
             const int chunk = c + t * LPR;
@@ -214,7 +220,7 @@ fused_adagrad_kernel(float* __restrict__ table, float* __restrict__ accum, int64
   const int64_t n = n_dev ? min(*n_dev, n_max) : n_max;
   const int c = threadIdx.x % LPR;
   const int64_t groups_per_block = blockDim.x / LPR;
-  const int vc_table = (int)(ld >> 2), vc_acc = (int)(gacc_ld >> 2);
+  const int vc_table = (K + 4) >> 2, vc_acc = (K + 6) >> 2;  // float4 chunks of a K+1 / K+3 wide row
   const int64_t n_round = (n + groups_per_block - 1) / groups_per_block * groups_per_block;  // keep warps converged
   for (int64_t u = (int64_t)blockIdx.x * groups_per_block + threadIdx.x / LPR; u < n_round;
        u += (int64_t)gridDim.x * groups_per_block) {
@@ -263,6 +269,92 @@ fused_adagrad_kernel(float* __restrict__ table, float* __restrict__ accum, int64
       }
       if (live && chunk < vc_acc)
         *reinterpret_cast<float4*>(gacc + u * gacc_ld + 4 * chunk) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+}
+
+// Adagrad over accumulator rows that live beside the table rows (gtab[row] belongs to
+// table[row]): one lane group per OCCURRENCE.  The first group to swap the row's cnt
+// column to zero owns the row and applies the update; later occurrences of the same
+// row see cnt == 0 and leave.  No de-duplication pass is needed.
+template <int LPR, int T>
+__global__ void __launch_bounds__(256)
+fused_adagrad_claim_kernel(float* __restrict__ table, float* __restrict__ accum, int64_t ld,
+                           const int64_t* __restrict__ rows, int64_t n_max, const int64_t* __restrict__ n_dev, int K,
+                           float* __restrict__ gtab, int64_t gtab_ld, float lr, float rf, float rb,
+                           const unsigned long long* __restrict__ guard) {
+  if (guard && *guard != kNoError) return;
+  const int64_t n = n_dev ? min(*n_dev, n_max) : n_max;
+  const int c = threadIdx.x % LPR;
+  const int64_t groups_per_block = blockDim.x / LPR;
+  const int vc_table = (K + 4) >> 2, vc_acc = (K + 6) >> 2;
+  const int cnt_chunk = (K + 2) >> 2, cnt_comp = (K + 2) & 3;
+  const int64_t n_round = (n + groups_per_block - 1) / groups_per_block * groups_per_block;
+  for (int64_t j = (int64_t)blockIdx.x * groups_per_block + threadIdx.x / LPR; j < n_round;
+       j += (int64_t)gridDim.x * groups_per_block) {
+    const bool live = j < n;
+    const int64_t id = live ? rows[j] : 0;
+    const int64_t row = id * ld, grow = id * gtab_ld;
+    float4 a[T], w[T], h[T];
+    float cnt = 0.f;
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+      const int chunk = c + t * LPR;
+      a[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+      w[t] = a[t]; h[t] = a[t];
+      if (live && chunk < vc_acc) a[t] = *reinterpret_cast<const float4*>(gtab + grow + 4 * chunk);
+      if (live && chunk < vc_table) {
+        w[t] = *reinterpret_cast<const float4*>(table + row + 4 * chunk);
+        h[t] = *reinterpret_cast<const float4*>(accum + row + 4 * chunk);
+      }
+    }
+    // The claim.  It waits for the row's own load (so the atomic hits a line that is already in
+    // L2 -- an atomic that misses L2 costs a DRAM round trip inside the atomic unit) and is
+    // skipped when the row was visibly consumed already.
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+      if (c + t * LPR == cnt_chunk) {
+        const float av[4] = {a[t].x, a[t].y, a[t].z, a[t].w};
+        float seen = 0.f;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) if (e == cnt_comp) seen = av[e];
+        if (live && seen != 0.f) cnt = atomicExch(gtab + grow + 4 * cnt_chunk + cnt_comp, 0.f);
+      }
+    }
+    cnt = sum_in_group<LPR>(cnt);
+    float D = 0.f;
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+      const int chunk = c + t * LPR;
+      const float av[4] = {a[t].x, a[t].y, a[t].z, a[t].w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if (4 * chunk + e == K + 1) D += av[e];
+    }
+    D = sum_in_group<LPR>(D);
+    if (!(live && cnt != 0.f)) continue;  // another occurrence of this row got there first
+    const float fac_scale = cnt * rf - D, bias_scale = cnt * rb;
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+      const int chunk = c + t * LPR;
+      if (chunk < vc_table) {
+        const float av[4] = {a[t].x, a[t].y, a[t].z, a[t].w};
+        float wv[4] = {w[t].x, w[t].y, w[t].z, w[t].w};
+        float hv[4] = {h[t].x, h[t].y, h[t].z, h[t].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int col = 4 * chunk + e;
+          float g = 0.f;
+          if (col == 0) g = fmaf(bias_scale, wv[e], av[e]);
+          else if (col <= K) g = fmaf(wv[e], fac_scale, av[e]);
+          hv[e] = fmaf(g, g, hv[e]);
+          wv[e] -= __fdiv_rn(lr * g, __fsqrt_rn(hv[e]));
+        }
+        *reinterpret_cast<float4*>(table + row + 4 * chunk) = make_float4(wv[0], wv[1], wv[2], wv[3]);
+        *reinterpret_cast<float4*>(accum + row + 4 * chunk) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+      }
+      if (chunk < vc_acc && 4 * chunk <= K + 2)
+        *reinterpret_cast<float4*>(gtab + grow + 4 * chunk) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
   }
 }
@@ -320,13 +412,15 @@ FM_EXPORT int fm_fused_score_scatter(const int64_t* feature_ids, const int32_t* 
   FM_REQUIRE(gacc_ld >= factor_num + 3 && gacc_ld % 4 == 0, "fm_fused_score_scatter: gacc_ld must be a multiple of 4 and >= K+3");
   FM_REQUIRE(loss_kind == FM_LOSS_LOGISTIC || loss_kind == FM_LOSS_MSE, "fm_fused_score_scatter: unknown loss kind");
   FM_REQUIRE(loss && reg_score && workspace, "fm_fused_score_scatter: null pointer");
-  FM_REQUIRE(batch == 0 || (feature_ids && local_ids && feature_vals && feature_poses && labels && table && pred_score && gacc),
+  FM_REQUIRE(batch == 0 || (feature_ids && feature_vals && feature_poses && table && pred_score),
              "fm_fused_score_scatter: null pointer");
+  FM_REQUIRE(batch == 0 || (labels == nullptr) == (gacc == nullptr),
+             "fm_fused_score_scatter: labels and gacc go together (both NULL = scoring only)");
   FM_REQUIRE((((uintptr_t)table | (uintptr_t)gacc) & 15) == 0, "fm_fused_score_scatter: table and gacc must be 16-byte aligned");
   if (workspace_bytes < fm_fused_workspace(batch))
     return fm_fail(FM_E_WORKSPACE, "fm_fused_score_scatter: workspace %zu < %zu", workspace_bytes, fm_fused_workspace(batch));
   Shape sh;
-  if (!pick_shape(gacc_ld / 4 > table_ld / 4 ? gacc_ld / 4 : table_ld / 4, &sh))
+  if (!pick_shape((factor_num + 6) / 4, &sh))
     return fm_fail(FM_E_LIMIT, "fm_fused_score_scatter: factor_num %lld too large", (long long)factor_num);
   const int blocks = fused_blocks(batch);
   float* partials = reinterpret_cast<float*>(workspace);
@@ -357,7 +451,7 @@ FM_EXPORT int fm_fused_adagrad(float* table, float* accum, int64_t table_ld, con
   FM_REQUIRE(table && accum && ori_ids && gacc, "fm_fused_adagrad: null pointer");
   FM_REQUIRE((((uintptr_t)table | (uintptr_t)accum | (uintptr_t)gacc) & 15) == 0, "fm_fused_adagrad: 16-byte alignment required");
   Shape sh;
-  if (!pick_shape(gacc_ld / 4 > table_ld / 4 ? gacc_ld / 4 : table_ld / 4, &sh))
+  if (!pick_shape((factor_num + 6) / 4, &sh))
     return fm_fail(FM_E_LIMIT, "fm_fused_adagrad: factor_num %lld too large", (long long)factor_num);
   const int64_t groups_per_block = 256 / sh.lpr;
   int64_t blocks = (n_unique + groups_per_block - 1) / groups_per_block;
@@ -367,6 +461,33 @@ FM_EXPORT int fm_fused_adagrad(float* table, float* accum, int64_t table_ld, con
       table, accum, table_ld, ori_ids, n_unique, n_unique_dev, (int)factor_num, gacc, gacc_ld,           \
       learning_rate, reg_grad * factor_lambda, reg_grad * bias_lambda,                                   \
       reinterpret_cast<const unsigned long long*>(guard))
+  FM_DISPATCH_SHAPE(sh, CALL)
+#undef CALL
+  FM_LAUNCH_CHECK();
+  return FM_OK;
+}
+
+FM_EXPORT int fm_fused_adagrad_claim(float* table, float* accum, int64_t table_ld, const int64_t* rows, int64_t n,
+                                     const int64_t* n_dev, int64_t factor_num, float* gtab, int64_t gtab_ld,
+                                     float learning_rate, float factor_lambda, float bias_lambda, float reg_grad,
+                                     const uint64_t* guard, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  FM_REQUIRE(n >= 0 && factor_num >= 0, "fm_fused_adagrad_claim: bad shape");
+  FM_REQUIRE(table_ld >= factor_num + 1 && table_ld % 4 == 0, "fm_fused_adagrad_claim: table_ld must be a multiple of 4 and >= K+1");
+  FM_REQUIRE(gtab_ld >= factor_num + 3 && gtab_ld % 4 == 0, "fm_fused_adagrad_claim: gtab_ld must be a multiple of 4 and >= K+3");
+  if (n == 0) return FM_OK;
+  FM_REQUIRE(table && accum && rows && gtab, "fm_fused_adagrad_claim: null pointer");
+  FM_REQUIRE((((uintptr_t)table | (uintptr_t)accum | (uintptr_t)gtab) & 15) == 0, "fm_fused_adagrad_claim: 16-byte alignment required");
+  Shape sh;
+  if (!pick_shape((factor_num + 6) / 4, &sh))
+    return fm_fail(FM_E_LIMIT, "fm_fused_adagrad_claim: factor_num %lld too large", (long long)factor_num);
+  const int64_t groups_per_block = 256 / sh.lpr;
+  int64_t blocks = (n + groups_per_block - 1) / groups_per_block;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+#define CALL(LPR, T)                                                                                      \
+  fused_adagrad_claim_kernel<LPR, T><<<(unsigned)blocks, 256, 0, stream>>>(                               \
+      table, accum, table_ld, rows, n, n_dev, (int)factor_num, gtab, gtab_ld, learning_rate,              \
+      reg_grad * factor_lambda, reg_grad * bias_lambda, reinterpret_cast<const unsigned long long*>(guard))
   FM_DISPATCH_SHAPE(sh, CALL)
 #undef CALL
   FM_LAUNCH_CHECK();

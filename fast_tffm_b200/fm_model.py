@@ -29,9 +29,22 @@ def _no_mark(name):
     pass
 
 
+def _stride_for(width):
+    """row stride (floats) for rows of `width` floats: a multiple of 4 (16-byte aligned rows,
+    128-bit loads); rows of up to 128 bytes get a power-of-two stride so that no row straddles
+    a 128-byte line (ncu: an 80-byte row at an 80-byte stride costs ~190 B of DRAM per read,
+    at a 128-byte stride 128 B)."""
+    ld = (width + 3) // 4 * 4
+    if ld <= 32:
+        p = 4
+        while p < ld:
+            p *= 2
+        ld = p
+    return ld
+
+
 def _ld_for(factor_num):
-    """row stride of the table in floats: K+1 rounded up to 4 so rows are 16-byte aligned"""
-    return (factor_num + 1 + 3) // 4 * 4
+    return _stride_for(factor_num + 1)
 
 
 class Model(object):
@@ -140,21 +153,33 @@ class Model(object):
         self.predict_files = expand(pfiles) if pfiles is not None else []
 
     # ---- the vocabulary table ------------------------------------------------------
-    def build(self, device=None, init_table=None, seed=None, max_nnz_per_line=None, ld=None):
-        """Allocates table + Adagrad accumulator in HBM.  The table is ONE array
-        [vocabulary_size, ld] (row = feature id, ld = K+1 rounded up to 4 floats); the
-        reference's vocabulary_block_num blocks (fm_model.py:269-284) are a relabelling
-        applied when checkpoints are written (blocks_state / load_blocks_state).
+    def build(self, device=None, init_table=None, seed=None, max_nnz_per_line=None, ld=None, layout="split"):
+        """Allocates table + Adagrad accumulator (+ table-shaped gradient accumulator) in HBM.
+        The table is [vocabulary_size, ld] (row = feature id, see _stride_for); the reference's
+        vocabulary_block_num blocks (fm_model.py:269-284) are a relabelling applied when
+        checkpoints are written (blocks_state / load_blocks_state).
+        layout "split": three arrays; "interleaved": one array whose row holds the weight,
+        Adagrad and gradient-accumulator rows of one id side by side (the update kernel then
+        touches one contiguous piece of memory per id).
         init: uniform(-init_value_range, init_value_range) (:278-281) or `init_table`
         ([vocabulary_size, K+1], for parity runs)."""
-        load()
+        lib = load()
         if device is None:
             device = torch.device("cuda", torch.cuda.current_device())
         self.device = torch.device(device)
         k, v = self.factor_num, self.vocabulary_size
         self.ld = _ld_for(k) if ld is None else int(ld)
-        assert self.ld >= k + 1
-        self.table = torch.zeros(v, self.ld, dtype=torch.float32, device=self.device)
+        assert self.ld >= k + 1 and self.ld % 4 == 0
+        self.gld = _stride_for(int(lib.fm_fused_gacc_ld(k)))
+        self.layout = layout
+        if layout == "interleaved":
+            part = max(self.ld, self.gld)
+            self._store = torch.zeros(v, 3 * part, dtype=torch.float32, device=self.device)
+            self.table = self._store[:, :part]
+            self.gtab = self._store[:, 2 * part:]
+        else:
+            self.table = torch.zeros(v, self.ld, dtype=torch.float32, device=self.device)
+            self.gtab = None  # allocated on the first step that needs it
         if init_table is not None:
             self.table[:, :k + 1] = torch.as_tensor(init_table, dtype=torch.float32)[:, :k + 1].to(self.device)
         else:
@@ -162,10 +187,19 @@ class Model(object):
             if seed is not None:
                 gen.manual_seed(seed)
             self.table[:, :k + 1].uniform_(-self.init_value_range, self.init_value_range, generator=gen)
-        self.accum = torch.full_like(self.table, self.adagrad_init_accumulator)
+        if layout == "interleaved":
+            self.accum = self._store[:, part:2 * part]
+            self.accum.fill_(self.adagrad_init_accumulator)
+        else:
+            self.accum = torch.full_like(self.table, self.adagrad_init_accumulator)
         self._bufs = None
         self._max_nnz_per_line = max_nnz_per_line
         return self
+
+    def _gtab(self):
+        if self.gtab is None:
+            self.gtab = torch.zeros(self.vocabulary_size, self.gld, dtype=torch.float32, device=self.device)
+        return self.gtab
 
     def _buffers(self, n_lines, text_bytes):
         """per-batch device buffers, allocated once and grown on demand"""
@@ -185,10 +219,10 @@ class Model(object):
             labels=torch.empty(lines, dtype=f32, device=dev), sizes=torch.empty(lines, dtype=i32, device=dev),
             poses=torch.empty(lines + 1, dtype=i32, device=dev), ids=torch.empty(cap, dtype=i64, device=dev),
             vals=torch.empty(cap, dtype=f32, device=dev), ori=torch.empty(cap, dtype=i64, device=dev),
-            local=torch.empty(cap, dtype=i32, device=dev), rows=torch.empty(cap, self.ld, dtype=f32, device=dev),
+            local=torch.empty(cap, dtype=i32, device=dev), rows=None,
             grad=None, pred=torch.empty(lines, dtype=f32, device=dev),
             gacc_ld=int(lib.fm_fused_gacc_ld(self.factor_num)),
-            gacc=torch.zeros(cap, int(lib.fm_fused_gacc_ld(self.factor_num)), dtype=f32, device=dev),
+            gacc=None,
             ws_fused=_lib.workspace(lib.fm_fused_workspace(lines), dev),
             pred_grad=torch.empty(lines, dtype=f32, device=dev),
             # [first_error, nnz, n_lines, reserved] (fm_parse_status), n_unique, then loss and reg as f32 bits
@@ -202,8 +236,8 @@ class Model(object):
         self._bufs = b
         return b
 
-    def _parse_unique(self, packed, b, mark=_no_mark):
-        """parse -> unique (+ cumsum), all sizes device-resident.
+    def _parse_unique(self, packed, b, mark=_no_mark, unique=True):
+        """parse (-> unique) (+ cumsum), all sizes device-resident.
         mark(name) is called after each stage is enqueued (bench.py records CUDA events there)."""
         lib, st = load(), stream()
         n_lines = packed.n_lines
@@ -217,6 +251,8 @@ class Model(object):
                                 ptr(b["poses"]), ptr(b["labels"]), ptr(b["ids"]), ptr(b["vals"]), b["cap"], status,
                                 ptr(b["ws_parse"]), b["ws_parse"].numel(), st), "fm_parse_fill")
         mark("parse_fill")
+        if not unique:
+            return
         check(lib.fm_unique(ptr(b["ids"]), b["cap"], nnz_dev, ptr(b["ori"]), ptr(b["local"]), nuniq_dev,
                             ptr(b["ws_unique"]), b["ws_unique"].numel(), st), "fm_unique")
         mark("unique")
@@ -226,36 +262,64 @@ class Model(object):
         lib, st = load(), stream()
         n_lines, k = packed.n_lines, self.factor_num
         status, nuniq_dev = ptr(b["status"]), _off(b["status"], 4)
+        if b["rows"] is None:
+            b["rows"] = torch.empty(b["cap"], self.ld, dtype=torch.float32, device=self.device)
         self._parse_unique(packed, b, mark)
-        check(lib.fm_lookup(ptr(self.table), self.ld, ptr(b["ori"]), b["cap"], nuniq_dev, k, ptr(b["rows"]), self.ld,
-                            status, st), "fm_lookup")
+        check(lib.fm_lookup(ptr(self.table), self.table.stride(0), ptr(b["ori"]), b["cap"], nuniq_dev, k,
+                            ptr(b["rows"]), self.ld, status, st), "fm_lookup")
         mark("lookup")
         check(lib.fm_score(ptr(b["local"]), ptr(b["rows"]), self.ld, ptr(b["vals"]), ptr(b["poses"]), n_lines, k,
                            self.factor_lambda, self.bias_lambda, ptr(b["pred"]), _off(b["status"], 7),
                            ptr(b["ws_score"]), b["ws_score"].numel(), st), "fm_score")
         mark("score")
 
-    def train_step_async(self, packed: PackedLines, weights=None, mark=_no_mark, fused=True):
+    PATHS = ("claim", "fused", "composed")
+
+    def train_step_async(self, packed: PackedLines, weights=None, mark=_no_mark, path="claim"):
         """One training step on a device-resident batch; enqueues only.  Returns the
         buffers dict: status[0] parse status word, status[1] nnz, status[4] n_unique,
         scalars[0] loss, scalars[2] reg.
-        fused=True  (default) parse -> unique -> fm_fused_score_scatter -> fm_fused_adagrad:
-                    each table row is read once per step;
-        fused=False the reference's op-by-op chain (lookup, scorer, loss, grad, Adagrad)."""
+        path "claim"    (default) parse -> fm_fused_score_scatter into table-shaped accumulator
+                        rows -> fm_fused_adagrad_claim: no tf.unique, each table row read once;
+             "fused"    parse -> unique -> fm_fused_score_scatter (compact accumulators) ->
+                        fm_fused_adagrad;
+             "composed" the reference's op-by-op chain (unique, lookup, scorer, loss, grad, Adagrad)."""
+        if path not in self.PATHS:
+            raise ValueError("path must be one of %s" % (self.PATHS,))
         b = self._buffers(packed.n_lines, packed.text.numel())
         lib, st = load(), stream()
         n_lines, k = packed.n_lines, self.factor_num
-        if fused:
+        tstride = self.table.stride(0)
+        if path == "claim":
+            gtab = self._gtab()
+            self._parse_unique(packed, b, mark, unique=False)
+            check(lib.fm_fused_score_scatter(
+                ptr(b["ids"]), None, ptr(b["vals"]), ptr(b["poses"]), ptr(b["labels"]), ptr(weights),
+                n_lines, k, ptr(self.table), tstride, self.factor_lambda, self.bias_lambda,
+                _lib.LOSS_KIND[self.loss_type], 0, ptr(b["pred"]), _off(b["status"], 6), _off(b["status"], 7),
+                ptr(gtab), gtab.stride(0), ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st),
+                "fm_fused_score_scatter")
+            mark("score_scatter")
+            check(lib.fm_fused_adagrad_claim(
+                ptr(self.table), ptr(self.accum), tstride, ptr(b["ids"]), b["cap"], _off(b["status"], 1), k,
+                ptr(gtab), gtab.stride(0), self.learning_rate, self.factor_lambda, self.bias_lambda,
+                1.0 / self.batch_size, ptr(b["status"]), st), "fm_fused_adagrad_claim")
+            mark("adagrad")
+            self.global_step += 1
+            return b
+        if path == "fused":
+            if b["gacc"] is None:
+                b["gacc"] = torch.zeros(b["cap"], b["gacc_ld"], dtype=torch.float32, device=self.device)
             self._parse_unique(packed, b, mark)
             check(lib.fm_fused_score_scatter(
                 ptr(b["ids"]), ptr(b["local"]), ptr(b["vals"]), ptr(b["poses"]), ptr(b["labels"]), ptr(weights),
-                n_lines, k, ptr(self.table), self.ld, self.factor_lambda, self.bias_lambda,
+                n_lines, k, ptr(self.table), tstride, self.factor_lambda, self.bias_lambda,
                 _lib.LOSS_KIND[self.loss_type], 0, ptr(b["pred"]), _off(b["status"], 6), _off(b["status"], 7),
                 ptr(b["gacc"]), b["gacc_ld"], ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st),
                 "fm_fused_score_scatter")
             mark("score_scatter")
             check(lib.fm_fused_adagrad(
-                ptr(self.table), ptr(self.accum), self.ld, ptr(b["ori"]), b["cap"], _off(b["status"], 4), k,
+                ptr(self.table), ptr(self.accum), tstride, ptr(b["ori"]), b["cap"], _off(b["status"], 4), k,
                 ptr(b["gacc"]), b["gacc_ld"], self.learning_rate, self.factor_lambda, self.bias_lambda,
                 1.0 / self.batch_size, ptr(b["status"]), st), "fm_fused_adagrad")
             mark("adagrad")
@@ -274,31 +338,43 @@ class Model(object):
                           self.factor_lambda, self.bias_lambda, ptr(b["pred_grad"]), 1.0 / self.batch_size, None,
                           b["cap"], nuniq_dev, ptr(b["grad"]), st), "fm_grad")
         mark("grad")
-        check(lib.fm_sparse_adagrad(ptr(self.table), ptr(self.accum), self.ld, ptr(b["ori"]), b["cap"], nuniq_dev, k,
+        check(lib.fm_sparse_adagrad(ptr(self.table), ptr(self.accum), tstride, ptr(b["ori"]), b["cap"], nuniq_dev, k,
                                     ptr(b["grad"]), self.ld, self.learning_rate, ptr(b["status"]), st),
               "fm_sparse_adagrad")
         mark("adagrad")
         self.global_step += 1
         return b
 
-    def train_step(self, lines, weights=None, fused=True):
+    def train_step(self, lines, weights=None, path="claim"):
         """lines: list of str / PackedLines (host or device); weights: per-example floats or None.
         Returns the batch loss (python float); raises FmParseError like the op would."""
         packed, weights = self._to_device(lines, weights)
-        b = self.train_step_async(packed, weights, fused=fused)
+        b = self.train_step_async(packed, weights, path=path)
         host = b["status"].cpu()
         _raise(host, packed)
         return float(host[6:8].view(torch.float32)[0])
 
-    def predict_async(self, packed: PackedLines):
+    def predict_async(self, packed: PackedLines, path="claim"):
+        """scores of a device-resident batch in b["pred"].  Default: parse, then the scorer reads
+        the rows straight from the table by feature id (no unique, no gathered copy);
+        path="composed" runs the reference's chain parse -> unique -> lookup -> fm_scorer."""
         b = self._buffers(packed.n_lines, packed.text.numel())
-        self._forward(packed, b)
+        if path == "composed":
+            self._forward(packed, b)
+            return b
+        lib, st = load(), stream()
+        self._parse_unique(packed, b, unique=False)
+        check(lib.fm_fused_score_scatter(
+            ptr(b["ids"]), None, ptr(b["vals"]), ptr(b["poses"]), None, None, packed.n_lines, self.factor_num,
+            ptr(self.table), self.table.stride(0), self.factor_lambda, self.bias_lambda, 0, 0, ptr(b["pred"]),
+            _off(b["status"], 6), _off(b["status"], 7), None, 4 * ((self.factor_num + 6) // 4), ptr(b["status"]),
+            ptr(b["ws_fused"]), b["ws_fused"].numel(), st), "fm_fused_score_scatter")
         return b
 
-    def predict(self, lines):
+    def predict(self, lines, path="claim"):
         """raw pred_score per line (no sigmoid), as tffm/fm_model.py:128-142"""
         packed, _ = self._to_device(lines, None)
-        b = self.predict_async(packed)
+        b = self.predict_async(packed, path)
         host = b["status"].cpu()
         _raise(host, packed)
         return b["pred"][:packed.n_lines].clone()

@@ -198,13 +198,15 @@ int fm_sparse_adagrad(float* table, float* accum, int64_t table_ld, const int64_
  * them the row's gradient is G_0 = C + cnt rg lb b, G_k = v_k (cnt rg lf - D) + B_k,
  * which equals the sum of FmGrad's per-occurrence terms (cc/fm_grad_op.h:88-97).
  * gacc must be all zero on entry; fm_fused_adagrad leaves it all zero again.
- * table_ld and gacc_ld are multiples of 4 floats, pad columns of `table` are
- * zero, table / gacc / accum are 16-byte aligned.
+ * table_ld and gacc_ld (row strides) are multiples of 4 floats, columns K+1 up to the
+ * next multiple of 4 of a table row are zero, table / gacc / accum are 16-byte aligned.
  *
  * fm_fused_adagrad: for u < U, forms G from gacc[u] and table[ori_ids[u]] and
  * applies TF1 SparseApplyAdagrad to table / accum; rg = reg_grad (the factor the
  * objective puts on reg_score: 1 / batch_size, tffm/fm_model.py:345-347).
  * guard: as in fm_sparse_adagrad; both calls are no-ops when it is tripped.
+ * labels == NULL and gacc == NULL together: scoring only (pred_score and reg_score; no
+ * loss, no scatter) -- the predict path, reading rows from the table by feature id.
  * loss_batch: denominator of the mean loss and of d loss / d pred; 0 = batch.  A rank
  * that holds a slice of a global batch passes the global size and sums the per-rank
  * losses afterwards. */
@@ -222,6 +224,16 @@ int fm_fused_adagrad(float* table, float* accum, int64_t table_ld, const int64_t
                      int64_t n_unique, const int64_t* n_unique_dev, int64_t factor_num,
                      float* gacc, int64_t gacc_ld, float learning_rate, float factor_lambda,
                      float bias_lambda, float reg_grad, const uint64_t* guard, void* stream);
+
+/* The same pair without tf.unique: when local_ids == NULL, fm_fused_score_scatter adds
+ * to the accumulator row of the feature id itself (gacc[feature_ids[j]]: a table-shaped
+ * accumulator), and fm_fused_adagrad_claim walks the n OCCURRENCES `rows` (= feature_ids):
+ * the first lane group to swap a row's cnt column to zero applies the update, later
+ * occurrences of that row see cnt == 0 and leave.  gtab[row] belongs to table[row]. */
+int fm_fused_adagrad_claim(float* table, float* accum, int64_t table_ld, const int64_t* rows,
+                           int64_t n, const int64_t* n_dev, int64_t factor_num, float* gtab,
+                           int64_t gtab_ld, float learning_rate, float factor_lambda,
+                           float bias_lambda, float reg_grad, const uint64_t* guard, void* stream);
 
 /* ---- D1: the parameter-server sharding of tffm/fm_model.py:269-291 + run_tffm.py:181-206,
  * as explicit routing around an all-to-all: rank id % n_ranks owns table row id / n_ranks ----

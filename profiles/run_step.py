@@ -1,5 +1,5 @@
 """Short driver for ncu: a few cfg2 train steps (device-resident batches), nothing else.
-usage: python profiles/run_step.py [steps] [dist]"""
+usage: python profiles/run_step.py [steps] [dist] [path]"""
 import os
 import sys
 
@@ -14,6 +14,7 @@ from fast_tffm_b200.fm_ops import PackedLines  # noqa: E402
 
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 dist = sys.argv[2] if len(sys.argv) > 2 else "uniform"
+path = sys.argv[3] if len(sys.argv) > 3 else "claim"
 dev = torch.device("cuda", 0)
 m = Model(vocabulary_size=CFG["vocab"], factor_num=CFG["factor_num"], batch_size=CFG["batch"], hash_feature_id=True,
           loss_type=CFG["loss_type"], learning_rate=CFG["learning_rate"], adagrad_init_accumulator=CFG["init_acc"],
@@ -23,7 +24,7 @@ for i in range(2):
     text, off, _ = bench_data.criteo_batch(CFG["batch"], 1 + i, dist)
     batches.append(PackedLines(torch.from_numpy(bench_data.pad16(text)).to(dev), torch.from_numpy(off).to(dev)))
 for s in range(steps):
-    b = m.train_step_async(batches[s % 2])
+    b = m.train_step_async(batches[s % 2], path=path)
 torch.cuda.synchronize()
 st = b["status"].cpu()
 print("ok", int(st[0]), int(st[1]), int(st[4]), float(st[6:8].view(torch.float32)[0]))

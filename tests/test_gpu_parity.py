@@ -386,9 +386,9 @@ def test_lookup_and_adagrad_vs_oracle():
 
 
 # ------------------------------------------------------------ whole step ----
-@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("path", ["claim", "fused", "composed"])
 @pytest.mark.parametrize("loss_type,hashed", [("mse", False), ("logistic", False), ("logistic", True)])
-def test_train_steps_match_reference_model(criteo_lines, loss_type, hashed, fused):
+def test_train_steps_match_reference_model(criteo_lines, loss_type, hashed, path):
     """cfg1 shape in small: sample.cfg's pipeline on the Criteo excerpt, explicit initial table,
     fixed batch order; loss per step and the trained table against the oracle model"""
     lines, weights = criteo_lines
@@ -403,14 +403,16 @@ def test_train_steps_match_reference_model(criteo_lines, loss_type, hashed, fuse
         sl = slice(step * bs, (step + 1) * bs)
         w = np.float32(weights[sl]) if step % 2 == 0 else None
         e = ref.train_step(lines[sl], w)
-        got = m.train_step(lines[sl], w, fused=fused)
+        got = m.train_step(lines[sl], w, path=path)
         np.testing.assert_allclose(got, e["loss"], rtol=RTOL)
         np.testing.assert_allclose(m._bufs["pred"][:bs].cpu().numpy(), e["pred"], rtol=1e-4, atol=1e-6)
         np.testing.assert_allclose(float(m._bufs["scalars"][2]), e["reg"], rtol=RTOL)
     np.testing.assert_allclose(m.table[:, :k + 1].cpu().numpy(), ref.flat_table(), rtol=1e-4, atol=1e-7)
     np.testing.assert_allclose(m.accum[:, :k + 1].cpu().numpy(), ref.flat_acc(), rtol=1e-4, atol=1e-9)
-    pred = m.predict(lines[1000:1300])
+    pred = m.predict(lines[1000:1300], path="composed" if path == "composed" else "claim")
     np.testing.assert_allclose(pred.cpu().numpy(), ref.predict(lines[1000:1300]), rtol=1e-4, atol=1e-6)
+    if path == "claim":   # table-shaped accumulators are left all zero by the update
+        assert not m.gtab.any()
 
 
 def test_failed_parse_leaves_the_table_untouched():
@@ -430,7 +432,7 @@ def test_full_size_step_properties():
               factor_lambda=1e-5, bias_lambda=1e-5).build(DEV, seed=3, max_nnz_per_line=39)
     packed = fm_ops.PackedLines(torch.from_numpy(bench_data.pad16(text)), torch.from_numpy(off)).to(DEV, False)
     table0 = m.table.clone()
-    b = m.train_step_async(packed)
+    b = m.train_step_async(packed, path="fused")
     st = b["status"].cpu()
     assert int(st[0]) == -1 and int(st[1]) == nnz
     u = int(st[4])
