@@ -40,14 +40,28 @@ def run_sharded(args, cfg, workload_config):
         host.append(PackedLines(ht, ho))
         devb.append(PackedLines(ht.to(dev), ho.to(dev)))
 
-    def timed(batches, steps, base):
+    stage_events = []
+
+    def timed(batches, steps, base, stages=False):
         dist.barrier()
         torch.cuda.synchronize()
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0.record()
         loss = None
         for s in range(steps):
-            loss = m.train_step(batches[(base + s) % len(batches)], global_batch=b * world)
+            evs = []
+
+            def mark(name, evs=evs):
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                evs.append((name, e))
+            if stages:
+                mark("start")
+            loss = m.train_step(batches[(base + s) % len(batches)], global_batch=b * world,
+                                mark=mark if stages else (lambda name: None))
+            if stages:
+                mark("allreduce_loss")
+                stage_events.append(evs)
         t1.record()
         torch.cuda.synchronize()
         dist.barrier()
@@ -59,8 +73,12 @@ def run_sharded(args, cfg, workload_config):
         m.train_step(devb[s % len(devb)], global_batch=b * world)
     sampler = ClockSampler(local_rank)
     sampler.start()
-    total_ms, loss = timed(devb, args.steps, args.warmup)
+    total_ms, loss = timed(devb, args.steps, args.warmup, stages=True)
     clocks = sampler.stop()
+    stage_ms = {}
+    for evs in stage_events:
+        for (_, e0), (name, e1) in zip(evs[:-1], evs[1:]):
+            stage_ms[name] = stage_ms.get(name, 0.0) + e0.elapsed_time(e1) / len(stage_events)
     e2e_ms, _ = timed(host, args.steps, args.warmup)            # host buffers: H2D of the text inside the region
 
     stats = torch.tensor([m.last["nnz"], m.last["n_unique"], m.last["sent_rows"]], dtype=torch.float64, device=dev)
@@ -90,6 +108,7 @@ def run_sharded(args, cfg, workload_config):
                     "h2d_bytes_per_step": int(host[0].text.numel() + host[0].offsets.numel() * 8) * world,
                     "d2h_bytes_per_step": 8 * world, "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": 20 * args.steps,
+            "stage_ms_rank0": {k_: round(v, 4) for k_, v in stage_ms.items()},
             "clocks": clocks, "final_loss": loss, "nnz_per_rank": nnz, "unique_per_rank": nuniq,
         }
         print(json.dumps(line))

@@ -124,14 +124,14 @@ local_rows_kernel(const int64_t* __restrict__ ids, int64_t n, int g, int64_t* __
 
 // dst[index[i], :] += src[i, :]  as float4 vector atomics; ld multiple of 4
 __global__ void __launch_bounds__(256)
-combine_rows_kernel(const float* __restrict__ src, const int32_t* __restrict__ index, int64_t n, int vec_per_row,
-                    float* __restrict__ dst) {
+combine_rows_kernel(const float* __restrict__ src, int64_t src_ld, const int64_t* __restrict__ index, int64_t n,
+                    int vec_per_row, float* __restrict__ dst, int64_t dst_ld) {
   const int64_t total = n * vec_per_row;
   for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
     const int64_t i = t / vec_per_row;
     const int v = (int)(t - i * vec_per_row);
-    const float4 x = __ldg(reinterpret_cast<const float4*>(src) + t);
-    float* d = dst + ((int64_t)index[i] * vec_per_row + v) * 4;
+    const float4 x = __ldg(reinterpret_cast<const float4*>(src + i * src_ld) + v);
+    float* d = dst + index[i] * dst_ld + 4 * v;
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d), "f"(x.x), "f"(x.y), "f"(x.z), "f"(x.w)
                  : "memory");
   }
@@ -197,14 +197,16 @@ FM_EXPORT int fm_shard_local_rows(const int64_t* ids, int64_t n, int64_t n_ranks
   return FM_OK;
 }
 
-FM_EXPORT int fm_shard_combine(const float* src_rows, const int32_t* index, int64_t n, int64_t ld, float* dst_rows,
-                               void* stream_) {
+FM_EXPORT int fm_shard_combine(const float* src_rows, int64_t src_ld, const int64_t* index, int64_t n, int64_t width,
+                               float* dst_rows, int64_t dst_ld, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
-  FM_REQUIRE(n >= 0 && ld > 0 && ld % 4 == 0, "fm_shard_combine: ld must be a positive multiple of 4");
+  FM_REQUIRE(n >= 0 && width > 0 && width % 4 == 0 && src_ld % 4 == 0 && dst_ld % 4 == 0 && src_ld >= width &&
+                 dst_ld >= width, "fm_shard_combine: width and strides must be positive multiples of 4");
   if (n == 0) return FM_OK;
   FM_REQUIRE(src_rows && index && dst_rows, "fm_shard_combine: null pointer");
   FM_REQUIRE((((uintptr_t)src_rows | (uintptr_t)dst_rows) & 15) == 0, "fm_shard_combine: 16-byte alignment required");
-  combine_rows_kernel<<<grid_for(n * (ld / 4), 256), 256, 0, stream>>>(src_rows, index, n, (int)(ld / 4), dst_rows);
+  combine_rows_kernel<<<grid_for(n * (width / 4), 256), 256, 0, stream>>>(src_rows, src_ld, index, n, (int)(width / 4),
+                                                                        dst_rows, dst_ld);
   FM_LAUNCH_CHECK();
   return FM_OK;
 }

@@ -30,6 +30,21 @@ lookup_kernel(const float* __restrict__ table, int64_t table_ld, const int64_t* 
   }
 }
 
+// float4 flavour: thread per (row, 16-byte chunk), no idle lanes
+__global__ void __launch_bounds__(256)
+lookup_vec_kernel(const float* __restrict__ table, int64_t table_ld, const int64_t* __restrict__ ori_ids,
+                  int64_t n_max, const int64_t* __restrict__ n_dev, int chunks, float* __restrict__ out,
+                  int64_t out_ld, const unsigned long long* __restrict__ guard) {
+  if (guard && *guard != 0xffffffffffffffffull) return;
+  const int64_t total = dev_count(n_max, n_dev) * chunks;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t u = t / chunks;
+    const int c = (int)(t - u * chunks);
+    *reinterpret_cast<float4*>(out + u * out_ld + 4 * c) =
+        __ldg(reinterpret_cast<const float4*>(table + ori_ids[u] * table_ld + 4 * c));
+  }
+}
+
 // acc += g^2 ; w -= lr * g / sqrt(acc)   (TF1 SparseApplyAdagrad: no epsilon; every
 // listed row is touched even when g == 0)
 template <int LPR>
@@ -133,8 +148,18 @@ FM_EXPORT int fm_lookup(const float* table, int64_t table_ld, const int64_t* ori
   FM_REQUIRE(n_unique >= 0 && factor_num >= 0 && table_ld >= width && out_ld >= width, "fm_lookup: bad shape");
   if (n_unique == 0) return FM_OK;
   FM_REQUIRE(table && ori_ids && out, "fm_lookup: null pointer");
-  dispatch_width<LookupLaunch>((int)width, table, table_ld, ori_ids, n_unique, n_unique_dev, (int)width, out,
-                               out_ld, reinterpret_cast<const unsigned long long*>(guard), stream);
+  const int64_t chunks = (width + 3) / 4;
+  if (table_ld % 4 == 0 && out_ld % 4 == 0 && out_ld >= 4 * chunks && table_ld >= 4 * chunks &&
+      (((uintptr_t)table | (uintptr_t)out) & 15) == 0) {
+    // rows as 16-byte chunks (the pad columns travel along)
+    int64_t blocks = (n_unique * chunks + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    lookup_vec_kernel<<<(unsigned)blocks, 256, 0, stream>>>(table, table_ld, ori_ids, n_unique, n_unique_dev, (int)chunks,
+                                                           out, out_ld, reinterpret_cast<const unsigned long long*>(guard));
+  } else {
+    dispatch_width<LookupLaunch>((int)width, table, table_ld, ori_ids, n_unique, n_unique_dev, (int)width, out,
+                                 out_ld, reinterpret_cast<const unsigned long long*>(guard), stream);
+  }
   FM_LAUNCH_CHECK();
   return FM_OK;
 }

@@ -13,9 +13,12 @@ and one step is
     all_to_all counts, all_to_all ids          -> every owner learns which rows are wanted
     owners gather rows (fm_lookup)             -> all_to_all rows back
     fm_fused_score_scatter on the received rows (loss over the GLOBAL batch size)
-    all_to_all accumulator rows to the owners  -> owners sum rows of the same id
-                                                  (fm_unique + fm_shard_combine) and apply
-                                                  fm_fused_adagrad once per id
+    all_to_all accumulator rows to the owners  -> owners add them into the accumulator row
+                                                  that sits beside each table row
+                                                  (fm_shard_combine), then
+                                                  fm_fused_adagrad_claim walks the received id
+                                                  list: the first entry of an id applies the
+                                                  update, its repeats from other ranks leave
     all_reduce(loss)
 
 so a G-GPU step equals the single-GPU step on the same global batch (sums are combined
@@ -31,7 +34,7 @@ import torch.distributed as dist
 
 from . import _lib
 from ._lib import check, load, ptr, stream
-from .fm_model import Model, _ld_for
+from .fm_model import Model, _ld_for, _stride_for
 from .fm_ops import FmParseError, PackedLines, pack_lines
 
 
@@ -121,19 +124,20 @@ class CudaShardKernels:
         return rows
 
     def lookup(self, table, rows, k):
-        out = torch.zeros(rows.numel(), table.stride(0), dtype=torch.float32, device=table.device)
+        """rows as they travel: K+1 floats rounded up to whole 16-byte chunks"""
+        out = torch.empty(rows.numel(), 4 * ((k + 4) // 4), dtype=torch.float32, device=table.device)
         check(self.lib.fm_lookup(ptr(table), table.stride(0), ptr(rows), rows.numel(), None, k, ptr(out),
                                  out.stride(0), None, stream()), "fm_lookup")
         return out
 
     def combine(self, src, index, dst):
-        check(self.lib.fm_shard_combine(ptr(src), ptr(index), src.shape[0], src.stride(0), ptr(dst), stream()),
-              "fm_shard_combine")
+        check(self.lib.fm_shard_combine(ptr(src), src.stride(0), ptr(index), src.shape[0], src.shape[1], ptr(dst),
+                                        dst.stride(0), stream()), "fm_shard_combine")
 
-    def adagrad(self, table, accum, rows, k, gacc, lr, lf, lb, reg_grad):
-        check(self.lib.fm_fused_adagrad(ptr(table), ptr(accum), table.stride(0), ptr(rows), rows.numel(), None, k,
-                                        ptr(gacc), gacc.stride(0), lr, lf, lb, reg_grad, None, stream()),
-              "fm_fused_adagrad")
+    def adagrad_claim(self, table, accum, rows, k, gtab, lr, lf, lb, reg_grad):
+        check(self.lib.fm_fused_adagrad_claim(ptr(table), ptr(accum), table.stride(0), ptr(rows), rows.numel(), None,
+                                              k, ptr(gtab), gtab.stride(0), lr, lf, lb, reg_grad, None, stream()),
+              "fm_fused_adagrad_claim")
 
     def gacc_ld(self, k):
         return int(self.lib.fm_fused_gacc_ld(k))
@@ -176,6 +180,8 @@ class ShardedModel:
             gen.manual_seed((seed or 0) * 1000 + r)
             self.table[:, :k + 1].uniform_(-self.cfg.init_value_range, self.cfg.init_value_range, generator=gen)
         self.accum = torch.full_like(self.table, self.cfg.adagrad_init_accumulator)
+        # gradient accumulator rows, one beside each table row of this shard (all zero between steps)
+        self.gtab = torch.zeros(rows, _stride_for(self.kernels.gacc_ld(k)), dtype=torch.float32, device=self.device)
         return self
 
     def gather_full_table(self):
@@ -189,30 +195,35 @@ class ShardedModel:
         return full[:self.cfg.vocabulary_size]
 
     # -- one step ----------------------------------------------------------------------
-    def _route(self, lines):
+    def _route(self, lines, mark=lambda name: None):
         """parse + unique locally, exchange ids, fetch rows.  Returns the step's working set."""
         kn, g, k = self.kernels, self.world, self.cfg.factor_num
         packed = lines if isinstance(lines, PackedLines) else pack_lines(list(lines))
         if packed.text.device != self.device:
             packed = packed.to(self.device, non_blocking=False)
         p = kn.parse_unique(packed, self.cfg.vocabulary_size, self.cfg.hash_feature_id)
+        mark("parse_unique")
         send_ids, pos, counts = kn.bucket(p["ori"], g)
         recv_counts_t = torch.empty_like(counts)
         dist.all_to_all_single(recv_counts_t, counts, group=self.group)
         send_counts, recv_counts = counts.tolist(), recv_counts_t.tolist()
+        mark("bucket_counts")
         want_ids = _exchange(send_ids, send_counts, recv_counts, self.group)      # ids other ranks want from me
-        own_rows = kn.local_rows(want_ids, g)
+        mark("xchg_ids")
+        own_rows = kn.local_rows(want_ids, g)                                     # my rows the others asked for
         rows_out = kn.lookup(self.table, own_rows, k)
+        mark("lookup")
         rows_in = _exchange(rows_out, recv_counts, send_counts, self.group)       # my distinct ids' rows, bucket order
+        mark("xchg_rows")
         slot64, slot32 = kn.remap(p["local"], pos)
-        p.update(send_counts=send_counts, recv_counts=recv_counts, want_ids=want_ids, rows_in=rows_in,
+        p.update(send_counts=send_counts, recv_counts=recv_counts, own_rows=own_rows, rows_in=rows_in,
                  slot64=slot64, slot32=slot32, n_lines=packed.n_lines)
         return p
 
-    def train_step(self, lines, weights=None, global_batch=None):
+    def train_step(self, lines, weights=None, global_batch=None, mark=lambda name: None):
         """lines / weights: this rank's slice of the global batch.  Returns the GLOBAL mean loss."""
         kn, g, k, cfg = self.kernels, self.world, self.cfg.factor_num, self.cfg
-        p = self._route(lines)
+        p = self._route(lines, mark)
         if global_batch is None:
             nb = torch.tensor([p["n_lines"]], dtype=torch.int64, device=self.device)
             dist.all_reduce(nb, group=self.group)
@@ -226,12 +237,13 @@ class ShardedModel:
         pred, scal = kn.score_scatter(p["slot64"], p["slot32"], p["vals"], p["poses"], p["labels"], weights, k,
                                       p["rows_in"], cfg.factor_lambda, cfg.bias_lambda, cfg.loss_type, global_batch,
                                       gacc)
+        mark("score_scatter")
         gacc_in = _exchange(gacc, p["send_counts"], p["recv_counts"], self.group)  # rows for ids I own
-        own_ids, inv = kn.unique(p["want_ids"])
-        own_gacc = torch.zeros(own_ids.numel(), gld, dtype=torch.float32, device=self.device)
-        kn.combine(gacc_in, inv, own_gacc)
-        kn.adagrad(self.table, self.accum, kn.local_rows(own_ids, g), k, own_gacc, cfg.learning_rate,
-                   cfg.factor_lambda, cfg.bias_lambda, 1.0 / cfg.batch_size)
+        mark("xchg_gacc")
+        kn.combine(gacc_in, p["own_rows"], self.gtab)            # sums over ranks land beside the table rows
+        kn.adagrad_claim(self.table, self.accum, p["own_rows"], k, self.gtab, cfg.learning_rate,
+                         cfg.factor_lambda, cfg.bias_lambda, 1.0 / cfg.batch_size)
+        mark("update")
         dist.all_reduce(scal, group=self.group)
         self.global_step += 1
         self.last = dict(pred=pred, reg=scal[1], n_unique=p["ori"].numel(), nnz=p["ids"].numel(),

@@ -242,16 +242,17 @@ int fm_fused_adagrad_claim(float* table, float* accum, int64_t table_ld, const i
  * fm_shard_remap: slot64[j] = slot32[j] = pos[local_ids[j]] (row index of occurrence j in
  *   the rows received back / the accumulator rows sent out).
  * fm_shard_local_rows: rows[j] = ids[j] / n_ranks (owner side).
- * fm_shard_combine: dst_rows[index[i], :] += src_rows[i, :] (owner side: accumulator rows
- *   from several ranks for one id are summed before the Adagrad square); ld % 4 == 0. */
+ * fm_shard_combine: dst_rows[index[i], 0:width] += src_rows[i, 0:width] (owner side:
+ *   accumulator rows from several ranks for one id are summed before the Adagrad square);
+ *   width and both strides are multiples of 4 floats. */
 size_t fm_shard_bucket_workspace(int64_t n, int64_t n_ranks);
 int fm_shard_bucket(const int64_t* ids, int64_t n, int64_t n_ranks, int64_t* send_ids, int32_t* pos,
                     int64_t* counts, void* workspace, size_t workspace_bytes, void* stream);
 int fm_shard_remap(const int32_t* local_ids, int64_t n, const int64_t* n_dev, const int32_t* pos,
                    int64_t* slot64, int32_t* slot32, void* stream);
 int fm_shard_local_rows(const int64_t* ids, int64_t n, int64_t n_ranks, int64_t* rows, void* stream);
-int fm_shard_combine(const float* src_rows, const int32_t* index, int64_t n, int64_t ld,
-                     float* dst_rows, void* stream);
+int fm_shard_combine(const float* src_rows, int64_t src_ld, const int64_t* index, int64_t n,
+                     int64_t width, float* dst_rows, int64_t dst_ld, void* stream);
 
 #ifdef __cplusplus
 }

@@ -70,27 +70,28 @@ class OracleShardKernels:
         return ids // n_ranks
 
     def lookup(self, table, rows, k):
-        out = torch.zeros(rows.numel(), table.shape[1])
+        out = torch.zeros(rows.numel(), 4 * ((k + 4) // 4))
         out[:, :k + 1] = table[rows, :k + 1]
         return out
 
     def combine(self, src, index, dst):
         acc = dst.numpy().astype(np.float64)
-        np.add.at(acc, index.numpy(), src.numpy().astype(np.float64))
+        np.add.at(acc[:, :src.shape[1]], index.numpy(), src.numpy().astype(np.float64))
         dst.copy_(_t(acc, torch.float32))
 
-    def adagrad(self, table, accum, rows, k, gacc, lr, lf, lb, reg_grad):
-        r = rows.numpy()
-        a = gacc.numpy().astype(np.float64)
+    def adagrad_claim(self, table, accum, rows, k, gtab, lr, lf, lb, reg_grad):
+        r = np.unique(rows.numpy())            # every listed row once, whoever lists it first
+        a = gtab.numpy()[r].astype(np.float64)
         w = table.numpy()[r, :k + 1].astype(np.float64)
         cnt, d = a[:, k + 2], a[:, k + 1]
         g = np.empty_like(w)
         g[:, 0] = a[:, 0] + cnt * reg_grad * lb * w[:, 0]
         g[:, 1:] = w[:, 1:] * (cnt * reg_grad * lf - d)[:, None] + a[:, 1:k + 1]
         h = accum.numpy()[r, :k + 1].astype(np.float64) + g * g
+        rows = _t(r)
         accum[rows, :k + 1] = _t(h, torch.float32)
         table[rows, :k + 1] = _t(w - lr * g / np.sqrt(h.astype(np.float32)), torch.float32)
-        gacc.zero_()
+        gtab[rows] = 0.0
 
     def gacc_ld(self, k):
         return (k + 3 + 3) // 4 * 4
