@@ -32,7 +32,7 @@ def run_sharded(args, cfg, workload_config):
                   loss_type=cfg["loss_type"], learning_rate=cfg["learning_rate"],
                   adagrad_init_accumulator=cfg["init_acc"], factor_lambda=cfg["factor_lambda"],
                   bias_lambda=cfg["bias_lambda"])
-    m = ShardedModel(model, device=dev).build(seed=0)
+    m = ShardedModel(model, device=dev, max_nnz_per_line=cfg["nnz_per_line"]).build(seed=0)
     host, devb = [], []
     for i in range(args.batches):
         text, off, _ = bench_data.criteo_batch(b, 1000 * (rank + 1) + i, args.dist)
@@ -57,8 +57,8 @@ def run_sharded(args, cfg, workload_config):
                 evs.append((name, e))
             if stages:
                 mark("start")
-            loss = m.train_step(batches[(base + s) % len(batches)], global_batch=b * world,
-                                mark=mark if stages else (lambda name: None))
+            loss = m.train_step_async(batches[(base + s) % len(batches)], global_batch=b * world,
+                                      mark=mark if stages else (lambda name: None))
             if stages:
                 mark("allreduce_loss")
                 stage_events.append(evs)
@@ -67,10 +67,10 @@ def run_sharded(args, cfg, workload_config):
         dist.barrier()
         ms = torch.tensor([t0.elapsed_time(t1)], device=dev)
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item()), loss
+        return float(ms.item()), float(loss[0].item())
 
     for s in range(args.warmup):
-        m.train_step(devb[s % len(devb)], global_batch=b * world)
+        m.train_step_async(devb[s % len(devb)], global_batch=b * world)
     sampler = ClockSampler(local_rank)
     sampler.start()
     total_ms, loss = timed(devb, args.steps, args.warmup, stages=True)
@@ -106,7 +106,7 @@ def run_sharded(args, cfg, workload_config):
             "cpu_baseline": None,
             "e2e": {"value": args.steps * b * world / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": int(host[0].text.numel() + host[0].offsets.numel() * 8) * world,
-                    "d2h_bytes_per_step": 8 * world, "ms_per_step": e2e_ms / args.steps},
+                    "d2h_bytes_per_step": 8 * (3 + world) * world * world, "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": 20 * args.steps,
             "stage_ms_rank0": {k_: round(v, 4) for k_, v in stage_ms.items()},
             "clocks": clocks, "final_loss": loss, "nnz_per_rank": nnz, "unique_per_rank": nuniq,

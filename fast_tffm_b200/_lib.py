@@ -50,7 +50,7 @@ _SIGNATURES = {
     "fm_fused_adagrad_claim": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _f32, _f32, _f32, _f32, _vp,
                                          _vp]),
     "fm_shard_bucket_workspace": (_sz, [_i64, _i64]),
-    "fm_shard_bucket": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "fm_shard_bucket": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
     "fm_shard_remap": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     "fm_shard_local_rows": (C.c_int, [_vp, _i64, _i64, _vp, _vp]),
     "fm_shard_combine": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _vp, _i64, _vp]),

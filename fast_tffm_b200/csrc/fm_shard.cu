@@ -25,8 +25,10 @@ constexpr int kBThreads = 256, kBItems = 4, kBTile = kBThreads * kBItems, kMaxRa
 __device__ __forceinline__ int owner_of(int64_t id, int g) { return (int)((uint64_t)id % (uint64_t)g); }
 
 __global__ void __launch_bounds__(kBThreads)
-bucket_hist_kernel(const int64_t* __restrict__ ids, int64_t n, int g, int* __restrict__ block_counts) {
+bucket_hist_kernel(const int64_t* __restrict__ ids, int64_t n_max, const int64_t* __restrict__ n_dev, int g,
+                   int* __restrict__ block_counts) {
   __shared__ int s_cnt[kMaxRanks];
+  const int64_t n = n_dev ? min(*n_dev, n_max) : n_max;
   if (threadIdx.x < kMaxRanks) s_cnt[threadIdx.x] = 0;
   __syncthreads();
   const int64_t base = (int64_t)blockIdx.x * kBTile + threadIdx.x * kBItems;
@@ -67,9 +69,11 @@ bucket_offsets_kernel(const int* __restrict__ block_counts, int64_t n_blocks, in
 }
 
 __global__ void __launch_bounds__(kBThreads)
-bucket_scatter_kernel(const int64_t* __restrict__ ids, int64_t n, int g, const int64_t* __restrict__ block_base,
-                      int64_t* __restrict__ send_ids, int32_t* __restrict__ pos) {
+bucket_scatter_kernel(const int64_t* __restrict__ ids, int64_t n_max, const int64_t* __restrict__ n_dev, int g,
+                      const int64_t* __restrict__ block_base, int64_t* __restrict__ send_ids,
+                      int32_t* __restrict__ pos) {
   __shared__ int s_warp[kBThreads / 32];
+  const int64_t n = n_dev ? min(*n_dev, n_max) : n_max;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t base = (int64_t)blockIdx.x * kBTile + tid * kBItems;
   int64_t id[kBItems];
@@ -153,8 +157,8 @@ FM_EXPORT size_t fm_shard_bucket_workspace(int64_t n, int64_t n_ranks) {
   return fm_align_up((size_t)blocks * (size_t)n_ranks * (sizeof(int) + sizeof(int64_t)) + 256, 256);
 }
 
-FM_EXPORT int fm_shard_bucket(const int64_t* ids, int64_t n, int64_t n_ranks, int64_t* send_ids, int32_t* pos,
-                              int64_t* counts, void* workspace, size_t workspace_bytes, void* stream_) {
+FM_EXPORT int fm_shard_bucket(const int64_t* ids, int64_t n, const int64_t* n_dev, int64_t n_ranks, int64_t* send_ids,
+                              int32_t* pos, int64_t* counts, void* workspace, size_t workspace_bytes, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   FM_REQUIRE(n >= 0 && n_ranks >= 1, "fm_shard_bucket: bad size");
   if (n_ranks > kMaxRanks) return fm_fail(FM_E_LIMIT, "fm_shard_bucket: more than %d ranks", kMaxRanks);
@@ -165,12 +169,13 @@ FM_EXPORT int fm_shard_bucket(const int64_t* ids, int64_t n, int64_t n_ranks, in
   const int64_t blocks = n <= 0 ? 1 : (n + kBTile - 1) / kBTile;
   int64_t* block_base = reinterpret_cast<int64_t*>(workspace);
   int* block_counts = reinterpret_cast<int*>(block_base + blocks * n_ranks);
-  bucket_hist_kernel<<<(unsigned)blocks, kBThreads, 0, stream>>>(ids, n, (int)n_ranks, block_counts);
+  bucket_hist_kernel<<<(unsigned)blocks, kBThreads, 0, stream>>>(ids, n, n_dev, (int)n_ranks, block_counts);
   FM_LAUNCH_CHECK();
   bucket_offsets_kernel<<<1, 256, 0, stream>>>(block_counts, blocks, (int)n_ranks, block_base, counts);
   FM_LAUNCH_CHECK();
   if (n > 0) {
-    bucket_scatter_kernel<<<(unsigned)blocks, kBThreads, 0, stream>>>(ids, n, (int)n_ranks, block_base, send_ids, pos);
+    bucket_scatter_kernel<<<(unsigned)blocks, kBThreads, 0, stream>>>(ids, n, n_dev, (int)n_ranks, block_base, send_ids,
+                                                                      pos);
     FM_LAUNCH_CHECK();
   }
   return FM_OK;

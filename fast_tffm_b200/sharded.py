@@ -9,8 +9,10 @@ gRPC, asynchronously).  Here the split is explicit and synchronous:
     rank r parses examples [r*B/G, (r+1)*B/G) of the global batch
 
 and one step is
-    parse + unique (local)                     -> distinct ids, grouped by owner (fm_shard_bucket)
-    all_to_all counts, all_to_all ids          -> every owner learns which rows are wanted
+    parse + unique (local) + group the distinct ids by owner (fm_shard_bucket)
+    all_gather of a small info vector (sizes, per-owner counts, parse status): the step's
+                                               ONE host synchronisation
+    all_to_all ids                             -> every owner learns which rows are wanted
     owners gather rows (fm_lookup)             -> all_to_all rows back
     fm_fused_score_scatter on the received rows (loss over the GLOBAL batch size)
     all_to_all accumulator rows to the owners  -> owners add them into the accumulator row
@@ -37,74 +39,78 @@ from ._lib import check, load, ptr, stream
 from .fm_model import Model, _ld_for, _stride_for
 from .fm_ops import FmParseError, PackedLines, pack_lines
 
+INFO_NNZ, INFO_UNIQUE, INFO_ERROR, INFO_COUNTS = 0, 1, 2, 3   # layout of the per-rank info vector
+
+
+def _at(t, index):
+    return ctypes.c_void_p(t.data_ptr() + index * t.element_size())
+
 
 class CudaShardKernels:
-    """the C ABI of libfm_b200.so behind the small set of operations ShardedModel needs"""
+    """the C ABI of libfm_b200.so behind the small set of operations ShardedModel needs.
+    Buffers are sized by capacity and reused; data-dependent sizes stay on the device."""
 
-    def __init__(self):
+    def __init__(self, max_nnz_per_line=None):
         self.lib = load()
+        self.max_nnz_per_line = max_nnz_per_line
+        self._b = None
+
+    def _buffers(self, n_lines, text_bytes, n_ranks, dev):
+        cap = int(text_bytes // 2 + 1)
+        if self.max_nnz_per_line:
+            cap = min(cap, int(n_lines * self.max_nnz_per_line))
+        b = self._b
+        if b is not None and b["lines"] >= n_lines and b["cap"] >= cap and b["ranks"] == n_ranks:
+            return b
+        lib = self.lib
+        lines, cap = max(n_lines, b["lines"] if b else 0), max(cap, b["cap"] if b else 0)
+        f32, i32, i64 = torch.float32, torch.int32, torch.int64
+        e = lambda n, dt: torch.empty(n, dtype=dt, device=dev)
+        self._b = b = dict(
+            lines=lines, cap=cap, ranks=n_ranks, labels=e(lines, f32), sizes=e(lines, i32), poses=e(lines + 1, i32),
+            ids=e(cap, i64), vals=e(cap, f32), ori=e(cap, i64), local=e(cap, i32), send_ids=e(cap, i64),
+            pos=e(cap, i32), slot64=e(cap, i64), slot32=e(cap, i32),
+            status=torch.zeros(8, dtype=i64, device=dev),                 # fm_parse_status + n_unique at [4]
+            info=torch.zeros(INFO_COUNTS + n_ranks, dtype=i64, device=dev),
+            ws_parse=_lib.workspace(lib.fm_parse_workspace(lines), dev),
+            ws_unique=_lib.workspace(lib.fm_unique_workspace(cap), dev),
+            ws_bucket=_lib.workspace(lib.fm_shard_bucket_workspace(cap, n_ranks), dev),
+            ws_fused=_lib.workspace(lib.fm_fused_workspace(lines), dev),
+            pred=e(lines, f32), scal=torch.zeros(2, dtype=f32, device=dev))
+        return b
 
     # -- local side ------------------------------------------------------------------
-    def parse_unique(self, packed, vocab, hashed):
-        lib, dev, n_lines = self.lib, packed.text.device, packed.n_lines
-        f32, i32, i64 = torch.float32, torch.int32, torch.int64
-        labels = torch.empty(n_lines, dtype=f32, device=dev)
-        sizes = torch.empty(n_lines, dtype=i32, device=dev)
-        poses = torch.empty(n_lines + 1, dtype=i32, device=dev)
-        status = torch.zeros(8, dtype=i64, device=dev)
-        ws = _lib.workspace(lib.fm_parse_workspace(n_lines), dev)
-        check(lib.fm_parse_count(ptr(packed.text), ptr(packed.offsets), n_lines, vocab, int(hashed), ptr(sizes),
-                                 ptr(poses), ptr(status), ptr(ws), ws.numel(), stream()), "fm_parse_count")
-        nnz = int(status[1].item())
-        ids = torch.empty(nnz, dtype=i64, device=dev)
-        vals = torch.empty(nnz, dtype=f32, device=dev)
-        check(lib.fm_parse_fill(ptr(packed.text), ptr(packed.offsets), n_lines, vocab, int(hashed), ptr(poses),
-                                ptr(labels), ptr(ids), ptr(vals), nnz, ptr(status), ptr(ws), ws.numel(), stream()),
-              "fm_parse_fill")
-        ori, local = self.unique(ids)
-        first = int(status[0].item()) & 0xFFFFFFFFFFFFFFFF
-        if first != _lib.NO_ERROR:
-            raise FmParseError(first & 7, first >> 3, packed.line(first >> 3))
-        return dict(labels=labels, poses=poses, ids=ids, vals=vals, ori=ori, local=local)
-
-    def unique(self, ids):
-        lib, n = self.lib, ids.numel()
-        ori = torch.empty(max(n, 1), dtype=torch.int64, device=ids.device)
-        local = torch.empty(n, dtype=torch.int32, device=ids.device)
-        n_unique = torch.zeros(1, dtype=torch.int64, device=ids.device)
-        ws = _lib.workspace(lib.fm_unique_workspace(n), ids.device)
-        check(lib.fm_unique(ptr(ids), n, None, ptr(ori), ptr(local), ptr(n_unique), ptr(ws), ws.numel(), stream()),
-              "fm_unique")
-        return ori[:int(n_unique.item())], local
-
-    def bucket(self, ori, n_ranks):
-        lib, n = self.lib, ori.numel()
-        send_ids = torch.empty(n, dtype=torch.int64, device=ori.device)
-        pos = torch.empty(n, dtype=torch.int32, device=ori.device)
-        counts = torch.zeros(n_ranks, dtype=torch.int64, device=ori.device)
-        ws = _lib.workspace(lib.fm_shard_bucket_workspace(n, n_ranks), ori.device)
-        check(lib.fm_shard_bucket(ptr(ori), n, n_ranks, ptr(send_ids), ptr(pos), ptr(counts), ptr(ws), ws.numel(),
-                                  stream()), "fm_shard_bucket")
-        return send_ids, pos, counts
-
-    def remap(self, local, pos):
-        n = local.numel()
-        slot64 = torch.empty(n, dtype=torch.int64, device=local.device)
-        slot32 = torch.empty(n, dtype=torch.int32, device=local.device)
-        check(self.lib.fm_shard_remap(ptr(local), n, None, ptr(pos), ptr(slot64), ptr(slot32), stream()),
-              "fm_shard_remap")
-        return slot64, slot32
+    def parse_unique_bucket(self, packed, vocab, hashed, n_ranks):
+        """parse -> unique -> group distinct ids by owner -> per-occurrence slots; enqueues only.
+        Returns capacity-sized tensors and `info` = [nnz, n_unique, parse status, counts[G]] (device)."""
+        lib, dev, n_lines, st = self.lib, packed.text.device, packed.n_lines, stream()
+        b = self._buffers(n_lines, packed.text.numel(), n_ranks, dev)
+        status, nnz_dev, nuniq_dev = ptr(b["status"]), _at(b["status"], 1), _at(b["status"], 4)
+        check(lib.fm_parse_count(ptr(packed.text), ptr(packed.offsets), n_lines, vocab, int(hashed), ptr(b["sizes"]),
+                                 ptr(b["poses"]), status, ptr(b["ws_parse"]), b["ws_parse"].numel(), st),
+              "fm_parse_count")
+        check(lib.fm_parse_fill(ptr(packed.text), ptr(packed.offsets), n_lines, vocab, int(hashed), ptr(b["poses"]),
+                                ptr(b["labels"]), ptr(b["ids"]), ptr(b["vals"]), b["cap"], status, ptr(b["ws_parse"]),
+                                b["ws_parse"].numel(), st), "fm_parse_fill")
+        check(lib.fm_unique(ptr(b["ids"]), b["cap"], nnz_dev, ptr(b["ori"]), ptr(b["local"]), nuniq_dev,
+                            ptr(b["ws_unique"]), b["ws_unique"].numel(), st), "fm_unique")
+        check(lib.fm_shard_bucket(ptr(b["ori"]), b["cap"], nuniq_dev, n_ranks, ptr(b["send_ids"]), ptr(b["pos"]),
+                                  _at(b["info"], INFO_COUNTS), ptr(b["ws_bucket"]), b["ws_bucket"].numel(), st),
+              "fm_shard_bucket")
+        check(lib.fm_shard_remap(ptr(b["local"]), b["cap"], nnz_dev, ptr(b["pos"]), ptr(b["slot64"]), ptr(b["slot32"]),
+                                 st), "fm_shard_remap")
+        b["info"][INFO_NNZ:INFO_COUNTS] = b["status"][[1, 4, 0]]      # nnz, n_unique, first_error
+        return dict(labels=b["labels"][:n_lines], poses=b["poses"][:n_lines + 1], vals=b["vals"],
+                    send_ids=b["send_ids"], slot64=b["slot64"], slot32=b["slot32"], info=b["info"])
 
     def score_scatter(self, slot64, slot32, vals, poses, labels, weights, k, rows, lf, lb, loss_type, global_batch,
                       gacc):
-        lib, b, dev = self.lib, labels.numel(), labels.device
-        pred = torch.empty(b, dtype=torch.float32, device=dev)
-        scal = torch.zeros(2, dtype=torch.float32, device=dev)
-        ws = _lib.workspace(lib.fm_fused_workspace(b), dev)
+        lib, b, bufs = self.lib, labels.numel(), self._b
+        pred, scal = bufs["pred"][:b], bufs["scal"]
         check(lib.fm_fused_score_scatter(
             ptr(slot64), ptr(slot32), ptr(vals), ptr(poses), ptr(labels), ptr(weights), b, k, ptr(rows),
-            rows.stride(0), lf, lb, _lib.LOSS_KIND[loss_type], global_batch, ptr(pred), ptr(scal),
-            ctypes.c_void_p(scal.data_ptr() + 4), ptr(gacc), gacc.stride(0), None, ptr(ws), ws.numel(), stream()),
+            rows.stride(0), lf, lb, _lib.LOSS_KIND[loss_type], global_batch, ptr(pred), ptr(scal), _at(scal, 1),
+            ptr(gacc), gacc.stride(0), None, ptr(bufs["ws_fused"]), bufs["ws_fused"].numel(), stream()),
             "fm_fused_score_scatter")
         return pred, scal
 
@@ -146,20 +152,20 @@ class CudaShardKernels:
 def _exchange(send, send_counts, recv_counts, group):
     """all_to_all of row blocks: send[sum(send_counts), ...] -> recv[sum(recv_counts), ...]"""
     out = send.new_empty((sum(recv_counts),) + tuple(send.shape[1:]))
-    dist.all_to_all_single(out, send.contiguous(), output_split_sizes=list(recv_counts),
-                           input_split_sizes=list(send_counts), group=group)
+    dist.all_to_all_single(out, send, output_split_sizes=list(recv_counts), input_split_sizes=list(send_counts),
+                           group=group)
     return out
 
 
 class ShardedModel:
     """Model (same config object) with the table row-partitioned over the ranks of `group`."""
 
-    def __init__(self, model: Model, group=None, kernels=None, device=None):
+    def __init__(self, model: Model, group=None, kernels=None, device=None, max_nnz_per_line=None):
         self.cfg = model
         self.group = group
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
-        self.kernels = kernels if kernels is not None else CudaShardKernels()
+        self.kernels = kernels if kernels is not None else CudaShardKernels(max_nnz_per_line)
         self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
         self.global_step = 0
 
@@ -200,29 +206,38 @@ class ShardedModel:
         kn, g, k = self.kernels, self.world, self.cfg.factor_num
         packed = lines if isinstance(lines, PackedLines) else pack_lines(list(lines))
         if packed.text.device != self.device:
-            packed = packed.to(self.device, non_blocking=False)
-        p = kn.parse_unique(packed, self.cfg.vocabulary_size, self.cfg.hash_feature_id)
-        mark("parse_unique")
-        send_ids, pos, counts = kn.bucket(p["ori"], g)
-        recv_counts_t = torch.empty_like(counts)
-        dist.all_to_all_single(recv_counts_t, counts, group=self.group)
-        send_counts, recv_counts = counts.tolist(), recv_counts_t.tolist()
-        mark("bucket_counts")
-        want_ids = _exchange(send_ids, send_counts, recv_counts, self.group)      # ids other ranks want from me
+            packed = packed.to(self.device, non_blocking=True)
+        p = kn.parse_unique_bucket(packed, self.cfg.vocabulary_size, self.cfg.hash_feature_id, g)
+        mark("parse_unique_bucket")
+        # every rank learns every rank's sizes and parse status in one small collective + one D2H copy
+        info_all = torch.empty(g * p["info"].numel(), dtype=torch.int64, device=self.device)
+        dist.all_gather_into_tensor(info_all, p["info"], group=self.group)
+        host = info_all.cpu().view(g, -1)
+        mark("sizes")
+        for r in range(g):   # a parse error anywhere aborts the step on every rank, before any update
+            first = int(host[r, INFO_ERROR]) & 0xFFFFFFFFFFFFFFFF
+            if first != _lib.NO_ERROR:
+                line = packed.line(first >> 3) if r == self.rank else "<rank %d, line %d>" % (r, first >> 3)
+                raise FmParseError(first & 7, first >> 3, line)
+        nnz, n_unique = int(host[self.rank, INFO_NNZ]), int(host[self.rank, INFO_UNIQUE])
+        send_counts = host[self.rank, INFO_COUNTS:].tolist()
+        recv_counts = host[:, INFO_COUNTS + self.rank].tolist()
+        want_ids = _exchange(p["send_ids"][:n_unique], send_counts, recv_counts, self.group)  # ids asked of me
         mark("xchg_ids")
-        own_rows = kn.local_rows(want_ids, g)                                     # my rows the others asked for
+        own_rows = kn.local_rows(want_ids, g)
         rows_out = kn.lookup(self.table, own_rows, k)
         mark("lookup")
-        rows_in = _exchange(rows_out, recv_counts, send_counts, self.group)       # my distinct ids' rows, bucket order
+        rows_in = _exchange(rows_out, recv_counts, send_counts, self.group)   # my distinct ids' rows, owner order
         mark("xchg_rows")
-        slot64, slot32 = kn.remap(p["local"], pos)
-        p.update(send_counts=send_counts, recv_counts=recv_counts, own_rows=own_rows, rows_in=rows_in,
-                 slot64=slot64, slot32=slot32, n_lines=packed.n_lines)
+        p.update(send_counts=send_counts, recv_counts=recv_counts, own_rows=own_rows, rows_in=rows_in, nnz=nnz,
+                 n_unique=n_unique, n_lines=packed.n_lines, vals=p["vals"][:nnz], slot64=p["slot64"][:nnz],
+                 slot32=p["slot32"][:nnz])
         return p
 
-    def train_step(self, lines, weights=None, global_batch=None, mark=lambda name: None):
-        """lines / weights: this rank's slice of the global batch.  Returns the GLOBAL mean loss."""
-        kn, g, k, cfg = self.kernels, self.world, self.cfg.factor_num, self.cfg
+    def train_step_async(self, lines, weights=None, global_batch=None, mark=lambda name: None):
+        """lines / weights: this rank's slice of the global batch.  Returns a device tensor
+        [global mean loss, global reg_score]; nothing after the size exchange synchronises."""
+        kn, k, cfg = self.kernels, self.cfg.factor_num, self.cfg
         p = self._route(lines, mark)
         if global_batch is None:
             nb = torch.tensor([p["n_lines"]], dtype=torch.int64, device=self.device)
@@ -232,8 +247,7 @@ class ShardedModel:
             weights = torch.as_tensor(weights, dtype=torch.float32)
         if weights is not None:
             weights = weights.to(self.device)
-        gld = kn.gacc_ld(k)
-        gacc = torch.zeros(p["ori"].numel(), gld, dtype=torch.float32, device=self.device)
+        gacc = torch.zeros(p["n_unique"], kn.gacc_ld(k), dtype=torch.float32, device=self.device)
         pred, scal = kn.score_scatter(p["slot64"], p["slot32"], p["vals"], p["poses"], p["labels"], weights, k,
                                       p["rows_in"], cfg.factor_lambda, cfg.bias_lambda, cfg.loss_type, global_batch,
                                       gacc)
@@ -244,11 +258,16 @@ class ShardedModel:
         kn.adagrad_claim(self.table, self.accum, p["own_rows"], k, self.gtab, cfg.learning_rate,
                          cfg.factor_lambda, cfg.bias_lambda, 1.0 / cfg.batch_size)
         mark("update")
-        dist.all_reduce(scal, group=self.group)
+        out = scal.clone()
+        dist.all_reduce(out, group=self.group)
         self.global_step += 1
-        self.last = dict(pred=pred, reg=scal[1], n_unique=p["ori"].numel(), nnz=p["ids"].numel(),
+        self.last = dict(pred=pred, n_unique=p["n_unique"], nnz=p["nnz"],
                          sent_rows=sum(p["send_counts"]) - p["send_counts"][self.rank])
-        return float(scal[0].item())
+        return out
+
+    def train_step(self, lines, weights=None, global_batch=None, mark=lambda name: None):
+        """Returns the GLOBAL mean loss as a python float."""
+        return float(self.train_step_async(lines, weights, global_batch, mark)[0].item())
 
     def predict(self, lines):
         kn, k = self.kernels, self.cfg.factor_num

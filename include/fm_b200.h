@@ -246,8 +246,9 @@ int fm_fused_adagrad_claim(float* table, float* accum, int64_t table_ld, const i
  *   accumulator rows from several ranks for one id are summed before the Adagrad square);
  *   width and both strides are multiples of 4 floats. */
 size_t fm_shard_bucket_workspace(int64_t n, int64_t n_ranks);
-int fm_shard_bucket(const int64_t* ids, int64_t n, int64_t n_ranks, int64_t* send_ids, int32_t* pos,
-                    int64_t* counts, void* workspace, size_t workspace_bytes, void* stream);
+int fm_shard_bucket(const int64_t* ids, int64_t n, const int64_t* n_dev, int64_t n_ranks,
+                    int64_t* send_ids, int32_t* pos, int64_t* counts, void* workspace,
+                    size_t workspace_bytes, void* stream);
 int fm_shard_remap(const int32_t* local_ids, int64_t n, const int64_t* n_dev, const int32_t* pos,
                    int64_t* slot64, int32_t* slot32, void* stream);
 int fm_shard_local_rows(const int64_t* ids, int64_t n, int64_t n_ranks, int64_t* rows, void* stream);

@@ -16,28 +16,26 @@ def _t(a, dtype=None):
 
 
 class OracleShardKernels:
-    def parse_unique(self, packed, vocab, hashed):
+    def parse_unique_bucket(self, packed, vocab, hashed, n_ranks):
         text, off = packed.text.numpy(), packed.offsets.numpy()
-        labels, sizes, ids, vals = O.parse(text, off, vocab, hashed)
+        rc = O.parse(text, off, vocab, hashed, raise_on_error=False)
+        if len(rc) == 2:   # (kind, line): report it the way the device status word does
+            kind, line = rc
+            info = np.zeros(3 + n_ranks, np.int64)
+            info[2] = (line << 3) | kind
+            z = lambda dt: torch.zeros(0, dtype=dt)
+            return dict(labels=z(torch.float32), poses=z(torch.int32), vals=z(torch.float32), send_ids=z(torch.int64),
+                        slot64=z(torch.int64), slot32=z(torch.int32), info=_t(info))
+        labels, sizes, ids, vals = rc
         ori, local = O.unique(ids)
-        return dict(labels=_t(labels), poses=_t(O.poses(sizes)), ids=_t(ids), vals=_t(vals), ori=_t(ori),
-                    local=_t(local))
-
-    def unique(self, ids):
-        ori, local = O.unique(ids.numpy())
-        return _t(ori), _t(local)
-
-    def bucket(self, ori, n_ranks):
-        ids = ori.numpy()
-        owner = (ids % n_ranks).astype(np.int64)
-        perm = np.argsort(owner, kind="stable")
-        pos = np.empty(ids.size, np.int32)
-        pos[perm] = np.arange(ids.size, dtype=np.int32)
-        return _t(ids[perm]), _t(pos), _t(np.bincount(owner, minlength=n_ranks).astype(np.int64))
-
-    def remap(self, local, pos):
-        s = pos.numpy()[local.numpy()]
-        return _t(s.astype(np.int64)), _t(s.astype(np.int32))
+        owner = (ori % n_ranks).astype(np.int64)
+        perm = np.argsort(owner, kind="stable")                 # stable counting sort by owner
+        pos = np.empty(ori.size, np.int32)
+        pos[perm] = np.arange(ori.size, dtype=np.int32)
+        slot = pos[local]
+        info = np.concatenate([[ids.size, ori.size, -1], np.bincount(owner, minlength=n_ranks)]).astype(np.int64)
+        return dict(labels=_t(labels), poses=_t(O.poses(sizes)), vals=_t(vals), send_ids=_t(ori[perm]),
+                    slot64=_t(slot.astype(np.int64)), slot32=_t(slot.astype(np.int32)), info=_t(info))
 
     def score_scatter(self, slot64, slot32, vals, poses, labels, weights, k, rows, lf, lb, loss_type, global_batch,
                       gacc):
