@@ -180,7 +180,8 @@ def workload_config(args, n_gpus, batch):
             "vocabulary_size": CFG["vocab"], "distinct_batches": args.batches,
             "l2_policy": "inputs larger than L2: %d distinct text batches (~37 MB each) + random rows of a "
                          "1.3 GB table / accumulator per step" % args.batches,
-            "parallelism": "single GPU" if n_gpus == 1 else "vocab-sharded x%d (id %% G), NCCL all-to-all" % n_gpus}
+            "parallelism": "single GPU" if n_gpus == 1 else "vocab-sharded x%d (id %% G), %s" % (
+                n_gpus, "NVLink peer loads + atomics" if args.shard_mode == "peer" else "NCCL all-to-all")}
 
 
 def run_ours(args):
@@ -334,6 +335,9 @@ def main():
                     help="claim: no unique, table-shaped accumulators (default); fused: unique + compact "
                          "accumulators; composed: the reference's op-by-op chain")
     ap.add_argument("--layout", default="split", choices=["split", "interleaved"])
+    ap.add_argument("--shard-mode", default="peer", choices=["peer", "exchange"],
+                    help="N > 1: peer = rows and gradients move by NVLink loads / atomics inside the kernels; "
+                         "exchange = NCCL all-to-all of ids, rows and accumulator rows")
     ap.add_argument("--ld", type=int, default=None, help="experiment: table row stride in floats")
     ap.add_argument("--l2-fetch", type=int, default=0, help="experiment: cudaLimitMaxL2FetchGranularity")
     args = ap.parse_args()

@@ -20,7 +20,7 @@ def run_sharded(args, cfg, workload_config):
     from bench import METRIC, UNIT, ClockSampler, algorithmic_bytes, measured_peak_gbs
     from fast_tffm_b200.fm_model import Model
     from fast_tffm_b200.fm_ops import PackedLines
-    from fast_tffm_b200.sharded import ShardedModel
+    from fast_tffm_b200.sharded import PeerShardedModel, ShardedModel
 
     world, rank = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"])
     local_rank = int(os.environ.get("LOCAL_RANK", rank))
@@ -32,7 +32,9 @@ def run_sharded(args, cfg, workload_config):
                   loss_type=cfg["loss_type"], learning_rate=cfg["learning_rate"],
                   adagrad_init_accumulator=cfg["init_acc"], factor_lambda=cfg["factor_lambda"],
                   bias_lambda=cfg["bias_lambda"])
-    m = ShardedModel(model, device=dev, max_nnz_per_line=cfg["nnz_per_line"]).build(seed=0)
+    peer = args.shard_mode == "peer"
+    cls = PeerShardedModel if peer else ShardedModel
+    m = cls(model, device=dev, max_nnz_per_line=cfg["nnz_per_line"]).build(seed=0)
     host, devb = [], []
     for i in range(args.batches):
         text, off, _ = bench_data.criteo_batch(b, 1000 * (rank + 1) + i, args.dist)
@@ -67,6 +69,9 @@ def run_sharded(args, cfg, workload_config):
         dist.barrier()
         ms = torch.tensor([t0.elapsed_time(t1)], device=dev)
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        if peer:
+            assert int(loss[1].item()) == -1, "parse error in the benchmark data"
+            loss = loss[0]
         return float(ms.item()), float(loss[0].item())
 
     for s in range(args.warmup):
@@ -81,7 +86,13 @@ def run_sharded(args, cfg, workload_config):
             stage_ms[name] = stage_ms.get(name, 0.0) + e0.elapsed_time(e1) / len(stage_events)
     e2e_ms, _ = timed(host, args.steps, args.warmup)            # host buffers: H2D of the text inside the region
 
-    stats = torch.tensor([m.last["nnz"], m.last["n_unique"], m.last["sent_rows"]], dtype=torch.float64, device=dev)
+    if peer:
+        st = m.last["status"].cpu()
+        nnz_local = int(st[1])
+        remote = nnz_local * (world - 1) / world
+        stats = torch.tensor([nnz_local, int(m.n_rows.item()), remote], dtype=torch.float64, device=dev)
+    else:
+        stats = torch.tensor([m.last["nnz"], m.last["n_unique"], m.last["sent_rows"]], dtype=torch.float64, device=dev)
     dist.all_reduce(stats)
     if rank == 0:
         nnz, nuniq, sent = (float(x) / world for x in stats.tolist())
@@ -91,7 +102,9 @@ def run_sharded(args, cfg, workload_config):
         step_s = total_ms / args.steps * 1e-3
         gld = (k + 3 + 3) // 4 * 4
         ld = (k + 1 + 3) // 4 * 4
-        xbytes = sent * (8 + 4 * ld + 4 * gld)                  # per rank per direction per step
+        # per rank per step over NVLink: exchange mode moves id + row + accumulator row per remote distinct id
+        # each way; peer mode reads a row and pushes an accumulator row per remote occurrence
+        xbytes = sent * (8 + 4 * ld + 4 * gld)
         line = {
             "metric": METRIC, "value": args.steps * b * world / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
@@ -107,7 +120,7 @@ def run_sharded(args, cfg, workload_config):
             "e2e": {"value": args.steps * b * world / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": int(host[0].text.numel() + host[0].offsets.numel() * 8) * world,
                     "d2h_bytes_per_step": 8 * (3 + world) * world * world, "ms_per_step": e2e_ms / args.steps},
-            "gpu_launches": 20 * args.steps,
+            "gpu_launches": (9 if peer else 20) * args.steps, "shard_mode": args.shard_mode,
             "stage_ms_rank0": {k_: round(v, 4) for k_, v in stage_ms.items()},
             "clocks": clocks, "final_loss": loss, "nnz_per_rank": nnz, "unique_per_rank": nuniq,
         }

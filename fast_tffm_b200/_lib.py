@@ -48,7 +48,11 @@ _SIGNATURES = {
     "fm_fused_score_scatter": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _i64, _f32, _f32, _i32, _i64,
                                          _vp, _vp, _vp, _vp, _i64, _vp, _vp, _sz, _vp]),
     "fm_fused_adagrad_claim": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _f32, _f32, _f32, _f32, _vp,
-                                         _vp]),
+                                         _i32, _vp]),
+    "fm_peer_score_scatter": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _i64, _vp, _f32, _f32,
+                                        _i32, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "fm_peer_touched_workspace": (_sz, [_i64]),
+    "fm_peer_touched_rows": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _vp, _sz, _vp]),
     "fm_shard_bucket_workspace": (_sz, [_i64, _i64]),
     "fm_shard_bucket": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
     "fm_shard_remap": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp]),

@@ -28,6 +28,7 @@
 // are zero.  Strides may be larger than the rows (e.g. weight, Adagrad and gradient
 // accumulator rows of one id interleaved in one allocation).
 #include "fm_common.cuh"
+#include "fm_scan.cuh"
 
 namespace fm {
 namespace {
@@ -39,6 +40,29 @@ __device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpre
 
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// sys-scope flavour for accumulator rows in a peer GPU's memory (NVLink atomics)
+__device__ __forceinline__ void red_add_v4_sys(float* p, float a, float b, float c, float d) {
+  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+__device__ __forceinline__ void red_or_sys(unsigned* p, unsigned v) {
+  asm volatile("red.relaxed.sys.global.or.b32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// The table sharded over the GPUs of one NVLink domain: rank id % n owns row id / n.  Every rank's
+// shard is mapped into this process, so a row is one pointer away wherever it lives.
+constexpr int kMaxPeers = 16;
+struct PeerPtrs {
+  const float* table[kMaxPeers];   // shard base of every rank
+  float* gtab[kMaxPeers];          // gradient accumulator rows beside them
+  unsigned* touched[kMaxPeers];    // bitmap: bit r set <=> row r of that shard got a contribution
+  int n;
+};
+__device__ __forceinline__ void split_id(int64_t id, int n, int* owner, int64_t* row) {
+  if ((uint64_t)id >> 32) { *owner = (int)((uint64_t)id % (uint64_t)n); *row = (int64_t)((uint64_t)id / (uint64_t)n); }
+  else { const unsigned u = (unsigned)id; *owner = (int)(u % (unsigned)n); *row = (int64_t)(u / (unsigned)n); }
 }
 
 template <int LPR>
@@ -55,14 +79,17 @@ __device__ __forceinline__ float sum_in_group(float v) {  // over the LPR lanes 
 }
 
 // LPR lanes share a row; lane c owns float4 chunks c, c + LPR, ... (T of them).
-template <int LPR, int T>
+// PEER: rows and accumulator rows are addressed through `peers` (id -> owner shard) instead
+// of table / gacc; reads and vector atomics then travel over NVLink where the owner is remote.
+template <int LPR, int T, bool PEER>
 __global__ void __launch_bounds__(kWarps * 32)
 fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __restrict__ local,
                            const float* __restrict__ vals, const int32_t* __restrict__ poses,
                            const float* __restrict__ labels, const float* __restrict__ weights, int64_t batch,
                            int K, const float* __restrict__ table, int64_t ld, float lam_f, float lam_b,
                            int loss_kind, float inv_batch, float* __restrict__ pred, float* __restrict__ gacc, int64_t gacc_ld,
-                           float* __restrict__ partials, const unsigned long long* __restrict__ guard) {
+                           float* __restrict__ partials, const unsigned long long* __restrict__ guard,
+                           const PeerPtrs peers) {
   constexpr int RPW = 32 / LPR;
   __shared__ float s_loss[kWarps], s_reg[kWarps];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -81,21 +108,30 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
     // ---- pass A: gather the rows once ------------------------------------------
     for (int base = start; base < end; base += 32) {
       const int j = base + lane;
-      const int64_t my_off = j < end ? ids[j] * ld : 0;
+      unsigned long long my_row = (unsigned long long)table;
+      if (j < end) {
+        if (PEER) {
+          int owner; int64_t row;
+          split_id(ids[j], peers.n, &owner, &row);
+          my_row = (unsigned long long)(peers.table[owner] + row * ld);
+        } else {
+          my_row = (unsigned long long)(table + ids[j] * ld);
+        }
+      }
       const float my_x = j < end ? vals[j] : 0.f;
       const int rows_here = min(32, end - base);
 #pragma unroll
       for (int s = 0; s < LPR; ++s) {
         const int jj = s * RPW + r;
         if (s * RPW >= rows_here) break;  // warp-uniform
-        const int64_t off = __shfl_sync(kFull, my_off, jj);
+        const float* rowp = reinterpret_cast<const float*>(__shfl_sync(kFull, my_row, jj));
         const float x = __shfl_sync(kFull, my_x, jj);
         if (jj < rows_here) {
 #pragma unroll
           for (int t = 0; t < T; ++t) {
             const int chunk = c + t * LPR;
             if (chunk < vc_table) {
-              float4 v = ldg4(table + off + 4 * chunk);
+              float4 v = ldg4(rowp + 4 * chunk);
               if (chunk == 0) {  // column 0 is the bias
                 bias_dot = fmaf(x, v.x, bias_dot);
                 bias_sq = fmaf(v.x, v.x, bias_sq);
@@ -147,18 +183,27 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
     // ---- pass B: scatter {C, B_k, D, cnt} to the accumulator rows ---------------------
     for (int base = start; base < end; base += 32) {
       const int j = base + lane;
-      const int64_t my_u = j < end ? (local ? (int64_t)local[j] : ids[j]) : 0;
+      unsigned long long my_arow = (unsigned long long)gacc;
+      if (j < end) {
+        if (PEER) {
+          int owner; int64_t row;
+          split_id(ids[j], peers.n, &owner, &row);
+          my_arow = (unsigned long long)(peers.gtab[owner] + row * gacc_ld);
+          red_or_sys(peers.touched[owner] + (row >> 5), 1u << (row & 31));
+        } else {
+          my_arow = (unsigned long long)(gacc + (local ? (int64_t)local[j] : ids[j]) * gacc_ld);
+        }
+      }
       const float my_x = j < end ? vals[j] : 0.f;
       const int rows_here = min(32, end - base);
 #pragma unroll
       for (int s = 0; s < LPR; ++s) {
         const int jj = s * RPW + r;
         if (s * RPW >= rows_here) break;
-        const int64_t u = __shfl_sync(kFull, my_u, jj);
+        float* arow = reinterpret_cast<float*>(__shfl_sync(kFull, my_arow, jj));
         const float x = __shfl_sync(kFull, my_x, jj);
         if (jj < rows_here) {
           const float pgx = pg * x;
-          float* arow = gacc + u * gacc_ld;
 #pragma unroll
           for (int t = 0; t < T; ++t) {
             const int chunk = c + t * LPR;
@@ -173,7 +218,10 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
                 else if (cc == K + 2) o[e] = 1.0f;       // cnt
                 else if (cc > K + 2) o[e] = 0.f;
               }
-              if (col <= K + 2) red_add_v4(arow + col, o[0], o[1], o[2], o[3]);
+              if (col <= K + 2) {
+                if (PEER) red_add_v4_sys(arow + col, o[0], o[1], o[2], o[3]);
+                else red_add_v4(arow + col, o[0], o[1], o[2], o[3]);
+              }
             }
           }
         }
@@ -190,6 +238,7 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
     partials[blockIdx.x] = a;
     partials[gridDim.x + blockIdx.x] = b;
   }
+  if (PEER) __threadfence_system();  // remote atomics are performed before the kernel is seen as done
 }
 
 // two fixed-order sums (loss, reg) of `n` per-block partials each
@@ -282,8 +331,9 @@ __global__ void __launch_bounds__(256)
 fused_adagrad_claim_kernel(float* __restrict__ table, float* __restrict__ accum, int64_t ld,
                            const int64_t* __restrict__ rows, int64_t n_max, const int64_t* __restrict__ n_dev, int K,
                            float* __restrict__ gtab, int64_t gtab_ld, float lr, float rf, float rb,
-                           const unsigned long long* __restrict__ guard) {
-  if (guard && *guard != kNoError) return;
+                           const unsigned long long* __restrict__ guard, int discard_on_guard) {
+  const bool tripped = guard && *guard != kNoError;
+  if (tripped && !discard_on_guard) return;
   const int64_t n = n_dev ? min(*n_dev, n_max) : n_max;
   const int c = threadIdx.x % LPR;
   const int64_t groups_per_block = blockDim.x / LPR;
@@ -337,7 +387,7 @@ fused_adagrad_claim_kernel(float* __restrict__ table, float* __restrict__ accum,
 #pragma unroll
     for (int t = 0; t < T; ++t) {
       const int chunk = c + t * LPR;
-      if (chunk < vc_table) {
+      if (chunk < vc_table && !tripped) {  // tripped: the step is void, only throw the sums away
         const float av[4] = {a[t].x, a[t].y, a[t].z, a[t].w};
         float wv[4] = {w[t].x, w[t].y, w[t].z, w[t].w};
         float hv[4] = {h[t].x, h[t].y, h[t].z, h[t].w};
@@ -358,6 +408,24 @@ fused_adagrad_claim_kernel(float* __restrict__ table, float* __restrict__ accum,
     }
   }
 }
+
+// bitmap of touched rows -> list of row numbers (and the bitmap is cleared on the way)
+struct TouchedIn {
+  unsigned* bits; int64_t n_words;
+  __device__ int64_t count() const { return n_words; }
+  __device__ long long operator()(int64_t w) const { return __popc(bits[w]); }
+};
+struct TouchedOut {
+  unsigned* bits; int64_t* rows; int64_t capacity; int64_t* n_out;
+  __device__ void operator()(int64_t w, long long excl, long long cnt) const {
+    if (cnt == 0) return;
+    unsigned m = bits[w];
+    bits[w] = 0u;
+    for (long long r = excl; m; m &= m - 1, ++r)
+      if (r < capacity) rows[r] = w * 32 + (__ffs(m) - 1);
+  }
+  __device__ void total(long long t) const { *n_out = t; }
+};
 
 struct Shape { int lpr, t; };
 static inline bool pick_shape(int64_t chunks, Shape* s) {
@@ -427,10 +495,10 @@ FM_EXPORT int fm_fused_score_scatter(const int64_t* feature_ids, const int32_t* 
   const int64_t denom = loss_batch > 0 ? loss_batch : batch;
   const float inv_batch = denom > 0 ? 1.0f / (float)denom : 0.f;
 #define CALL(LPR, T)                                                                                              \
-  fused_score_scatter_kernel<LPR, T><<<blocks, kWarps * 32, 0, stream>>>(                                         \
+  fused_score_scatter_kernel<LPR, T, false><<<blocks, kWarps * 32, 0, stream>>>(                                  \
       feature_ids, local_ids, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, table, table_ld, \
-      factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, gacc, gacc_ld, partials,                                 \
-      reinterpret_cast<const unsigned long long*>(guard))
+      factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, gacc, gacc_ld, partials,                      \
+      reinterpret_cast<const unsigned long long*>(guard), PeerPtrs())
   FM_DISPATCH_SHAPE(sh, CALL)
 #undef CALL
   FM_LAUNCH_CHECK();
@@ -470,7 +538,7 @@ FM_EXPORT int fm_fused_adagrad(float* table, float* accum, int64_t table_ld, con
 FM_EXPORT int fm_fused_adagrad_claim(float* table, float* accum, int64_t table_ld, const int64_t* rows, int64_t n,
                                      const int64_t* n_dev, int64_t factor_num, float* gtab, int64_t gtab_ld,
                                      float learning_rate, float factor_lambda, float bias_lambda, float reg_grad,
-                                     const uint64_t* guard, void* stream_) {
+                                     const uint64_t* guard, int discard_on_guard, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   FM_REQUIRE(n >= 0 && factor_num >= 0, "fm_fused_adagrad_claim: bad shape");
   FM_REQUIRE(table_ld >= factor_num + 1 && table_ld % 4 == 0, "fm_fused_adagrad_claim: table_ld must be a multiple of 4 and >= K+1");
@@ -487,9 +555,86 @@ FM_EXPORT int fm_fused_adagrad_claim(float* table, float* accum, int64_t table_l
 #define CALL(LPR, T)                                                                                      \
   fused_adagrad_claim_kernel<LPR, T><<<(unsigned)blocks, 256, 0, stream>>>(                               \
       table, accum, table_ld, rows, n, n_dev, (int)factor_num, gtab, gtab_ld, learning_rate,              \
-      reg_grad * factor_lambda, reg_grad * bias_lambda, reinterpret_cast<const unsigned long long*>(guard))
+      reg_grad * factor_lambda, reg_grad * bias_lambda, reinterpret_cast<const unsigned long long*>(guard),        \
+      discard_on_guard)
   FM_DISPATCH_SHAPE(sh, CALL)
 #undef CALL
+  FM_LAUNCH_CHECK();
+  return FM_OK;
+}
+
+// ---- the same pair over a table sharded across the GPUs of one NVLink domain ----
+FM_EXPORT int fm_peer_score_scatter(const int64_t* feature_ids, const float* feature_vals, const int32_t* feature_poses,
+                                    const float* labels, const float* weights, int64_t batch, int64_t factor_num,
+                                    int64_t n_ranks, const void* const* table_bases, int64_t table_ld,
+                                    void* const* gtab_bases, int64_t gtab_ld, void* const* touched_bases,
+                                    float factor_lambda, float bias_lambda, int loss_kind, int64_t loss_batch,
+                                    float* pred_score, float* loss, float* reg_score, const uint64_t* guard,
+                                    void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  FM_REQUIRE(batch >= 0 && factor_num >= 0, "fm_peer_score_scatter: bad shape");
+  if (n_ranks < 1 || n_ranks > kMaxPeers) return fm_fail(FM_E_LIMIT, "fm_peer_score_scatter: 1..%d ranks", kMaxPeers);
+  FM_REQUIRE(table_ld >= factor_num + 1 && table_ld % 4 == 0, "fm_peer_score_scatter: table_ld must be a multiple of 4 and >= K+1");
+  FM_REQUIRE(loss_kind == FM_LOSS_LOGISTIC || loss_kind == FM_LOSS_MSE, "fm_peer_score_scatter: unknown loss kind");
+  FM_REQUIRE(table_bases && loss && reg_score && workspace, "fm_peer_score_scatter: null pointer");
+  FM_REQUIRE(batch == 0 || (feature_ids && feature_vals && feature_poses && pred_score), "fm_peer_score_scatter: null pointer");
+  const bool training = labels != nullptr;
+  FM_REQUIRE(!training || (gtab_bases && touched_bases && gtab_ld >= factor_num + 3 && gtab_ld % 4 == 0),
+             "fm_peer_score_scatter: training needs gtab_bases, touched_bases and gtab_ld >= K+3 (multiple of 4)");
+  if (workspace_bytes < fm_fused_workspace(batch))
+    return fm_fail(FM_E_WORKSPACE, "fm_peer_score_scatter: workspace %zu < %zu", workspace_bytes, fm_fused_workspace(batch));
+  PeerPtrs peers;
+  peers.n = (int)n_ranks;
+  for (int r = 0; r < kMaxPeers; ++r) {
+    const bool in = r < n_ranks;
+    peers.table[r] = in ? static_cast<const float*>(table_bases[r]) : nullptr;
+    peers.gtab[r] = in && training ? static_cast<float*>(gtab_bases[r]) : nullptr;
+    peers.touched[r] = in && training ? static_cast<unsigned*>(touched_bases[r]) : nullptr;
+    if (in) {
+      FM_REQUIRE(peers.table[r] && ((uintptr_t)peers.table[r] & 15) == 0, "fm_peer_score_scatter: bad table base");
+      FM_REQUIRE(!training || (peers.gtab[r] && peers.touched[r] && ((uintptr_t)peers.gtab[r] & 15) == 0),
+                 "fm_peer_score_scatter: bad gtab / touched base");
+    }
+  }
+  Shape sh;
+  if (!pick_shape((factor_num + 6) / 4, &sh))
+    return fm_fail(FM_E_LIMIT, "fm_peer_score_scatter: factor_num %lld too large", (long long)factor_num);
+  const int blocks = fused_blocks(batch);
+  float* partials = reinterpret_cast<float*>(workspace);
+  const int64_t denom = loss_batch > 0 ? loss_batch : batch;
+  const float inv_batch = denom > 0 ? 1.0f / (float)denom : 0.f;
+  // gacc != NULL tells the kernel to scatter; the real targets come from `peers`
+  float* scatter_flag = training ? peers.gtab[0] : nullptr;
+#define CALL(LPR, T)                                                                                                \
+  fused_score_scatter_kernel<LPR, T, true><<<blocks, kWarps * 32, 0, stream>>>(                                     \
+      feature_ids, nullptr, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, peers.table[0],   \
+      table_ld, factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, scatter_flag, gtab_ld, partials,      \
+      reinterpret_cast<const unsigned long long*>(guard), peers)
+  FM_DISPATCH_SHAPE(sh, CALL)
+#undef CALL
+  FM_LAUNCH_CHECK();
+  reduce2_kernel<<<1, 256, 0, stream>>>(partials, blocks, inv_batch, loss, reg_score);
+  FM_LAUNCH_CHECK();
+  return FM_OK;
+}
+
+FM_EXPORT size_t fm_peer_touched_workspace(int64_t shard_rows) {
+  return scan_scratch_bytes((shard_rows + 31) / 32, 8);
+}
+
+FM_EXPORT int fm_peer_touched_rows(uint32_t* touched, int64_t shard_rows, int64_t* rows, int64_t capacity,
+                                   int64_t* n_rows, void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  FM_REQUIRE(shard_rows >= 0 && capacity >= 0, "fm_peer_touched_rows: bad size");
+  FM_REQUIRE(touched && n_rows && workspace && (capacity == 0 || rows), "fm_peer_touched_rows: null pointer");
+  const int64_t words = (shard_rows + 31) / 32;
+  if (workspace_bytes < scan_scratch_bytes(words, 8))
+    return fm_fail(FM_E_WORKSPACE, "fm_peer_touched_rows: workspace %zu < %zu", workspace_bytes, scan_scratch_bytes(words, 8));
+  FM_CUDA(cudaMemsetAsync(workspace, 0, scan_scratch_bytes(words, 8), stream));
+  TouchedIn in{touched, words};
+  TouchedOut out{touched, rows, capacity, n_rows};
+  const int64_t tiles = scan_tiles(words, 8);
+  scan_kernel<8><<<(unsigned)tiles, kScanThreads, 0, stream>>>(in, out, scan_scratch_at(workspace, words, 8), tiles);
   FM_LAUNCH_CHECK();
   return FM_OK;
 }

@@ -303,7 +303,7 @@ class Model(object):
             check(lib.fm_fused_adagrad_claim(
                 ptr(self.table), ptr(self.accum), tstride, ptr(b["ids"]), b["cap"], _off(b["status"], 1), k,
                 ptr(gtab), gtab.stride(0), self.learning_rate, self.factor_lambda, self.bias_lambda,
-                1.0 / self.batch_size, ptr(b["status"]), st), "fm_fused_adagrad_claim")
+                1.0 / self.batch_size, ptr(b["status"]), 0, st), "fm_fused_adagrad_claim")
             mark("adagrad")
             self.global_step += 1
             return b

@@ -142,7 +142,7 @@ class CudaShardKernels:
 
     def adagrad_claim(self, table, accum, rows, k, gtab, lr, lf, lb, reg_grad):
         check(self.lib.fm_fused_adagrad_claim(ptr(table), ptr(accum), table.stride(0), ptr(rows), rows.numel(), None,
-                                              k, ptr(gtab), gtab.stride(0), lr, lf, lb, reg_grad, None, stream()),
+                                              k, ptr(gtab), gtab.stride(0), lr, lf, lb, reg_grad, None, 0, stream()),
               "fm_fused_adagrad_claim")
 
     def gacc_ld(self, k):
@@ -273,3 +273,179 @@ class ShardedModel:
         kn, k = self.kernels, self.cfg.factor_num
         p = self._route(lines)
         return kn.score(p["slot32"], p["rows_in"], p["vals"], p["poses"], k)
+
+
+class PeerShardedModel:
+    """The sharded table over NVLink peer memory: no id, row or gradient exchange.
+
+    Every rank's table shard, gradient-accumulator shard and touched-row bitmap live in one
+    symmetric allocation that is mapped into every process of the box (torch symmetric
+    memory = CUDA VMM handles exchanged at start-up; plumbing).  A step is
+
+        parse (local)
+        fm_peer_score_scatter    rows read from whichever GPU owns them (LDG.128 over NVLink),
+                                 gradient sums red.add-ed into the owner's accumulator rows,
+                                 the rows' bits set in the owner's bitmap
+        all_reduce (1 word)      barrier + "did any rank fail to parse"
+        fm_peer_touched_rows     owner: bitmap -> list of touched rows
+        fm_fused_adagrad_claim   owner: Adagrad on those rows (or, if any rank failed, the
+                                 step is void everywhere: the sums are thrown away)
+        all_reduce (loss, reg)   also fences the update from the next step's reads
+
+    with no host synchronisation: train_step_async returns device tensors.  Results equal the
+    single-GPU step on the same global batch (tests/test_gpu_sharded.py).  There is no CPU form
+    of this path; the NCCL all-to-all form (ShardedModel) is the one that runs under gloo.
+    """
+
+    def __init__(self, model: Model, group=None, device=None, max_nnz_per_line=None):
+        self.cfg = model
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank = dist.get_rank(self.group)
+        self.world = dist.get_world_size(self.group)
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.max_nnz_per_line = max_nnz_per_line
+        self.lib = load()
+        self.global_step = 0
+        self._b = None
+
+    def rows_per_rank(self):
+        return self.cfg.vocabulary_size // self.world + 1
+
+    def build(self, init_table=None, seed=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        k, g, r, dev = self.cfg.factor_num, self.world, self.rank, self.device
+        rows = self.rows_per_rank()
+        self.ld, self.gld = _ld_for(k), _stride_for(int(self.lib.fm_fused_gacc_ld(k)))
+        n_table, n_gtab = rows * self.ld, rows * self.gld
+        n_bits = ((rows + 31) // 32 + 3) // 4 * 4
+        self._symm = symm_mem.empty(n_table + n_gtab + n_bits, dtype=torch.float32, device=dev)
+        self._hdl = symm_mem.rendezvous(self._symm, self.group)
+        self._symm.zero_()
+        self.table = self._symm[:n_table].view(rows, self.ld)
+        self.gtab = self._symm[n_table:n_table + n_gtab].view(rows, self.gld)
+        self.touched = self._symm[n_table + n_gtab:].view(torch.int32)
+        ptrs = [int(p) for p in self._hdl.buffer_ptrs]
+        arr = ctypes.c_void_p * g
+        self._table_bases = arr(*ptrs)
+        self._gtab_bases = arr(*[p + 4 * n_table for p in ptrs])
+        self._touched_bases = arr(*[p + 4 * (n_table + n_gtab) for p in ptrs])
+        if init_table is not None:
+            part = torch.as_tensor(init_table, dtype=torch.float32)[r::g, :k + 1]
+            self.table[:part.shape[0], :k + 1] = part.to(dev)
+        else:
+            gen = torch.Generator(device=dev)
+            gen.manual_seed((seed or 0) * 1000 + r)
+            self.table[:, :k + 1].uniform_(-self.cfg.init_value_range, self.cfg.init_value_range, generator=gen)
+        self.accum = torch.full((rows, self.ld), self.cfg.adagrad_init_accumulator, dtype=torch.float32, device=dev)
+        self.row_list = torch.empty(rows, dtype=torch.int64, device=dev)
+        self.n_rows = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.ws_touched = _lib.workspace(self.lib.fm_peer_touched_workspace(rows), dev)
+        torch.cuda.synchronize(dev)
+        dist.barrier(group=self.group)          # every shard is initialised before anyone reads it
+        return self
+
+    def gather_full_table(self):
+        k, g = self.cfg.factor_num, self.world
+        mine = self.table.contiguous()
+        parts = [torch.empty_like(mine) for _ in range(g)]
+        dist.all_gather(parts, mine, group=self.group)
+        full = torch.zeros(self.rows_per_rank() * g, k + 1, dtype=torch.float32, device=self.device)
+        for r in range(g):
+            full[r::g] = parts[r][:, :k + 1]
+        return full[:self.cfg.vocabulary_size]
+
+    def _buffers(self, n_lines, text_bytes):
+        cap = int(text_bytes // 2 + 1)
+        if self.max_nnz_per_line:
+            cap = min(cap, int(n_lines * self.max_nnz_per_line))
+        b = self._b
+        if b is not None and b["lines"] >= n_lines and b["cap"] >= cap:
+            return b
+        lib, dev = self.lib, self.device
+        lines, cap = max(n_lines, b["lines"] if b else 0), max(cap, b["cap"] if b else 0)
+        f32, i32, i64 = torch.float32, torch.int32, torch.int64
+        e = lambda n, dt: torch.empty(n, dtype=dt, device=dev)
+        self._b = b = dict(lines=lines, cap=cap, labels=e(lines, f32), sizes=e(lines, i32), poses=e(lines + 1, i32),
+                           ids=e(cap, i64), vals=e(cap, f32), status=torch.zeros(8, dtype=i64, device=dev),
+                           pred=e(lines, f32), scal=torch.zeros(2, dtype=f32, device=dev),
+                           ws_parse=_lib.workspace(lib.fm_parse_workspace(lines), dev),
+                           ws_fused=_lib.workspace(lib.fm_fused_workspace(lines), dev))
+        return b
+
+    def _parse(self, lines):
+        lib, st, cfg = self.lib, stream(), self.cfg
+        packed = lines if isinstance(lines, PackedLines) else pack_lines(list(lines))
+        if packed.text.device != self.device:
+            packed = packed.to(self.device, non_blocking=True)
+        b = self._buffers(packed.n_lines, packed.text.numel())
+        n_lines, hashed = packed.n_lines, int(cfg.hash_feature_id)
+        check(lib.fm_parse_count(ptr(packed.text), ptr(packed.offsets), n_lines, cfg.vocabulary_size, hashed,
+                                 ptr(b["sizes"]), ptr(b["poses"]), ptr(b["status"]), ptr(b["ws_parse"]),
+                                 b["ws_parse"].numel(), st), "fm_parse_count")
+        check(lib.fm_parse_fill(ptr(packed.text), ptr(packed.offsets), n_lines, cfg.vocabulary_size, hashed,
+                                ptr(b["poses"]), ptr(b["labels"]), ptr(b["ids"]), ptr(b["vals"]), b["cap"],
+                                ptr(b["status"]), ptr(b["ws_parse"]), b["ws_parse"].numel(), st), "fm_parse_fill")
+        return packed, b
+
+    def train_step_async(self, lines, weights=None, global_batch=None, mark=lambda name: None):
+        """Returns (scalars, flag): scalars = device f32 [global mean loss, global reg_score];
+        flag = device i64, -1 when every rank parsed its slice, else rank << 48 | line << 3 | kind
+        of a failing rank (the step was then void on every rank).  Nothing synchronises."""
+        lib, st, cfg, k, g = self.lib, stream(), self.cfg, self.cfg.factor_num, self.world
+        packed, b = self._parse(lines)
+        mark("parse")
+        if global_batch is None:
+            global_batch = packed.n_lines * g
+        if weights is not None and not isinstance(weights, torch.Tensor):
+            weights = torch.as_tensor(weights, dtype=torch.float32)
+        if weights is not None:
+            weights = weights.to(self.device)
+        check(lib.fm_peer_score_scatter(
+            ptr(b["ids"]), ptr(b["vals"]), ptr(b["poses"]), ptr(b["labels"]), ptr(weights), packed.n_lines, k, g,
+            self._table_bases, self.ld, self._gtab_bases, self.gld, self._touched_bases, cfg.factor_lambda,
+            cfg.bias_lambda, _lib.LOSS_KIND[cfg.loss_type], global_batch, ptr(b["pred"]), ptr(b["scal"]),
+            _at(b["scal"], 1), ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st),
+            "fm_peer_score_scatter")
+        mark("score_scatter")
+        # barrier that also tells every rank whether any rank's parse failed
+        err = b["status"][0:1]
+        flag = torch.where(err >= 0, err + (self.rank << 48), err)
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=self.group)
+        mark("barrier")
+        check(lib.fm_peer_touched_rows(ptr(self.touched), self.table.shape[0], ptr(self.row_list),
+                                       self.row_list.numel(), ptr(self.n_rows), ptr(self.ws_touched),
+                                       self.ws_touched.numel(), st), "fm_peer_touched_rows")
+        check(lib.fm_fused_adagrad_claim(ptr(self.table), ptr(self.accum), self.ld, ptr(self.row_list),
+                                         self.row_list.numel(), ptr(self.n_rows), k, ptr(self.gtab), self.gld,
+                                         cfg.learning_rate, cfg.factor_lambda, cfg.bias_lambda, 1.0 / cfg.batch_size,
+                                         ptr(flag), 1, st), "fm_fused_adagrad_claim")
+        mark("update")
+        out = b["scal"].clone()
+        dist.all_reduce(out, group=self.group)   # also: nobody reads rows of the next step before all updates ran
+        mark("allreduce_loss")
+        self.global_step += 1
+        self.last = dict(pred=b["pred"][:packed.n_lines], packed=packed, status=b["status"])
+        return out, flag
+
+    def train_step(self, lines, weights=None, global_batch=None):
+        out, flag = self.train_step_async(lines, weights, global_batch)
+        f = int(flag.item())
+        if f >= 0:
+            rank, first = f >> 48, f & ((1 << 48) - 1)
+            line = self.last["packed"].line(first >> 3) if rank == self.rank else "<rank %d, line %d>" % (rank, first >> 3)
+            raise FmParseError(first & 7, first >> 3, line)
+        return float(out[0].item())
+
+    def predict(self, lines):
+        lib, st, cfg, k, g = self.lib, stream(), self.cfg, self.cfg.factor_num, self.world
+        packed, b = self._parse(lines)
+        check(lib.fm_peer_score_scatter(
+            ptr(b["ids"]), ptr(b["vals"]), ptr(b["poses"]), None, None, packed.n_lines, k, g, self._table_bases,
+            self.ld, None, self.gld, None, cfg.factor_lambda, cfg.bias_lambda, 0, 0, ptr(b["pred"]), ptr(b["scal"]),
+            _at(b["scal"], 1), ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st),
+            "fm_peer_score_scatter")
+        host = b["status"].cpu()
+        first = int(host[0]) & 0xFFFFFFFFFFFFFFFF
+        if first != _lib.NO_ERROR:
+            raise FmParseError(first & 7, first >> 3, packed.line(first >> 3))
+        return b["pred"][:packed.n_lines].clone()

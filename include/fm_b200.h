@@ -229,11 +229,15 @@ int fm_fused_adagrad(float* table, float* accum, int64_t table_ld, const int64_t
  * to the accumulator row of the feature id itself (gacc[feature_ids[j]]: a table-shaped
  * accumulator), and fm_fused_adagrad_claim walks the n OCCURRENCES `rows` (= feature_ids):
  * the first lane group to swap a row's cnt column to zero applies the update, later
- * occurrences of that row see cnt == 0 and leave.  gtab[row] belongs to table[row]. */
+ * occurrences of that row see cnt == 0 and leave.  gtab[row] belongs to table[row].
+ * guard tripped: discard_on_guard == 0 -> the call is a no-op (`rows` may be garbage);
+ * != 0 -> `rows` is trusted, the accumulated sums of those rows are thrown away and the
+ * table is left alone (a step that some other rank voided). */
 int fm_fused_adagrad_claim(float* table, float* accum, int64_t table_ld, const int64_t* rows,
                            int64_t n, const int64_t* n_dev, int64_t factor_num, float* gtab,
                            int64_t gtab_ld, float learning_rate, float factor_lambda,
-                           float bias_lambda, float reg_grad, const uint64_t* guard, void* stream);
+                           float bias_lambda, float reg_grad, const uint64_t* guard,
+                           int discard_on_guard, void* stream);
 
 /* ---- D1: the parameter-server sharding of tffm/fm_model.py:269-291 + run_tffm.py:181-206,
  * as explicit routing around an all-to-all: rank id % n_ranks owns table row id / n_ranks ----
@@ -254,6 +258,34 @@ int fm_shard_remap(const int32_t* local_ids, int64_t n, const int64_t* n_dev, co
 int fm_shard_local_rows(const int64_t* ids, int64_t n, int64_t n_ranks, int64_t* rows, void* stream);
 int fm_shard_combine(const float* src_rows, int64_t src_ld, const int64_t* index, int64_t n,
                      int64_t width, float* dst_rows, int64_t dst_ld, void* stream);
+
+/* ---- D1 over NVLink peer memory: no id / row / gradient exchange at all ----
+ * Every rank's table shard, accumulator shard and touched-row bitmap are mapped into
+ * every process of the box (CUDA IPC / symmetric memory; the *_bases arrays are HOST arrays
+ * of n_ranks device pointers, entry r = rank r's shard as mapped here).  Rank id % n_ranks
+ * owns row id / n_ranks.
+ * fm_peer_score_scatter = fm_fused_score_scatter (table-shaped accumulators) with the row of
+ *   every occurrence read from its owner's HBM (128-bit loads over NVLink where remote), the
+ *   gradient sums added to the owner's accumulator row with system-scope vector atomics, and
+ *   the row's bit set in the owner's bitmap.  labels == NULL: scoring only.
+ * All ranks must have finished this call (a stream-ordered barrier, e.g. a tiny all_reduce)
+ *   before any owner runs the update:
+ * fm_peer_touched_rows: owner side; turns its bitmap into the list of touched rows
+ *   (rows[0..*n_rows), ascending) and clears the bitmap.  Feed the list to
+ *   fm_fused_adagrad_claim(table_shard, accum_shard, ..., rows, capacity, n_rows, ..., gtab_shard).
+ * A second barrier (the loss all_reduce serves) must separate the update from the next
+ *   step's reads. */
+int fm_peer_score_scatter(const int64_t* feature_ids, const float* feature_vals,
+                          const int32_t* feature_poses, const float* labels, const float* weights,
+                          int64_t batch, int64_t factor_num, int64_t n_ranks,
+                          const void* const* table_bases, int64_t table_ld,
+                          void* const* gtab_bases, int64_t gtab_ld, void* const* touched_bases,
+                          float factor_lambda, float bias_lambda, int loss_kind, int64_t loss_batch,
+                          float* pred_score, float* loss, float* reg_score, const uint64_t* guard,
+                          void* workspace, size_t workspace_bytes, void* stream);
+size_t fm_peer_touched_workspace(int64_t shard_rows);
+int fm_peer_touched_rows(uint32_t* touched, int64_t shard_rows, int64_t* rows, int64_t capacity,
+                         int64_t* n_rows, void* workspace, size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -6,7 +6,7 @@ import torch
 import torch.distributed as dist
 
 
-def run(rank, world, port, backend, lines, weights, cfg_kw, init, steps, out_dir):
+def run(rank, world, port, backend, lines, weights, cfg_kw, init, steps, out_dir, mode="exchange"):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     if backend == "nccl":
         torch.cuda.set_device(rank)
@@ -16,8 +16,11 @@ def run(rank, world, port, backend, lines, weights, cfg_kw, init, steps, out_dir
         device, kernels = torch.device("cpu"), OracleShardKernels()
     dist.init_process_group(backend, rank=rank, world_size=world)
     from fast_tffm_b200.fm_model import Model
-    from fast_tffm_b200.sharded import ShardedModel
-    m = ShardedModel(Model(**cfg_kw), kernels=kernels, device=device).build(init_table=init)
+    from fast_tffm_b200.sharded import PeerShardedModel, ShardedModel
+    if mode == "peer":
+        m = PeerShardedModel(Model(**cfg_kw), device=device).build(init_table=init)
+    else:
+        m = ShardedModel(Model(**cfg_kw), kernels=kernels, device=device).build(init_table=init)
     bs = cfg_kw["batch_size"]
     per = bs // world
     losses = []

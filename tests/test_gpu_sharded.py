@@ -11,8 +11,9 @@ from test_sharded_gloo import _reference
 pytestmark = pytest.mark.gpu
 
 
+@pytest.mark.parametrize("mode", ["exchange", "peer"])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_nccl_ranks_equal_single_process(criteo_lines, tmp_path, world):
+def test_nccl_ranks_equal_single_process(criteo_lines, tmp_path, world, mode):
     if torch.cuda.device_count() < world:
         pytest.skip("needs %d GPUs" % world)
     lines, weights = criteo_lines
@@ -21,7 +22,8 @@ def test_nccl_ranks_equal_single_process(criteo_lines, tmp_path, world):
                   bias_lambda=1e-3, learning_rate=0.05, adagrad_init_accumulator=0.1, loss_type="logistic")
     init = rng.uniform(-0.01, 0.01, (cfg_kw["vocabulary_size"], 17)).astype(np.float32)
     steps = 3
-    mp.spawn(shard_worker.run, args=(world, 29700 + world, "nccl", lines, weights, cfg_kw, init, steps, str(tmp_path)),
+    port = 29700 + world + (50 if mode == "peer" else 0)
+    mp.spawn(shard_worker.run, args=(world, port, "nccl", lines, weights, cfg_kw, init, steps, str(tmp_path), mode),
              nprocs=world, join=True)
     ref, exp_losses = _reference(lines, weights, cfg_kw, init, steps, world)
     np.testing.assert_allclose(np.load(tmp_path / "losses.npy"), exp_losses, rtol=1e-5)
