@@ -231,6 +231,8 @@ def run_ours(args):
     sampler = ClockSampler(local_rank)
     sampler.start()
     torch.cuda.synchronize()
+    ahead_on = fused == "claim" and not args.no_parse_ahead
+    ahead = m.parse_ahead(devb[0]) if ahead_on else None
     for s in range(args.steps):
         cursor = [0]
         ev[s][0].record()
@@ -238,7 +240,10 @@ def run_ours(args):
         def mark(name, evs=ev[s], cursor=cursor):
             cursor[0] += 1
             evs[cursor[0]].record()
-        bufs = m.train_step_async(devb[s % len(devb)], mark=mark, path=fused)
+        # the parse of batch s+1 runs on a side stream under the table kernels of batch s
+        nxt = m.parse_ahead(devb[(s + 1) % len(devb)]) if ahead_on else None
+        bufs = m.train_step_async(devb[s % len(devb)], mark=mark, path=fused, parsed=ahead)
+        ahead = nxt
     torch.cuda.synchronize()
     clocks = sampler.stop()
     total_ms = ev[0][0].elapsed_time(ev[-1][-1])
@@ -277,9 +282,11 @@ def run_ours(args):
     consumed = [torch.cuda.Event() for _ in range(2)]
 
     def e2e_loop(n_steps, base):
-        # double-buffered: the copy of batch s+1 runs on copy_stream while batch s computes
+        # three-deep pipeline: H2D copy of batch s+1 on copy_stream and its parse on the side stream
+        # while the table kernels of batch s run on the main stream
         main = torch.cuda.current_stream()
-        for s in range(n_steps):
+
+        def copy_in(s):
             slot = s % 2
             with torch.cuda.stream(copy_stream):
                 if s >= 2:
@@ -288,10 +295,32 @@ def run_ours(args):
                 stage_in[slot].text.copy_(hb.text, non_blocking=True)
                 stage_in[slot].offsets.copy_(hb.offsets, non_blocking=True)
                 ready[slot].record(copy_stream)
-            main.wait_event(ready[slot])
-            bb = m.train_step_async(stage_in[slot], path=fused)
-            consumed[slot].record(main)
-            pinned_status[base + s].copy_(bb["status"], non_blocking=True)   # loss + status back to the host
+
+        def parse_in(s):
+            h = m.parse_ahead(stage_in[s % 2], after=ready[s % 2])
+            consumed[s % 2] = h["done"]           # the text is not needed once it is parsed
+            return h
+
+        if ahead_on:
+            copy_in(0)
+            h = parse_in(0)
+        for s in range(n_steps):
+            slot = s % 2
+            if ahead_on:
+                h_next = None
+                if s + 1 < n_steps:
+                    copy_in(s + 1)
+                    h_next = parse_in(s + 1)
+                bb = m.train_step_async(stage_in[slot], path=fused, parsed=h)
+                pinned_status[base + s].copy_(bb["status_snapshot"], non_blocking=True)
+                h = h_next
+            else:
+                copy_in(s)
+                main.wait_event(ready[slot])
+                bb = m.train_step_async(stage_in[slot], path=fused)
+                consumed[slot] = torch.cuda.Event()
+                consumed[slot].record(main)
+                pinned_status[base + s].copy_(bb["status"], non_blocking=True)   # loss + status back to the host
 
     e2e_loop(args.warmup, 0)
     torch.cuda.synchronize()
@@ -315,7 +344,7 @@ def run_ours(args):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": KERNELS_PER_STEP[fused] * args.steps,
-        "path": fused, "layout": args.layout, "unique_per_step": n_unique,
+        "path": fused, "layout": args.layout, "unique_per_step": n_unique, "parse_ahead": ahead_on,
         "clocks": clocks,
         "final_loss": loss, "nnz_per_step": nnz,
     }
@@ -334,7 +363,9 @@ def main():
     ap.add_argument("--path", default="claim", choices=["claim", "fused", "composed"],
                     help="claim: no unique, table-shaped accumulators (default); fused: unique + compact "
                          "accumulators; composed: the reference's op-by-op chain")
-    ap.add_argument("--layout", default="split", choices=["split", "interleaved"])
+    ap.add_argument("--layout", default="interleaved", choices=["split", "interleaved"])
+    ap.add_argument("--no-parse-ahead", action="store_true",
+                    help="parse each batch inline instead of on a side stream under the previous batch's kernels")
     ap.add_argument("--shard-mode", default="peer", choices=["peer", "exchange"],
                     help="N > 1: peer = rows and gradients move by NVLink loads / atomics inside the kernels; "
                          "exchange = NCCL all-to-all of ids, rows and accumulator rows")

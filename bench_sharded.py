@@ -43,6 +43,7 @@ def run_sharded(args, cfg, workload_config):
         devb.append(PackedLines(ht.to(dev), ho.to(dev)))
 
     stage_events = []
+    ahead_on = peer and not args.no_parse_ahead
 
     def timed(batches, steps, base, stages=False):
         dist.barrier()
@@ -50,6 +51,7 @@ def run_sharded(args, cfg, workload_config):
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0.record()
         loss = None
+        ahead = m.parse_ahead(batches[base % len(batches)]) if ahead_on else None
         for s in range(steps):
             evs = []
 
@@ -59,8 +61,14 @@ def run_sharded(args, cfg, workload_config):
                 evs.append((name, e))
             if stages:
                 mark("start")
+            kw = {}
+            if ahead_on:   # parse of the next batch under this batch's NVLink-bound kernels
+                nxt = m.parse_ahead(batches[(base + s + 1) % len(batches)])
+                kw["parsed"] = ahead
             loss = m.train_step_async(batches[(base + s) % len(batches)], global_batch=b * world,
-                                      mark=mark if stages else (lambda name: None))
+                                      mark=mark if stages else (lambda name: None), **kw)
+            if ahead_on:
+                ahead = nxt
             if stages:
                 mark("allreduce_loss")
                 stage_events.append(evs)
@@ -93,7 +101,8 @@ def run_sharded(args, cfg, workload_config):
 
     def e2e_loop(n_steps, base):
         main = torch.cuda.current_stream()
-        for s in range(n_steps):
+
+        def copy_in(s):
             slot = s % 2
             with torch.cuda.stream(copy_stream):
                 if s >= 2:
@@ -102,9 +111,30 @@ def run_sharded(args, cfg, workload_config):
                 stage_in[slot].text.copy_(hb.text, non_blocking=True)
                 stage_in[slot].offsets.copy_(hb.offsets, non_blocking=True)
                 ready[slot].record(copy_stream)
-            main.wait_event(ready[slot])
-            out = m.train_step_async(stage_in[slot], global_batch=b * world)
-            consumed[slot].record(main)
+
+        def parse_in(s):
+            h = m.parse_ahead(stage_in[s % 2], after=ready[s % 2])
+            consumed[s % 2] = h["done"]
+            return h
+
+        if ahead_on:
+            copy_in(0)
+            h = parse_in(0)
+        for s in range(n_steps):
+            slot = s % 2
+            if ahead_on:
+                h_next = None
+                if s + 1 < n_steps:
+                    copy_in(s + 1)
+                    h_next = parse_in(s + 1)
+                out = m.train_step_async(stage_in[slot], global_batch=b * world, parsed=h)
+                h = h_next
+            else:
+                copy_in(s)
+                main.wait_event(ready[slot])
+                out = m.train_step_async(stage_in[slot], global_batch=b * world)
+                consumed[slot] = torch.cuda.Event()
+                consumed[slot].record(main)
             pinned_loss[base + s].copy_(out[0] if peer else out, non_blocking=True)
 
     e2e_loop(args.warmup, 0)
@@ -154,7 +184,7 @@ def run_sharded(args, cfg, workload_config):
             "e2e": {"value": args.steps * b * world / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": int(host[0].text.numel() + host[0].offsets.numel() * 8) * world,
                     "d2h_bytes_per_step": 8 * world, "ms_per_step": e2e_ms / args.steps},
-            "gpu_launches": (9 if peer else 20) * args.steps, "shard_mode": args.shard_mode,
+            "gpu_launches": (9 if peer else 20) * args.steps, "shard_mode": args.shard_mode, "parse_ahead": ahead_on,
             "stage_ms_rank0": {k_: round(v, 4) for k_, v in stage_ms.items()},
             "clocks": clocks, "final_loss": loss, "nnz_per_rank": nnz, "unique_per_rank": nuniq,
         }

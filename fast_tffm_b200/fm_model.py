@@ -81,6 +81,9 @@ class Model(object):
         self.table = self.accum = None
         self.global_step = 0
         self._bufs = None
+        self._slots = {}
+        self._ahead_slot = 0
+        self._parse_stream = None
 
     # ---- INI config, same sections / keys as tffm/fm_model.py:367-475 -----------------
     def _get_config(self, config_file, verbose=True):
@@ -193,21 +196,48 @@ class Model(object):
         else:
             self.accum = torch.full_like(self.table, self.adagrad_init_accumulator)
         self._bufs = None
+        self._slots = {}
         self._max_nnz_per_line = max_nnz_per_line
         return self
+
+    def parse_ahead(self, packed: PackedLines, after=None):
+        """Enqueues the parse of a device-resident batch on a side stream, into the buffer set the
+        current step is not using, and returns a handle for train_step_async(parsed=...).  The
+        parser is instruction-bound while the table kernels are memory-bound, so the two overlap."""
+        if self._parse_stream is None:
+            self._parse_stream = torch.cuda.Stream(device=self.device)
+        self._ahead_slot ^= 1
+        slot = self._ahead_slot
+        b = self._buffers(packed.n_lines, packed.text.numel(), slot=slot)
+        main = torch.cuda.current_stream(self.device)
+        side = self._parse_stream
+        side.wait_stream(main) if b.get("free") is None else side.wait_event(b["free"])
+        if after is not None:      # e.g. the event of the H2D copy that brings `packed` in
+            side.wait_event(after)
+        with torch.cuda.stream(side):
+            self._parse_unique(packed, b, unique=False)
+            done = torch.cuda.Event()
+            done.record(side)
+        return dict(b=b, done=done, packed=packed)
 
     def _gtab(self):
         if self.gtab is None:
             self.gtab = torch.zeros(self.vocabulary_size, self.gld, dtype=torch.float32, device=self.device)
         return self.gtab
 
-    def _buffers(self, n_lines, text_bytes):
-        """per-batch device buffers, allocated once and grown on demand"""
+    def _buffers(self, n_lines, text_bytes, slot=0):
+        """per-batch device buffers, allocated once and grown on demand (two sets: the second one
+        lets parse_ahead() fill the next batch while the current one trains)"""
+        b = self._buffers_one(self._slots.get(slot), n_lines, text_bytes)
+        self._slots[slot] = b
+        self._bufs = b          # the set used last (tests and callers read results from it)
+        return b
+
+    def _buffers_one(self, b, n_lines, text_bytes):
         # every feature costs at least two bytes (" x"), so nnz <= text_bytes / 2
         cap = int(text_bytes // 2 + 1)
         if self._max_nnz_per_line:
             cap = min(cap, int(n_lines * self._max_nnz_per_line))
-        b = self._bufs
         if b is not None and b["lines"] >= n_lines and b["cap"] >= cap:
             return b
         lib, dev = load(), self.device
@@ -233,7 +263,6 @@ class Model(object):
             ws_loss=_lib.workspace(lib.fm_loss_workspace(lines), dev),
         )
         b["scalars"] = b["status"][6:8].view(torch.float32)  # [loss, -, reg, -]
-        self._bufs = b
         return b
 
     def _parse_unique(self, packed, b, mark=_no_mark, unique=True):
@@ -275,7 +304,7 @@ class Model(object):
 
     PATHS = ("claim", "fused", "composed")
 
-    def train_step_async(self, packed: PackedLines, weights=None, mark=_no_mark, path="claim"):
+    def train_step_async(self, packed: PackedLines, weights=None, mark=_no_mark, path="claim", parsed=None):
         """One training step on a device-resident batch; enqueues only.  Returns the
         buffers dict: status[0] parse status word, status[1] nnz, status[4] n_unique,
         scalars[0] loss, scalars[2] reg.
@@ -286,13 +315,20 @@ class Model(object):
              "composed" the reference's op-by-op chain (unique, lookup, scorer, loss, grad, Adagrad)."""
         if path not in self.PATHS:
             raise ValueError("path must be one of %s" % (self.PATHS,))
-        b = self._buffers(packed.n_lines, packed.text.numel())
+        if parsed is not None and path != "claim":
+            raise ValueError("parse_ahead() feeds the claim path only")
+        b = parsed["b"] if parsed is not None else self._buffers(packed.n_lines, packed.text.numel())
         lib, st = load(), stream()
         n_lines, k = packed.n_lines, self.factor_num
         tstride = self.table.stride(0)
         if path == "claim":
             gtab = self._gtab()
-            self._parse_unique(packed, b, mark, unique=False)
+            if parsed is not None:
+                torch.cuda.current_stream(self.device).wait_event(parsed["done"])
+                mark("parse_count")
+                mark("parse_fill")
+            else:
+                self._parse_unique(packed, b, mark, unique=False)
             check(lib.fm_fused_score_scatter(
                 ptr(b["ids"]), None, ptr(b["vals"]), ptr(b["poses"]), ptr(b["labels"]), ptr(weights),
                 n_lines, k, ptr(self.table), tstride, self.factor_lambda, self.bias_lambda,
@@ -305,6 +341,10 @@ class Model(object):
                 ptr(gtab), gtab.stride(0), self.learning_rate, self.factor_lambda, self.bias_lambda,
                 1.0 / self.batch_size, ptr(b["status"]), 0, st), "fm_fused_adagrad_claim")
             mark("adagrad")
+            if parsed is not None:   # the buffer set may be refilled once this step is through with it
+                b["status_snapshot"] = b["status"].clone()
+                b["free"] = torch.cuda.Event()
+                b["free"].record(torch.cuda.current_stream(self.device))
             self.global_step += 1
             return b
         if path == "fused":

@@ -306,7 +306,9 @@ class PeerShardedModel:
         self.max_nnz_per_line = max_nnz_per_line
         self.lib = load()
         self.global_step = 0
-        self._b = None
+        self._slots = {}
+        self._ahead_slot = 0
+        self._parse_stream = None
 
     def rows_per_rank(self):
         return self.cfg.vocabulary_size // self.world + 1
@@ -354,30 +356,47 @@ class PeerShardedModel:
             full[r::g] = parts[r][:, :k + 1]
         return full[:self.cfg.vocabulary_size]
 
-    def _buffers(self, n_lines, text_bytes):
+    def _buffers(self, n_lines, text_bytes, slot=0):
         cap = int(text_bytes // 2 + 1)
         if self.max_nnz_per_line:
             cap = min(cap, int(n_lines * self.max_nnz_per_line))
-        b = self._b
+        b = self._slots.get(slot)
         if b is not None and b["lines"] >= n_lines and b["cap"] >= cap:
             return b
         lib, dev = self.lib, self.device
         lines, cap = max(n_lines, b["lines"] if b else 0), max(cap, b["cap"] if b else 0)
         f32, i32, i64 = torch.float32, torch.int32, torch.int64
         e = lambda n, dt: torch.empty(n, dtype=dt, device=dev)
-        self._b = b = dict(lines=lines, cap=cap, labels=e(lines, f32), sizes=e(lines, i32), poses=e(lines + 1, i32),
-                           ids=e(cap, i64), vals=e(cap, f32), status=torch.zeros(8, dtype=i64, device=dev),
-                           pred=e(lines, f32), scal=torch.zeros(2, dtype=f32, device=dev),
-                           ws_parse=_lib.workspace(lib.fm_parse_workspace(lines), dev),
-                           ws_fused=_lib.workspace(lib.fm_fused_workspace(lines), dev))
+        self._slots[slot] = b = dict(
+            lines=lines, cap=cap, labels=e(lines, f32), sizes=e(lines, i32), poses=e(lines + 1, i32),
+            ids=e(cap, i64), vals=e(cap, f32), status=torch.zeros(8, dtype=i64, device=dev),
+            pred=e(lines, f32), scal=torch.zeros(2, dtype=f32, device=dev),
+            ws_parse=_lib.workspace(lib.fm_parse_workspace(lines), dev),
+            ws_fused=_lib.workspace(lib.fm_fused_workspace(lines), dev))
         return b
 
-    def _parse(self, lines):
+    def parse_ahead(self, lines, after=None):
+        """parse of the next batch on a side stream (see Model.parse_ahead)"""
+        if self._parse_stream is None:
+            self._parse_stream = torch.cuda.Stream(device=self.device)
+        self._ahead_slot ^= 1
+        main, side = torch.cuda.current_stream(self.device), self._parse_stream
+        b = self._slots.get(self._ahead_slot)
+        side.wait_stream(main) if b is None or b.get("free") is None else side.wait_event(b["free"])
+        if after is not None:
+            side.wait_event(after)
+        with torch.cuda.stream(side):
+            packed, b = self._parse(lines, slot=self._ahead_slot)
+            done = torch.cuda.Event()
+            done.record(side)
+        return dict(b=b, packed=packed, done=done)
+
+    def _parse(self, lines, slot=0):
         lib, st, cfg = self.lib, stream(), self.cfg
         packed = lines if isinstance(lines, PackedLines) else pack_lines(list(lines))
         if packed.text.device != self.device:
             packed = packed.to(self.device, non_blocking=True)
-        b = self._buffers(packed.n_lines, packed.text.numel())
+        b = self._buffers(packed.n_lines, packed.text.numel(), slot)
         n_lines, hashed = packed.n_lines, int(cfg.hash_feature_id)
         check(lib.fm_parse_count(ptr(packed.text), ptr(packed.offsets), n_lines, cfg.vocabulary_size, hashed,
                                  ptr(b["sizes"]), ptr(b["poses"]), ptr(b["status"]), ptr(b["ws_parse"]),
@@ -387,12 +406,17 @@ class PeerShardedModel:
                                 ptr(b["status"]), ptr(b["ws_parse"]), b["ws_parse"].numel(), st), "fm_parse_fill")
         return packed, b
 
-    def train_step_async(self, lines, weights=None, global_batch=None, mark=lambda name: None):
+    def train_step_async(self, lines, weights=None, global_batch=None, mark=lambda name: None, parsed=None):
         """Returns (scalars, flag): scalars = device f32 [global mean loss, global reg_score];
         flag = device i64, -1 when every rank parsed its slice, else rank << 48 | line << 3 | kind
-        of a failing rank (the step was then void on every rank).  Nothing synchronises."""
+        of a failing rank (the step was then void on every rank).  Nothing synchronises.
+        parsed: handle from parse_ahead(lines) (then `lines` is not parsed again)."""
         lib, st, cfg, k, g = self.lib, stream(), self.cfg, self.cfg.factor_num, self.world
-        packed, b = self._parse(lines)
+        if parsed is not None:
+            torch.cuda.current_stream(self.device).wait_event(parsed["done"])
+            packed, b = parsed["packed"], parsed["b"]
+        else:
+            packed, b = self._parse(lines)
         mark("parse")
         if global_batch is None:
             global_batch = packed.n_lines * g
@@ -423,6 +447,9 @@ class PeerShardedModel:
         out = b["scal"].clone()
         dist.all_reduce(out, group=self.group)   # also: nobody reads rows of the next step before all updates ran
         mark("allreduce_loss")
+        if parsed is not None:
+            b["free"] = torch.cuda.Event()
+            b["free"].record(torch.cuda.current_stream(self.device))
         self.global_step += 1
         self.last = dict(pred=b["pred"][:packed.n_lines], packed=packed, status=b["status"])
         return out, flag

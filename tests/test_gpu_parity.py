@@ -415,6 +415,30 @@ def test_train_steps_match_reference_model(criteo_lines, loss_type, hashed, path
         assert not m.gtab.any()
 
 
+def test_parse_ahead_pipeline_matches_inline_steps(criteo_lines):
+    """parse of batch t+1 on a side stream under batch t's kernels: same table as step-by-step"""
+    lines, _ = criteo_lines
+    rng = np.random.default_rng(33)
+    vocab, k, bs = 200003, 16, 250
+    flat = rng.uniform(-0.01, 0.01, (vocab, k + 1)).astype(np.float32)
+    kw = dict(vocabulary_size=vocab, factor_num=k, batch_size=bs, learning_rate=0.05, loss_type="logistic",
+              factor_lambda=1e-3, bias_lambda=1e-3)
+    a = Model(**kw).build(DEV, init_table=flat, layout="interleaved")
+    b = Model(**kw).build(DEV, init_table=flat)
+    batches = [fm_ops.pack_lines(lines[i * bs:(i + 1) * bs]).to(DEV, False) for i in range(6)]
+    ahead = a.parse_ahead(batches[0])
+    losses = []
+    for i in range(6):
+        nxt = a.parse_ahead(batches[i + 1]) if i + 1 < 6 else None
+        out = a.train_step_async(batches[i], parsed=ahead)
+        losses.append(out["status_snapshot"])
+        ahead = nxt
+    exp = [b.train_step(batches[i]) for i in range(6)]
+    got = [float(s.cpu()[6:8].view(torch.float32)[0]) for s in losses]
+    np.testing.assert_allclose(got, exp, rtol=1e-6)
+    np.testing.assert_allclose(a.table[:, :k + 1].cpu().numpy(), b.table[:, :k + 1].cpu().numpy(), rtol=1e-5, atol=1e-8)
+
+
 def test_failed_parse_leaves_the_table_untouched():
     m = Model(vocabulary_size=100, factor_num=4, batch_size=2).build(DEV, seed=0)
     before = m.table.clone()
