@@ -176,10 +176,15 @@ class Model(object):
         self.gld = _stride_for(int(lib.fm_fused_gacc_ld(k)))
         self.layout = layout
         if layout == "interleaved":
-            part = max(self.ld, self.gld)
-            self._store = torch.zeros(v, 3 * part, dtype=torch.float32, device=self.device)
+            # [w | h | g] of one id packed at 16-byte granularity in a block that is a whole number of
+            # 128-byte lines (K=16: 3 x 20 floats in 256 B = 2 lines; the weight row never straddles)
+            part = max((k + 1 + 3) // 4 * 4, int(lib.fm_fused_gacc_ld(k)))
+            block = (3 * part + 31) // 32 * 32
+            if ld is not None:
+                part, block = int(ld), 3 * int(ld)
+            self._store = torch.zeros(v, block, dtype=torch.float32, device=self.device)
             self.table = self._store[:, :part]
-            self.gtab = self._store[:, 2 * part:]
+            self.gtab = self._store[:, 2 * part:3 * part]
         else:
             self.table = torch.zeros(v, self.ld, dtype=torch.float32, device=self.device)
             self.gtab = None  # allocated on the first step that needs it
