@@ -317,20 +317,24 @@ class PeerShardedModel:
         import torch.distributed._symmetric_memory as symm_mem
         k, g, r, dev = self.cfg.factor_num, self.world, self.rank, self.device
         rows = self.rows_per_rank()
-        self.ld, self.gld = _ld_for(k), _stride_for(int(self.lib.fm_fused_gacc_ld(k)))
-        n_table, n_gtab = rows * self.ld, rows * self.gld
+        # per id one block [w | h | g] of whole 128-byte lines (K=16: 3 x 20 floats in 256 B), as in
+        # Model(layout="interleaved"); peers read w (line 0) and add into g, h is only the owner's
+        part = max((k + 1 + 3) // 4 * 4, int(self.lib.fm_fused_gacc_ld(k)))
+        block = (3 * part + 31) // 32 * 32
+        self.ld = self.gld = block
+        n_store = rows * block
         n_bits = ((rows + 31) // 32 + 3) // 4 * 4
-        self._symm = symm_mem.empty(n_table + n_gtab + n_bits, dtype=torch.float32, device=dev)
+        self._symm = symm_mem.empty(n_store + n_bits, dtype=torch.float32, device=dev)
         self._hdl = symm_mem.rendezvous(self._symm, self.group)
         self._symm.zero_()
-        self.table = self._symm[:n_table].view(rows, self.ld)
-        self.gtab = self._symm[n_table:n_table + n_gtab].view(rows, self.gld)
-        self.touched = self._symm[n_table + n_gtab:].view(torch.int32)
+        store = self._symm[:n_store].view(rows, block)
+        self.table, self.accum, self.gtab = store[:, :part], store[:, part:2 * part], store[:, 2 * part:3 * part]
+        self.touched = self._symm[n_store:].view(torch.int32)
         ptrs = [int(p) for p in self._hdl.buffer_ptrs]
         arr = ctypes.c_void_p * g
         self._table_bases = arr(*ptrs)
-        self._gtab_bases = arr(*[p + 4 * n_table for p in ptrs])
-        self._touched_bases = arr(*[p + 4 * (n_table + n_gtab) for p in ptrs])
+        self._gtab_bases = arr(*[p + 4 * 2 * part for p in ptrs])
+        self._touched_bases = arr(*[p + 4 * n_store for p in ptrs])
         if init_table is not None:
             part = torch.as_tensor(init_table, dtype=torch.float32)[r::g, :k + 1]
             self.table[:part.shape[0], :k + 1] = part.to(dev)
@@ -338,7 +342,7 @@ class PeerShardedModel:
             gen = torch.Generator(device=dev)
             gen.manual_seed((seed or 0) * 1000 + r)
             self.table[:, :k + 1].uniform_(-self.cfg.init_value_range, self.cfg.init_value_range, generator=gen)
-        self.accum = torch.full((rows, self.ld), self.cfg.adagrad_init_accumulator, dtype=torch.float32, device=dev)
+        self.accum.fill_(self.cfg.adagrad_init_accumulator)
         self.row_list = torch.empty(rows, dtype=torch.int64, device=dev)
         self.n_rows = torch.zeros(1, dtype=torch.int64, device=dev)
         self.ws_touched = _lib.workspace(self.lib.fm_peer_touched_workspace(rows), dev)
