@@ -326,30 +326,35 @@ fused_adagrad_kernel(float* __restrict__ table, float* __restrict__ accum, int64
 // table[row]): one lane group per OCCURRENCE.  The first group to swap the row's cnt
 // column to zero owns the row and applies the update; later occurrences of the same
 // row see cnt == 0 and leave.  No de-duplication pass is needed.
-template <int LPR, int T>
+// A group is exactly `gs` lanes = the float4 chunks of a K+3 wide row (gs <= 32; wider
+// rows take T chunks per lane), so a warp works on 32 / gs rows at once with no idle
+// lanes inside a group.
+template <int T>
 __global__ void __launch_bounds__(256)
 fused_adagrad_claim_kernel(float* __restrict__ table, float* __restrict__ accum, int64_t ld,
                            const int64_t* __restrict__ rows, int64_t n_max, const int64_t* __restrict__ n_dev, int K,
                            float* __restrict__ gtab, int64_t gtab_ld, float lr, float rf, float rb,
-                           const unsigned long long* __restrict__ guard, int discard_on_guard) {
+                           const unsigned long long* __restrict__ guard, int discard_on_guard, int gs) {
   const bool tripped = guard && *guard != kNoError;
   if (tripped && !discard_on_guard) return;
   const int64_t n = n_dev ? min(*n_dev, n_max) : n_max;
-  const int c = threadIdx.x % LPR;
-  const int64_t groups_per_block = blockDim.x / LPR;
+  const int lane = threadIdx.x & 31;
+  const int rows_per_warp = 32 / gs;
+  const int g = lane / gs, c = lane - g * gs;
+  const bool lane_on = g < rows_per_warp;
   const int vc_table = (K + 4) >> 2, vc_acc = (K + 6) >> 2;
-  const int cnt_chunk = (K + 2) >> 2, cnt_comp = (K + 2) & 3;
-  const int64_t n_round = (n + groups_per_block - 1) / groups_per_block * groups_per_block;
-  for (int64_t j = (int64_t)blockIdx.x * groups_per_block + threadIdx.x / LPR; j < n_round;
-       j += (int64_t)gridDim.x * groups_per_block) {
-    const bool live = j < n;
+  const int cnt_chunk = (K + 2) >> 2, cnt_comp = (K + 2) & 3, d_chunk = (K + 1) >> 2, d_comp = (K + 1) & 3;
+  const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
+  const int64_t warp_id = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  for (int64_t base = warp_id * rows_per_warp; base < n; base += warps_total * rows_per_warp) {  // warp-uniform
+    const int64_t j = base + g;
+    const bool live = lane_on && j < n;
     const int64_t id = live ? rows[j] : 0;
     const int64_t row = id * ld, grow = id * gtab_ld;
     float4 a[T], w[T], h[T];
-    float cnt = 0.f;
 #pragma unroll
     for (int t = 0; t < T; ++t) {
-      const int chunk = c + t * LPR;
+      const int chunk = c + t * gs;
       a[t] = make_float4(0.f, 0.f, 0.f, 0.f);
       w[t] = a[t]; h[t] = a[t];
       if (live && chunk < vc_acc) a[t] = *reinterpret_cast<const float4*>(gtab + grow + 4 * chunk);
@@ -361,32 +366,26 @@ fused_adagrad_claim_kernel(float* __restrict__ table, float* __restrict__ accum,
     // The claim.  It waits for the row's own load (so the atomic hits a line that is already in
     // L2 -- an atomic that misses L2 costs a DRAM round trip inside the atomic unit) and is
     // skipped when the row was visibly consumed already.
+    float cnt = 0.f, D = 0.f;
 #pragma unroll
     for (int t = 0; t < T; ++t) {
-      if (c + t * LPR == cnt_chunk) {
-        const float av[4] = {a[t].x, a[t].y, a[t].z, a[t].w};
-        float seen = 0.f;
-#pragma unroll
-        for (int e = 0; e < 4; ++e) if (e == cnt_comp) seen = av[e];
-        if (live && seen != 0.f) cnt = atomicExch(gtab + grow + 4 * cnt_chunk + cnt_comp, 0.f);
-      }
-    }
-    cnt = sum_in_group<LPR>(cnt);
-    float D = 0.f;
-#pragma unroll
-    for (int t = 0; t < T; ++t) {
-      const int chunk = c + t * LPR;
+      const int chunk = c + t * gs;
       const float av[4] = {a[t].x, a[t].y, a[t].z, a[t].w};
 #pragma unroll
-      for (int e = 0; e < 4; ++e)
-        if (4 * chunk + e == K + 1) D += av[e];
+      for (int e = 0; e < 4; ++e) {
+        if (chunk == cnt_chunk && e == cnt_comp && live && av[e] != 0.f)
+          cnt = atomicExch(gtab + grow + 4 * cnt_chunk + cnt_comp, 0.f);
+        if (chunk == d_chunk && e == d_comp) D = av[e];
+      }
     }
-    D = sum_in_group<LPR>(D);
+    // cnt / D sit in one lane of the group: hand them to the others
+    cnt = __shfl_sync(kFull, cnt, g * gs + cnt_chunk % gs);
+    D = __shfl_sync(kFull, D, g * gs + d_chunk % gs);
     if (!(live && cnt != 0.f)) continue;  // another occurrence of this row got there first
     const float fac_scale = cnt * rf - D, bias_scale = cnt * rb;
 #pragma unroll
     for (int t = 0; t < T; ++t) {
-      const int chunk = c + t * LPR;
+      const int chunk = c + t * gs;
       if (chunk < vc_table && !tripped) {  // tripped: the step is void, only throw the sums away
         const float av[4] = {a[t].x, a[t].y, a[t].z, a[t].w};
         float wv[4] = {w[t].x, w[t].y, w[t].z, w[t].w};
@@ -394,11 +393,11 @@ fused_adagrad_claim_kernel(float* __restrict__ table, float* __restrict__ accum,
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const int col = 4 * chunk + e;
-          float g = 0.f;
-          if (col == 0) g = fmaf(bias_scale, wv[e], av[e]);
-          else if (col <= K) g = fmaf(wv[e], fac_scale, av[e]);
-          hv[e] = fmaf(g, g, hv[e]);
-          wv[e] -= __fdiv_rn(lr * g, __fsqrt_rn(hv[e]));
+          float gr = 0.f;
+          if (col == 0) gr = fmaf(bias_scale, wv[e], av[e]);
+          else if (col <= K) gr = fmaf(wv[e], fac_scale, av[e]);
+          hv[e] = fmaf(gr, gr, hv[e]);
+          wv[e] = fmaf(-lr * gr, rsqrtf(hv[e]), wv[e]);   // w -= lr g / sqrt(acc)  (TF: g * lr * rsqrt(acc))
         }
         *reinterpret_cast<float4*>(table + row + 4 * chunk) = make_float4(wv[0], wv[1], wv[2], wv[3]);
         *reinterpret_cast<float4*>(accum + row + 4 * chunk) = make_float4(hv[0], hv[1], hv[2], hv[3]);
@@ -546,18 +545,19 @@ FM_EXPORT int fm_fused_adagrad_claim(float* table, float* accum, int64_t table_l
   if (n == 0) return FM_OK;
   FM_REQUIRE(table && accum && rows && gtab, "fm_fused_adagrad_claim: null pointer");
   FM_REQUIRE((((uintptr_t)table | (uintptr_t)accum | (uintptr_t)gtab) & 15) == 0, "fm_fused_adagrad_claim: 16-byte alignment required");
-  Shape sh;
-  if (!pick_shape((factor_num + 6) / 4, &sh))
-    return fm_fail(FM_E_LIMIT, "fm_fused_adagrad_claim: factor_num %lld too large", (long long)factor_num);
-  const int64_t groups_per_block = 256 / sh.lpr;
-  int64_t blocks = (n + groups_per_block - 1) / groups_per_block;
+  const int64_t chunks = (factor_num + 6) / 4;
+  const int gs = chunks <= 32 ? (int)chunks : 32;
+  const int t = (int)((chunks + gs - 1) / gs);
+  if (t > 3) return fm_fail(FM_E_LIMIT, "fm_fused_adagrad_claim: factor_num %lld too large", (long long)factor_num);
+  const int64_t rows_per_block = 8 * (32 / gs);
+  int64_t blocks = (n + rows_per_block - 1) / rows_per_block;
   if (blocks > 148 * 16) blocks = 148 * 16;
-#define CALL(LPR, T)                                                                                      \
-  fused_adagrad_claim_kernel<LPR, T><<<(unsigned)blocks, 256, 0, stream>>>(                               \
+#define CALL(T)                                                                                           \
+  fused_adagrad_claim_kernel<T><<<(unsigned)blocks, 256, 0, stream>>>(                                    \
       table, accum, table_ld, rows, n, n_dev, (int)factor_num, gtab, gtab_ld, learning_rate,              \
-      reg_grad * factor_lambda, reg_grad * bias_lambda, reinterpret_cast<const unsigned long long*>(guard),        \
-      discard_on_guard)
-  FM_DISPATCH_SHAPE(sh, CALL)
+      reg_grad * factor_lambda, reg_grad * bias_lambda, reinterpret_cast<const unsigned long long*>(guard), \
+      discard_on_guard, gs)
+  if (t == 1) { CALL(1); } else if (t == 2) { CALL(2); } else { CALL(3); }
 #undef CALL
   FM_LAUNCH_CHECK();
   return FM_OK;

@@ -156,7 +156,8 @@ class Model(object):
         self.predict_files = expand(pfiles) if pfiles is not None else []
 
     # ---- the vocabulary table ------------------------------------------------------
-    def build(self, device=None, init_table=None, seed=None, max_nnz_per_line=None, ld=None, layout="split"):
+    def build(self, device=None, init_table=None, seed=None, max_nnz_per_line=None, ld=None,
+              layout="interleaved"):
         """Allocates table + Adagrad accumulator (+ table-shaped gradient accumulator) in HBM.
         The table is [vocabulary_size, ld] (row = feature id, see _stride_for); the reference's
         vocabulary_block_num blocks (fm_model.py:269-284) are a relabelling applied when
