@@ -78,10 +78,11 @@ __device__ __forceinline__ float sum_in_group(float v) {  // over the LPR lanes 
   return v;
 }
 
-// LPR lanes share a row; lane c owns float4 chunks c, c + LPR, ... (T of them).
+// gs lanes share a row (gs = the float4 chunks of a K+3 wide row, at most 32); lane c of a
+// group owns chunks c, c + gs, ... (T of them); a warp walks 32 / gs rows per step.
 // PEER: rows and accumulator rows are addressed through `peers` (id -> owner shard) instead
 // of table / gacc; reads and vector atomics then travel over NVLink where the owner is remote.
-template <int LPR, int T, bool PEER>
+template <int T, bool PEER>
 __global__ void __launch_bounds__(kWarps * 32)
 fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __restrict__ local,
                            const float* __restrict__ vals, const int32_t* __restrict__ poses,
@@ -89,11 +90,12 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
                            int K, const float* __restrict__ table, int64_t ld, float lam_f, float lam_b,
                            int loss_kind, float inv_batch, float* __restrict__ pred, float* __restrict__ gacc, int64_t gacc_ld,
                            float* __restrict__ partials, const unsigned long long* __restrict__ guard,
-                           const PeerPtrs peers) {
-  constexpr int RPW = 32 / LPR;
+                           const PeerPtrs peers, int gs) {
   __shared__ float s_loss[kWarps], s_reg[kWarps];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int r = lane / LPR, c = lane % LPR;
+  const int RPW = 32 / gs;                       // rows per warp step
+  const int r = lane / gs, c = lane - r * gs;
+  const bool lane_on = r < RPW;                  // 32 % gs trailing lanes idle
   const int vc_table = (K + 4) >> 2, vc_acc = (K + 6) >> 2;  // float4 chunks of a K+1 / K+3 wide row
   const bool active = !(guard && *guard != kNoError);
   float loss_acc = 0.f, reg_acc = 0.f;
@@ -120,16 +122,15 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
       }
       const float my_x = j < end ? vals[j] : 0.f;
       const int rows_here = min(32, end - base);
-#pragma unroll
-      for (int s = 0; s < LPR; ++s) {
+#pragma unroll 4
+      for (int s = 0; s * RPW < rows_here; ++s) {  // warp-uniform
         const int jj = s * RPW + r;
-        if (s * RPW >= rows_here) break;  // warp-uniform
-        const float* rowp = reinterpret_cast<const float*>(__shfl_sync(kFull, my_row, jj));
-        const float x = __shfl_sync(kFull, my_x, jj);
-        if (jj < rows_here) {
+        const float* rowp = reinterpret_cast<const float*>(__shfl_sync(kFull, my_row, jj & 31));
+        const float x = __shfl_sync(kFull, my_x, jj & 31);
+        if (lane_on && jj < rows_here) {
 #pragma unroll
           for (int t = 0; t < T; ++t) {
-            const int chunk = c + t * LPR;
+            const int chunk = c + t * gs;
             if (chunk < vc_table) {
               float4 v = ldg4(rowp + 4 * chunk);
               if (chunk == 0) {  // column 0 is the bias
@@ -150,10 +151,16 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
     float second = 0.f;
 #pragma unroll
     for (int t = 0; t < T; ++t) {
-      S[t].x = sum_row_groups<LPR>(S[t].x);
-      S[t].y = sum_row_groups<LPR>(S[t].y);
-      S[t].z = sum_row_groups<LPR>(S[t].z);
-      S[t].w = sum_row_groups<LPR>(S[t].w);
+      // column totals over the row groups (lanes c, c + gs, ...); every lane ends up with its column's total
+      float4 tot = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int g2 = 0; g2 < RPW; ++g2) {
+        const int src = c + g2 * gs;
+        tot.x += __shfl_sync(kFull, S[t].x, src);
+        tot.y += __shfl_sync(kFull, S[t].y, src);
+        tot.z += __shfl_sync(kFull, S[t].z, src);
+        tot.w += __shfl_sync(kFull, S[t].w, src);
+      }
+      S[t] = tot;
       second += S[t].x * S[t].x + S[t].y * S[t].y + S[t].z * S[t].z + S[t].w * S[t].w;
     }
     if (r != 0) second = 0.f;  // every row group holds the same column totals: count them once
@@ -196,17 +203,16 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
       }
       const float my_x = j < end ? vals[j] : 0.f;
       const int rows_here = min(32, end - base);
-#pragma unroll
-      for (int s = 0; s < LPR; ++s) {
+#pragma unroll 4
+      for (int s = 0; s * RPW < rows_here; ++s) {
         const int jj = s * RPW + r;
-        if (s * RPW >= rows_here) break;
-        float* arow = reinterpret_cast<float*>(__shfl_sync(kFull, my_arow, jj));
-        const float x = __shfl_sync(kFull, my_x, jj);
-        if (jj < rows_here) {
+        float* arow = reinterpret_cast<float*>(__shfl_sync(kFull, my_arow, jj & 31));
+        const float x = __shfl_sync(kFull, my_x, jj & 31);
+        if (lane_on && jj < rows_here) {
           const float pgx = pg * x;
 #pragma unroll
           for (int t = 0; t < T; ++t) {
-            const int chunk = c + t * LPR;
+            const int chunk = c + t * gs;
             if (chunk < vc_acc) {
               const int col = 4 * chunk;
               float o[4] = {pgx * S[t].x, pgx * S[t].y, pgx * S[t].z, pgx * S[t].w};
@@ -486,19 +492,20 @@ FM_EXPORT int fm_fused_score_scatter(const int64_t* feature_ids, const int32_t* 
   FM_REQUIRE((((uintptr_t)table | (uintptr_t)gacc) & 15) == 0, "fm_fused_score_scatter: table and gacc must be 16-byte aligned");
   if (workspace_bytes < fm_fused_workspace(batch))
     return fm_fail(FM_E_WORKSPACE, "fm_fused_score_scatter: workspace %zu < %zu", workspace_bytes, fm_fused_workspace(batch));
-  Shape sh;
-  if (!pick_shape((factor_num + 6) / 4, &sh))
-    return fm_fail(FM_E_LIMIT, "fm_fused_score_scatter: factor_num %lld too large", (long long)factor_num);
+  const int64_t chunks = (factor_num + 6) / 4;
+  const int gs = chunks <= 32 ? (int)chunks : 32;
+  const int t = (int)((chunks + gs - 1) / gs);
+  if (t > 3) return fm_fail(FM_E_LIMIT, "fm_fused_score_scatter: factor_num %lld too large", (long long)factor_num);
   const int blocks = fused_blocks(batch);
   float* partials = reinterpret_cast<float*>(workspace);
   const int64_t denom = loss_batch > 0 ? loss_batch : batch;
   const float inv_batch = denom > 0 ? 1.0f / (float)denom : 0.f;
-#define CALL(LPR, T)                                                                                              \
-  fused_score_scatter_kernel<LPR, T, false><<<blocks, kWarps * 32, 0, stream>>>(                                  \
+#define CALL(T)                                                                                                   \
+  fused_score_scatter_kernel<T, false><<<blocks, kWarps * 32, 0, stream>>>(                                       \
       feature_ids, local_ids, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, table, table_ld, \
       factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, gacc, gacc_ld, partials,                      \
-      reinterpret_cast<const unsigned long long*>(guard), PeerPtrs())
-  FM_DISPATCH_SHAPE(sh, CALL)
+      reinterpret_cast<const unsigned long long*>(guard), PeerPtrs(), gs)
+  if (t == 1) { CALL(1); } else if (t == 2) { CALL(2); } else { CALL(3); }
 #undef CALL
   FM_LAUNCH_CHECK();
   reduce2_kernel<<<1, 256, 0, stream>>>(partials, blocks, inv_batch, loss, reg_score);
@@ -596,21 +603,22 @@ FM_EXPORT int fm_peer_score_scatter(const int64_t* feature_ids, const float* fea
                  "fm_peer_score_scatter: bad gtab / touched base");
     }
   }
-  Shape sh;
-  if (!pick_shape((factor_num + 6) / 4, &sh))
-    return fm_fail(FM_E_LIMIT, "fm_peer_score_scatter: factor_num %lld too large", (long long)factor_num);
+  const int64_t chunks = (factor_num + 6) / 4;
+  const int gs = chunks <= 32 ? (int)chunks : 32;
+  const int t = (int)((chunks + gs - 1) / gs);
+  if (t > 3) return fm_fail(FM_E_LIMIT, "fm_peer_score_scatter: factor_num %lld too large", (long long)factor_num);
   const int blocks = fused_blocks(batch);
   float* partials = reinterpret_cast<float*>(workspace);
   const int64_t denom = loss_batch > 0 ? loss_batch : batch;
   const float inv_batch = denom > 0 ? 1.0f / (float)denom : 0.f;
   // gacc != NULL tells the kernel to scatter; the real targets come from `peers`
   float* scatter_flag = training ? peers.gtab[0] : nullptr;
-#define CALL(LPR, T)                                                                                                \
-  fused_score_scatter_kernel<LPR, T, true><<<blocks, kWarps * 32, 0, stream>>>(                                     \
+#define CALL(T)                                                                                                     \
+  fused_score_scatter_kernel<T, true><<<blocks, kWarps * 32, 0, stream>>>(                                          \
       feature_ids, nullptr, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, peers.table[0],   \
       table_ld, factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, scatter_flag, gtab_ld, partials,      \
-      reinterpret_cast<const unsigned long long*>(guard), peers)
-  FM_DISPATCH_SHAPE(sh, CALL)
+      reinterpret_cast<const unsigned long long*>(guard), peers, gs)
+  if (t == 1) { CALL(1); } else if (t == 2) { CALL(2); } else { CALL(3); }
 #undef CALL
   FM_LAUNCH_CHECK();
   reduce2_kernel<<<1, 256, 0, stream>>>(partials, blocks, inv_batch, loss, reg_score);
