@@ -28,6 +28,7 @@ import bench_data  # noqa: E402
 
 CFG = dict(vocab=1 << 24, factor_num=16, batch=65536, nnz_per_line=39, hash_feature_id=True,
            loss_type="logistic", learning_rate=0.01, init_acc=0.1, factor_lambda=1e-5, bias_lambda=1e-5)
+CFG3 = dict(CFG, vocab=1 << 27, factor_num=64, batch=32768)   # BASELINE config 3 (meant for 8 GPUs)
 METRIC, UNIT = "fm_train_examples_per_sec", "examples/s"
 STAGES = {  # stage marks per step, in order
     "claim": ["parse_count", "parse_fill", "score_scatter", "adagrad"],
@@ -174,10 +175,12 @@ def run_reference(args):
 
 
 def workload_config(args, n_gpus, batch):
-    return {"workload": "cfg2: synthetic Criteo shape, 39 fields, 2^24 hashed vocab, factor 16, "
-                        "batch %d per GPU, logistic loss, Adagrad(0.01, 0.1), lambda 1e-5" % batch,
-            "ids": args.dist, "batch_per_gpu": batch, "global_batch": batch * n_gpus, "factor_num": CFG["factor_num"],
-            "vocabulary_size": CFG["vocab"], "distinct_batches": args.batches,
+    cfg = CFG3 if args.workload == "cfg3" else CFG
+    return {"workload": "%s: synthetic Criteo shape, 39 fields, 2^%d hashed vocab, factor %d, "
+                        "batch %d per GPU, logistic loss, Adagrad(0.01, 0.1), lambda 1e-5"
+                        % (args.workload, cfg["vocab"].bit_length() - 1, cfg["factor_num"], batch),
+            "ids": args.dist, "batch_per_gpu": batch, "global_batch": batch * n_gpus, "factor_num": cfg["factor_num"],
+            "vocabulary_size": cfg["vocab"], "distinct_batches": args.batches,
             "l2_policy": "inputs larger than L2: %d distinct text batches (~37 MB each) + random rows of a "
                          "1.3 GB table / accumulator per step" % args.batches,
             "parallelism": "single GPU" if n_gpus == 1 else "vocab-sharded x%d (id %% G), %s" % (
@@ -194,7 +197,7 @@ def run_ours(args):
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:
         from bench_sharded import run_sharded  # vocab-sharded path
-        return run_sharded(args, CFG, workload_config)
+        return run_sharded(args, CFG3 if args.workload == "cfg3" else CFG, workload_config)
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     b, k = CFG["batch"], CFG["factor_num"]
@@ -360,6 +363,9 @@ def main():
     ap.add_argument("--dist", default="uniform", choices=["uniform", "zipf"])
     ap.add_argument("--batches", type=int, default=8, help="distinct synthetic batches cycled through")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3"],
+                    help="cfg2 (default): 2^24 vocab, K=16, 65536 examples per GPU; cfg3: 2^27 vocab, K=64, "
+                         "32768 examples per GPU (BASELINE config 3, 8 GPUs)")
     ap.add_argument("--path", default="claim", choices=["claim", "fused", "composed"],
                     help="claim: no unique, table-shaped accumulators (default); fused: unique + compact "
                          "accumulators; composed: the reference's op-by-op chain")

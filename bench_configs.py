@@ -1,0 +1,111 @@
+#!/usr/bin/env python
+"""Measurements for the BASELINE.json configs that are not bench.py's headline line.
+
+    python bench_configs.py cfg4            mse + per-example weights, ragged rows (1-512 nnz), K=32
+    python bench_configs.py cfg5 [--quick]  predict-only sweep: batch 4K-1M x factor 8-128, 1 GPU
+
+Prints one JSON line per measurement (CUDA events, device-resident inputs, >= 3 warm-up runs).
+cfg3 (2^27 vocab, K=64, 8 GPUs) is `bench.py --gpus 8 --workload cfg3` under torchrun.
+"""
+import argparse
+import json
+import sys
+import time
+
+import numpy as np
+import torch
+
+import bench_data
+from fast_tffm_b200.fm_model import Model
+from fast_tffm_b200.fm_ops import PackedLines, pack_lines
+
+
+def ragged_text(batch, seed, max_nnz=512, vocab=1 << 24):
+    """cfg4 lines: label '%.6g', 1..max_nnz tokens 'id:%.6g' (values from a pool of N(0,1) draws)"""
+    rng = np.random.default_rng(seed)
+    n = rng.integers(1, max_nnz + 1, batch)
+    total = int(n.sum())
+    pool = np.array(["%.6g" % v for v in rng.normal(size=65536)])
+    toks = np.char.add(np.char.add(np.char.mod("%d", rng.integers(0, vocab, total)), ":"),
+                       pool[rng.integers(0, pool.size, total)])
+    labels = pool[rng.integers(0, pool.size, batch)]
+    off = np.concatenate([[0], np.cumsum(n)])
+    lines = [labels[i] + " " + " ".join(toks[off[i]:off[i + 1]]) for i in range(batch)]
+    weights = np.round(rng.uniform(0.5, 2.0, batch), 3).astype(np.float32)
+    return lines, weights, total
+
+
+def timed(fn, steps, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(steps):
+        fn()
+    t1.record()
+    torch.cuda.synchronize()
+    return t0.elapsed_time(t1) / steps
+
+
+def cfg4(args):
+    dev = torch.device("cuda", 0)
+    b, k, vocab = 65536, 32, 1 << 24
+    t = time.time()
+    batches = []
+    for i in range(1):   # one batch (16.8 M features, ~290 MB of text: far beyond L2), reused
+        lines, weights, nnz = ragged_text(b, 10 + i)
+        batches.append((pack_lines(lines).to(dev, False), torch.from_numpy(weights).to(dev), nnz))
+    batches.append(batches[0])
+    gen_s = time.time() - t
+    m = Model(vocabulary_size=vocab, factor_num=k, batch_size=b, hash_feature_id=False, loss_type="mse",
+              learning_rate=0.01, adagrad_init_accumulator=0.1, factor_lambda=1e-5, bias_lambda=1e-5).build(
+        dev, seed=0, max_nnz_per_line=512)
+    it = [0]
+
+    def step():
+        p, w, _ = batches[it[0] % 2]
+        it[0] += 1
+        return m.train_step_async(p, w)
+    ms = timed(step, args.steps)
+    bufs = step()
+    st = bufs["status"].cpu()
+    assert int(st[0]) == -1
+    text_bytes = int(batches[0][0].offsets[-1])
+    print(json.dumps({"config": "cfg4: mse, per-example weights, 1-512 nnz/row (mean 256.5), K=32, V=2^24, B=65536, 1xB200",
+                      "metric": "fm_train_examples_per_sec", "value": b / (ms * 1e-3), "ms_per_step": ms,
+                      "nnz_per_step": int(st[1]), "text_mb": round(text_bytes / 1e6, 1), "path": "claim",
+                      "loss": float(st[6:8].view(torch.float32)[0]), "data_gen_s": round(gen_s, 1)}))
+
+
+def cfg5(args):
+    dev = torch.device("cuda", 0)
+    vocab = 1 << 24
+    sizes = [4096, 65536] if args.quick else [4096, 16384, 65536, 262144, 1048576]
+    ks = [16, 64] if args.quick else [8, 16, 32, 64, 128]
+    data = {}
+    for b in sizes:
+        text, off, nnz = bench_data.criteo_batch(b, 5)
+        data[b] = PackedLines(torch.from_numpy(bench_data.pad16(text)).to(dev), torch.from_numpy(off).to(dev))
+    for k in ks:
+        m = Model(vocabulary_size=vocab, factor_num=k, batch_size=65536, hash_feature_id=True).build(
+            dev, seed=0, max_nnz_per_line=39, layout="split")
+        for b in sizes:
+            ms = timed(lambda: m.predict_async(data[b]), max(3, min(args.steps, int(2e6 // b) + 3)))
+            st = m._bufs["status"].cpu()
+            assert int(st[0]) == -1
+            print(json.dumps({"config": "cfg5: predict-only (parse -> score from the table), 39 nnz, V=2^24, 1xB200",
+                              "metric": "fm_predict_examples_per_sec", "batch": b, "factor_num": k,
+                              "value": b / (ms * 1e-3), "ms_per_batch": ms}))
+            sys.stdout.flush()
+        del m
+        torch.cuda.empty_cache()
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("which", choices=["cfg4", "cfg5"])
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--quick", action="store_true")
+    a = ap.parse_args()
+    {"cfg4": cfg4, "cfg5": cfg5}[a.which](a)
