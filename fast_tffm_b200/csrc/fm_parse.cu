@@ -220,33 +220,34 @@ struct PosesOut {
 
 // ---- pass 2 ---------------------------------------------------------------
 
-// [+-]digits[.digits][e[+-]digits] through the cheap exact tiers only.  Returns the bytes
-// consumed, or 0 when the text is anything else (leading whitespace, inf/nan, hex, a
-// mantissa or exponent beyond the tiers): the caller then sends the line to the
-// sequential kernel, which knows the whole of strtof.
-__device__ __forceinline__ int scan_value_fast(const uint8_t* __restrict__ p, int n, uint32_t* bits) {
+// [+-]digits[.digits][e[+-]digits] through the cheap exact tiers only.  getc(i) yields byte i of
+// the candidate text (0 at and past its end).  Returns the bytes consumed, or 0 when the text is
+// anything else (leading whitespace, inf/nan, hex, a mantissa or exponent beyond the tiers): the
+// caller then sends the line to the sequential kernel, which knows the whole of strtof.
+template <class GetC>
+__device__ __forceinline__ int scan_value_fast(GetC getc, uint32_t* bits) {
   int i = 0;
-  uint8_t c = n > 0 ? p[0] : (uint8_t)0;
+  uint32_t c = getc(0);
   uint32_t sign = 0;
-  if (c == '-') { sign = 0x80000000u; ++i; c = i < n ? p[i] : (uint8_t)0; }
-  else if (c == '+') { ++i; c = i < n ? p[i] : (uint8_t)0; }
+  if (c == '-') { sign = 0x80000000u; c = getc(++i); }
+  else if (c == '+') { c = getc(++i); }
   uint64_t w = 0;
   int nd = 0, frac = 0;
   bool any = false;
-  for (; fmnp::is_digit(c); c = ++i < n ? p[i] : (uint8_t)0) { w = w * 10 + (c - '0'); nd += (w != 0); any = true; }
+  for (; c - '0' < 10u; c = getc(++i)) { w = w * 10 + (c - '0'); nd += (w != 0); any = true; }
   if (c == '.') {
-    c = ++i < n ? p[i] : (uint8_t)0;
-    for (; fmnp::is_digit(c); c = ++i < n ? p[i] : (uint8_t)0) { w = w * 10 + (c - '0'); nd += (w != 0); ++frac; any = true; }
+    c = getc(++i);
+    for (; c - '0' < 10u; c = getc(++i)) { w = w * 10 + (c - '0'); nd += (w != 0); ++frac; any = true; }
   }
   if (!any || nd > 19) return 0;
   int ex = 0;
   if ((c | 0x20) == 'e') {
     int k = i + 1;
-    uint8_t d = k < n ? p[k] : (uint8_t)0;
+    uint32_t d = getc(k);
     bool eneg = false;
-    if (d == '-') { eneg = true; d = ++k < n ? p[k] : (uint8_t)0; } else if (d == '+') { d = ++k < n ? p[k] : (uint8_t)0; }
-    if (fmnp::is_digit(d)) {
-      for (; fmnp::is_digit(d); d = ++k < n ? p[k] : (uint8_t)0) if (ex < 10000) ex = ex * 10 + (d - '0');
+    if (d == '-') { eneg = true; d = getc(++k); } else if (d == '+') { d = getc(++k); }
+    if (d - '0' < 10u) {
+      for (; d - '0' < 10u; d = getc(++k)) if (ex < 10000) ex = ex * 10 + (int)(d - '0');
       if (eneg) ex = -ex;
       i = k;
     }
@@ -255,6 +256,152 @@ __device__ __forceinline__ int scan_value_fast(const uint8_t* __restrict__ p, in
   if (!fmnp::dec_to_f32_fast(w, (int64_t)ex - frac, &r)) return 0;
   *bits = sign | r;
   return i;
+}
+
+struct MemBytes {  // bytes straight from memory (fallback for tokens that outgrow the register window)
+  const uint8_t* p; int n;
+  __device__ __forceinline__ uint32_t operator()(int i) const { return i < n ? p[i] : 0u; }
+};
+
+// ---- tokens from a 32-byte register window ------------------------------------------
+// 0x80 in every byte of x that is zero (exact)
+__device__ __forceinline__ uint64_t zero_bytes(uint64_t x) {
+  const uint64_t k = 0x7f7f7f7f7f7f7f7full;
+  return ~(((x & k) + k) | x | k);
+}
+__device__ __forceinline__ uint64_t keep_low_bytes(int n) {  // mask of the n lowest bytes, n clipped to 0..8
+  return n >= 8 ? ~0ull : n <= 0 ? 0ull : ((1ull << (8 * n)) - 1ull);
+}
+struct Window {   // 32 bytes of text from the token start; bytes at and past the line end are 0
+  uint64_t w0, w1, w2, w3;
+  __device__ __forceinline__ uint64_t word(int j) const { return j == 0 ? w0 : j == 1 ? w1 : j == 2 ? w2 : j == 3 ? w3 : 0ull; }
+  __device__ __forceinline__ uint32_t byte(int i) const { return (uint32_t)(word(i >> 3) >> (8 * (i & 7))) & 0xffu; }
+  // 8 bytes starting at byte `off` (zeros past byte 31)
+  __device__ __forceinline__ uint64_t at(int off) const {
+    const int j = off >> 3, sh = (off & 7) * 8;
+    const uint64_t lo = word(j);
+    return sh ? ((lo >> sh) | (word(j + 1) << (64 - sh))) : lo;
+  }
+};
+__device__ __forceinline__ Window load_window(const uint8_t* __restrict__ text, int64_t q, int64_t limit, int avail) {
+  const int64_t a = q & ~(int64_t)7;
+  uint64_t v[5];
+#pragma unroll
+  for (int k = 0; k < 5; ++k)
+    v[k] = (a + 8 * k + 8 <= limit) ? __ldg(reinterpret_cast<const uint64_t*>(text + a + 8 * k)) : 0ull;
+  const int sh = ((int)q & 7) * 8;
+  Window w;
+  if (sh) {
+    w.w0 = (v[0] >> sh) | (v[1] << (64 - sh)); w.w1 = (v[1] >> sh) | (v[2] << (64 - sh));
+    w.w2 = (v[2] >> sh) | (v[3] << (64 - sh)); w.w3 = (v[3] >> sh) | (v[4] << (64 - sh));
+  } else {
+    w.w0 = v[0]; w.w1 = v[1]; w.w2 = v[2]; w.w3 = v[3];
+  }
+  w.w0 &= keep_low_bytes(avail); w.w1 &= keep_low_bytes(avail - 8);
+  w.w2 &= keep_low_bytes(avail - 16); w.w3 &= keep_low_bytes(avail - 24);
+  return w;
+}
+// index of the first byte that is NUL, ' ' or (with_colon) ':' in the 32-byte window; 32 if none
+__device__ __forceinline__ int find_end(const Window& w, bool with_colon) {
+  const uint64_t sp = 0x2020202020202020ull, co = 0x3a3a3a3a3a3a3a3aull;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const uint64_t x = w.word(j);
+    uint64_t f = zero_bytes(x) | zero_bytes(x ^ sp);
+    if (with_colon) f |= zero_bytes(x ^ co);
+    if (f) return 8 * j + ((__ffsll((long long)f) >> 3) - 1);
+  }
+  return 32;
+}
+struct RegBytes {  // up to 16 bytes held in two registers
+  uint64_t lo, hi; int n;
+  __device__ __forceinline__ uint32_t operator()(int i) const {
+    return i < n ? (uint32_t)((i < 8 ? lo : hi) >> (8 * (i & 7))) & 0xffu : 0u;
+  }
+};
+
+enum { kTokOk = 0, kTokFallback = 1, kTokBad = 2 };
+
+// one token "id[:val]" (or the label when is_label) starting at q, from registers.
+// kTokFallback: the token does not fit the window, use the byte-wise parser.
+__device__ __forceinline__ int parse_token_regs(const uint8_t* __restrict__ text, int64_t q, int64_t e, int64_t limit,
+                                                int hash, int64_t vocab, bool is_label, int64_t* id_out,
+                                                uint32_t* bits_out) {
+  const int avail = e - q >= 32 ? 32 : (int)(e - q);
+  const Window w = load_window(text, q, limit, avail);
+  int vstart = 0;
+  if (!is_label) {
+    const int n = find_end(w, true);
+    if (n >= 32) return kTokFallback;
+    if (n == 0) return kTokBad;  // empty token: the sequential path knows what the reference does with it
+    int64_t id;
+    if (hash) {
+      const uint64_t m = 0xc6a4a7935bd1e995ull;
+      uint64_t h = 0xDECAFCAFFEull ^ ((uint64_t)n * m);
+#pragma unroll
+      for (int j = 0; j < 3; ++j)
+        if (8 * (j + 1) <= n) { uint64_t k = w.word(j); k *= m; k ^= k >> 47; k *= m; h ^= k; h *= m; }
+      if (n & 7) { h ^= w.word(n >> 3) & keep_low_bytes(n & 7); h *= m; }
+      h ^= h >> 47; h *= m; h ^= h >> 47;
+      id = (int64_t)((vocab & (vocab - 1)) == 0 ? (h & (uint64_t)(vocab - 1)) : (h % (uint64_t)vocab));
+    } else {
+      if (n > 18) return kTokBad;
+      uint64_t acc = 0;
+      for (int i = 0; i < n; ++i) {
+        const uint32_t d = w.byte(i) - '0';
+        if (d >= 10u) return kTokBad;
+        acc = acc * 10 + d;
+      }
+      if ((int64_t)acc >= vocab) return kTokBad;
+      id = (int64_t)acc;
+    }
+    *id_out = id;
+    if (w.byte(n) != ':') { *bits_out = 0x3f800000u; return kTokOk; }  // ' ' or line end: value 1
+    vstart = n + 1;
+  }
+  // the value (or label): must end at a space or at the line end, inside the window
+  RegBytes v;
+  v.lo = w.at(vstart);
+  v.hi = w.at(vstart + 8);
+  const uint64_t sp = 0x2020202020202020ull;
+  const uint64_t f0 = zero_bytes(v.lo) | zero_bytes(v.lo ^ sp), f1 = zero_bytes(v.hi) | zero_bytes(v.hi ^ sp);
+  const int vlen = f0 ? (__ffsll((long long)f0) >> 3) - 1 : f1 ? 8 + (__ffsll((long long)f1) >> 3) - 1 : 16;
+  if (vstart + vlen >= 32 || vlen >= 16) return kTokFallback;   // may continue past what we hold
+  v.n = vlen;
+  if (vlen == 0) return kTokBad;
+  const int used = scan_value_fast(v, bits_out);
+  return used == vlen ? kTokOk : kTokBad;
+}
+
+// the same token, byte by byte from memory (any length)
+__device__ __noinline__ int parse_token_bytes(const uint8_t* __restrict__ text, int64_t q, int64_t e, int hash,
+                                              int64_t vocab, bool is_label, int64_t* id_out, uint32_t* bits_out) {
+  if (!is_label) {
+    if (hash) {
+      const int64_t a = q;
+      uint8_t ch = text[q];
+      while (ch != ':' && ch != ' ') { ++q; if (q >= e) break; ch = text[q]; }
+      if (q == a) return kTokBad;
+      const uint64_t hsh = fmnp::hash64(text + a, q - a);
+      *id_out = (int64_t)((vocab & (vocab - 1)) == 0 ? (hsh & (uint64_t)(vocab - 1)) : (hsh % (uint64_t)vocab));
+    } else {
+      int nd = 0;
+      uint64_t acc = 0;
+      for (; q < e && fmnp::is_digit(text[q]) && nd < 18; ++q, ++nd) acc = acc * 10 + (text[q] - '0');
+      if (nd == 0 || (q < e && fmnp::is_digit(text[q])) || (int64_t)acc >= vocab) return kTokBad;
+      *id_out = (int64_t)acc;
+    }
+    if (!(q < e && text[q] == ':')) {
+      *bits_out = 0x3f800000u;
+      return (q == e || text[q] == ' ') ? kTokOk : kTokBad;
+    }
+    ++q;
+  }
+  MemBytes mb{text + q, (int)min((int64_t)64, e - q)};
+  const int used = scan_value_fast(mb, bits_out);
+  if (used == 0) return kTokBad;
+  q += used;
+  return (q == e || text[q] == ' ') ? kTokOk : kTokBad;
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
@@ -268,6 +415,7 @@ parse_fill_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ 
   const int64_t line = ((int64_t)blockIdx.x * kWarpsPerBlock + warp) * kLinesPerWarp + g;
   if (line >= n_lines) return;
   const int64_t s = off[line], e = off[line + 1] - 1;
+  const int64_t limit = (off[n_lines] + 15) & ~(int64_t)15;   // readable extent of the text (header contract)
   const int64_t out_base = poses[line];
   const int32_t cnt = poses[line + 1] - poses[line];
   uint8_t* tok = s_tok[warp][g];
@@ -304,42 +452,25 @@ parse_fill_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ 
       for (uint32_t f = sp[k]; f; f &= f - 1) tok[wpos++] = (uint8_t)(c * 16 + 4 * k + (__ffs(f) >> 3));
     __syncwarp(gm);
     for (int t = c; t < tot; t += kLPL) {
-      // tok[] holds 0..128; 128 (the byte after a space that ends the chunk) does not fit a signed char but fits u8
-      int64_t q = pos + tok[t];
+      // tok[] holds 0..128 (128 = the byte after a space that ends the chunk)
+      const int64_t q = pos + tok[t];
       const int32_t ordinal = ord_base + t;
-      uint32_t bits = 0x3f800000u;  // 1.0f
-      if (ordinal < 0) {            // label: everything up to the first space
-        const int used = scan_value_fast(text + q, (int)min((int64_t)64, e - q), &bits);
-        q += used;
-        if (used == 0 || !(q == e || text[q] == ' ')) { bad = true; continue; }
-        labels[line] = __uint_as_float(bits);
-        continue;
+      const bool is_label = ordinal < 0;
+      if (!is_label) {
+        if (q >= e) { bad |= ordinal != cnt; continue; }  // trailing space: breaks without counting (:79-81)
+        if (ordinal >= cnt) { bad = true; continue; }
       }
-      if (q >= e) { bad |= ordinal != cnt; continue; }  // trailing space: breaks without counting (:79-81)
-      if (ordinal >= cnt) { bad = true; continue; }
       int64_t id = 0;
-      if (hash) {
-        const int64_t a = q;
-        uint8_t ch = text[q];
-        while (ch != ':' && ch != ' ') { ++q; if (q >= e) break; ch = text[q]; }
-        if (q == a) { bad = true; continue; }  // empty token: leave it to the sequential path
-        id = (int64_t)(fmnp::hash64(text + a, q - a) % (uint64_t)vocab);
+      uint32_t bits = 0x3f800000u;
+      int rc = parse_token_regs(text, q, e, limit, hash, vocab, is_label, &id, &bits);
+      if (rc == kTokFallback) rc = parse_token_bytes(text, q, e, hash, vocab, is_label, &id, &bits);
+      if (rc != kTokOk) { bad = true; continue; }
+      if (is_label) {
+        labels[line] = __uint_as_float(bits);
       } else {
-        int nd = 0;
-        uint64_t acc = 0;
-        for (; q < e && fmnp::is_digit(text[q]) && nd < 18; ++q, ++nd) acc = acc * 10 + (text[q] - '0');
-        if (nd == 0 || (q < e && fmnp::is_digit(text[q])) || (int64_t)acc >= vocab) { bad = true; continue; }
-        id = (int64_t)acc;
+        ids[out_base + ordinal] = id;
+        vals[out_base + ordinal] = __uint_as_float(bits);
       }
-      if (q < e && text[q] == ':') {
-        ++q;
-        const int used = scan_value_fast(text + q, (int)min((int64_t)64, e - q), &bits);
-        if (used == 0) { bad = true; continue; }
-        q += used;
-      }
-      if (!(q == e || text[q] == ' ')) { bad = true; continue; }
-      ids[out_base + ordinal] = id;
-      vals[out_base + ordinal] = __uint_as_float(bits);
     }
     ord_base += tot;
     bad = __any_sync(gm, bad);
