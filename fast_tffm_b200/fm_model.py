@@ -310,7 +310,8 @@ class Model(object):
 
     PATHS = ("claim", "fused", "composed")
 
-    def train_step_async(self, packed: PackedLines, weights=None, mark=_no_mark, path="claim", parsed=None):
+    def train_step_async(self, packed: PackedLines, weights=None, mark=_no_mark, path="claim", parsed=None,
+                         prefetch=None):
         """One training step on a device-resident batch; enqueues only.  Returns the
         buffers dict: status[0] parse status word, status[1] nnz, status[4] n_unique,
         scalars[0] loss, scalars[2] reg.
@@ -318,7 +319,11 @@ class Model(object):
                         rows -> fm_fused_adagrad_claim: no tf.unique, each table row read once;
              "fused"    parse -> unique -> fm_fused_score_scatter (compact accumulators) ->
                         fm_fused_adagrad;
-             "composed" the reference's op-by-op chain (unique, lookup, scorer, loss, grad, Adagrad)."""
+             "composed" the reference's op-by-op chain (unique, lookup, scorer, loss, grad, Adagrad).
+        parsed:   handle from parse_ahead() for THIS batch (claim path);
+        prefetch: the NEXT batch (device-resident): its parse is started on the side stream right
+                  after this batch's scorer kernel, i.e. under the DRAM-bound update kernel, and the
+                  handle comes back as result["ahead"]."""
         if path not in self.PATHS:
             raise ValueError("path must be one of %s" % (self.PATHS,))
         if parsed is not None and path != "claim":
@@ -342,11 +347,17 @@ class Model(object):
                 ptr(gtab), gtab.stride(0), ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st),
                 "fm_fused_score_scatter")
             mark("score_scatter")
+            ahead = None
+            if prefetch is not None:
+                scored = torch.cuda.Event()
+                scored.record(torch.cuda.current_stream(self.device))
+                ahead = self.parse_ahead(prefetch, after=scored)
             check(lib.fm_fused_adagrad_claim(
                 ptr(self.table), ptr(self.accum), tstride, ptr(b["ids"]), b["cap"], _off(b["status"], 1), k,
                 ptr(gtab), gtab.stride(0), self.learning_rate, self.factor_lambda, self.bias_lambda,
                 1.0 / self.batch_size, ptr(b["status"]), 0, st), "fm_fused_adagrad_claim")
             mark("adagrad")
+            b["ahead"] = ahead
             if parsed is not None:   # the buffer set may be refilled once this step is through with it
                 b["status_snapshot"] = b["status"].clone()
                 b["free"] = torch.cuda.Event()
