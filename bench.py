@@ -270,8 +270,19 @@ def run_ours(args):
                  for n, ms in merged.items()}
     # the dominant GATHER/SCATTER kernel: the longest of the table-touching stages
     dom = max(merged, key=lambda n: merged[n])
+    # DRAM bytes per launch of that kernel from the committed ncu --set full capture of this very
+    # workload (profiles/traffic_r1.json); null for any other workload / path / layout
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic_r1.json")
+    if (os.path.exists(tpath) and args.workload == "cfg2" and args.dist == "uniform" and fused == "claim"
+            and args.layout == "interleaved" and args.ld is None):
+        per_kernel = json.load(open(tpath))["dram_bytes_per_launch"]
+        stage_kernels = {"adagrad": ["fused_adagrad_claim"], "score_scatter": ["fused_score_scatter"],
+                         "parse": ["parse_count_kernel", "parse_fill_kernel"]}
+        if all(kn in per_kernel for kn in stage_kernels.get(dom, ["?"])):
+            traffic = sum(per_kernel[kn] for kn in stage_kernels[dom])
     roofline = {"bound": "hbm", "kernel": dom, "achieved": per_stage[dom]["gbs"], "peak": peak,
-                "peak_kind": peak_kind, "unit": "GB/s", "frac": per_stage[dom]["frac"], "traffic": None,
+                "peak_kind": peak_kind, "unit": "GB/s", "frac": per_stage[dom]["frac"], "traffic": traffic,
                 "step_frac": round(sum(alg.values()) / (total_ms / args.steps * 1e-3) / 1e9 / peak, 4),
                 "stages": per_stage}
 
