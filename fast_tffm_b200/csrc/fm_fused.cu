@@ -66,12 +66,6 @@ __device__ __forceinline__ void split_id(int64_t id, int n, int* owner, int64_t*
 }
 
 template <int LPR>
-__device__ __forceinline__ float sum_row_groups(float v) {  // over lanes with equal (lane % LPR)
-#pragma unroll
-  for (int o = 16; o >= LPR; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
-  return v;
-}
-template <int LPR>
 __device__ __forceinline__ float sum_in_group(float v) {  // over the LPR lanes of one row
 #pragma unroll
   for (int o = LPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);

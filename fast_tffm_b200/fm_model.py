@@ -254,8 +254,7 @@ class Model(object):
             lines=lines, cap=cap,
             labels=torch.empty(lines, dtype=f32, device=dev), sizes=torch.empty(lines, dtype=i32, device=dev),
             poses=torch.empty(lines + 1, dtype=i32, device=dev), ids=torch.empty(cap, dtype=i64, device=dev),
-            vals=torch.empty(cap, dtype=f32, device=dev), ori=torch.empty(cap, dtype=i64, device=dev),
-            local=torch.empty(cap, dtype=i32, device=dev), rows=None,
+            vals=torch.empty(cap, dtype=f32, device=dev), ori=None, local=None, ws_unique=None, rows=None,
             grad=None, pred=torch.empty(lines, dtype=f32, device=dev),
             gacc_ld=int(lib.fm_fused_gacc_ld(self.factor_num)),
             gacc=None,
@@ -264,7 +263,6 @@ class Model(object):
             # [first_error, nnz, n_lines, reserved] (fm_parse_status), n_unique, then loss and reg as f32 bits
             status=torch.zeros(8, dtype=i64, device=dev),
             ws_parse=_lib.workspace(lib.fm_parse_workspace(lines), dev),
-            ws_unique=_lib.workspace(lib.fm_unique_workspace(cap), dev),
             ws_score=_lib.workspace(lib.fm_score_workspace(lines), dev),
             ws_loss=_lib.workspace(lib.fm_loss_workspace(lines), dev),
         )
@@ -288,6 +286,11 @@ class Model(object):
         mark("parse_fill")
         if not unique:
             return
+        if b["ws_unique"] is None:   # only the fused / composed paths de-duplicate
+            dev = self.device
+            b["ori"] = torch.empty(b["cap"], dtype=torch.int64, device=dev)
+            b["local"] = torch.empty(b["cap"], dtype=torch.int32, device=dev)
+            b["ws_unique"] = _lib.workspace(lib.fm_unique_workspace(b["cap"]), dev)
         check(lib.fm_unique(ptr(b["ids"]), b["cap"], nnz_dev, ptr(b["ori"]), ptr(b["local"]), nuniq_dev,
                             ptr(b["ws_unique"]), b["ws_unique"].numel(), st), "fm_unique")
         mark("unique")

@@ -36,3 +36,34 @@ def run(rank, world, port, backend, lines, weights, cfg_kw, init, steps, out_dir
     np.save(os.path.join(out_dir, "pred%d.npy" % rank), pred)
     dist.barrier()
     dist.destroy_process_group()
+
+
+def run_bad_line(rank, world, port, lines, cfg_kw, init, out_dir, mode):
+    """rank 1's slice holds a line the parser rejects: the step must be void on EVERY rank"""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    device = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world)
+    from fast_tffm_b200.fm_model import Model
+    from fast_tffm_b200.fm_ops import FmParseError
+    from fast_tffm_b200.sharded import PeerShardedModel, ShardedModel
+    cls = PeerShardedModel if mode == "peer" else ShardedModel
+    m = cls(Model(**cfg_kw), device=device).build(init_table=init)
+    per = cfg_kw["batch_size"] // world
+    mine = list(lines[rank * per:(rank + 1) * per])
+    if rank == 1:
+        mine[7] = "1 3:oops"
+    raised = False
+    try:
+        m.train_step(mine)
+    except FmParseError as e:
+        raised = "Invalid feature value" in str(e)
+    after_bad = m.gather_full_table().cpu().numpy()
+    loss = m.train_step(lines[rank * per:(rank + 1) * per])      # and the next, clean step works
+    after_good = m.gather_full_table().cpu().numpy()
+    np.save(os.path.join(out_dir, "bad%d.npy" % rank), np.array([float(raised), loss]))
+    if rank == 0:
+        np.save(os.path.join(out_dir, "after_bad.npy"), after_bad)
+        np.save(os.path.join(out_dir, "after_good.npy"), after_good)
+    dist.barrier()
+    dist.destroy_process_group()

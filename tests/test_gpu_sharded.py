@@ -30,3 +30,23 @@ def test_nccl_ranks_equal_single_process(criteo_lines, tmp_path, world, mode):
     np.testing.assert_allclose(np.load(tmp_path / "table.npy"), ref.flat_table(), rtol=1e-4, atol=1e-7)
     got = np.concatenate([np.load(tmp_path / ("pred%d.npy" % r)) for r in range(world)])
     np.testing.assert_allclose(got, ref.predict(lines[:400]), rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("mode", ["exchange", "peer"])
+def test_parse_error_on_one_rank_voids_the_step_everywhere(criteo_lines, tmp_path, mode):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    lines, _ = criteo_lines
+    rng = np.random.default_rng(6)
+    cfg_kw = dict(vocabulary_size=200003, factor_num=8, batch_size=200, hash_feature_id=False, factor_lambda=0.0,
+                  bias_lambda=0.0, learning_rate=0.05, adagrad_init_accumulator=0.1, loss_type="logistic")
+    init = rng.uniform(-0.01, 0.01, (cfg_kw["vocabulary_size"], 9)).astype(np.float32)
+    port = 29790 + (1 if mode == "peer" else 0)
+    mp.spawn(shard_worker.run_bad_line, args=(2, port, lines, cfg_kw, init, str(tmp_path), mode), nprocs=2, join=True)
+    for r in range(2):
+        raised, loss = np.load(tmp_path / ("bad%d.npy" % r))
+        assert raised == 1.0 and np.isfinite(loss)
+    np.testing.assert_array_equal(np.load(tmp_path / "after_bad.npy"), init)        # nothing moved
+    ref, exp = _reference(lines, [1.0] * len(lines), cfg_kw, init, 0, 2)
+    e = ref.train_step(lines[:200])
+    np.testing.assert_allclose(np.load(tmp_path / "after_good.npy"), ref.flat_table(), rtol=1e-4, atol=1e-7)
