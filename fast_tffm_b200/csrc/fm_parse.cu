@@ -412,10 +412,10 @@ parse_fill_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ 
   __shared__ uint8_t s_tok[kWarpsPerBlock][kLinesPerWarp][kChunk + 4];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane / kLPL, c = lane % kLPL;
   const unsigned gm = group_mask(lane);
-  const int64_t line = ((int64_t)blockIdx.x * kWarpsPerBlock + warp) * kLinesPerWarp + g;
-  if (line >= n_lines) return;
-  const int64_t s = off[line], e = off[line + 1] - 1;
   const int64_t limit = (off[n_lines] + 15) & ~(int64_t)15;   // readable extent of the text (header contract)
+  for (int64_t line = ((int64_t)blockIdx.x * kWarpsPerBlock + warp) * kLinesPerWarp + g; line < n_lines;
+       line += (int64_t)gridDim.x * kLinesPerBlock) {
+  const int64_t s = off[line], e = off[line + 1] - 1;
   const int64_t out_base = poses[line];
   const int32_t cnt = poses[line + 1] - poses[line];
   uint8_t* tok = s_tok[warp][g];
@@ -480,6 +480,7 @@ parse_fill_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ 
   // a line that ended short of its count (cannot happen for a regular line)
   if (!bad && ord_base != cnt && ord_base != cnt + 1) bad = true;
   if (bad && c == 0) slow_list[atomicAdd(slow_count, 1)] = (int32_t)line;
+  }
 }
 
 // the lines the fast path gave up on: sequential ParseLine with outputs and error reporting
@@ -608,7 +609,8 @@ FM_EXPORT int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, i
 FM_EXPORT int fm_parse_fill(const uint8_t* text, const int64_t* line_offsets, int64_t n_lines,
                             int64_t vocab_size, int hash_feature_id, const int32_t* feature_poses,
                             float* labels, int64_t* feature_ids, float* feature_vals, int64_t capacity,
-                            fm_parse_status* status, void* workspace, size_t workspace_bytes, void* stream_) {
+                            fm_parse_status* status, void* workspace, size_t workspace_bytes, int max_blocks,
+                            void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   FM_REQUIRE(n_lines >= 0 && vocab_size > 0 && capacity >= 0, "fm_parse_fill: bad size");
   if (n_lines == 0) return FM_OK;
@@ -618,7 +620,8 @@ FM_EXPORT int fm_parse_fill(const uint8_t* text, const int64_t* line_offsets, in
   const ParseWs ws = parse_ws(workspace, n_lines);
   if (workspace_bytes < ws.total)
     return fm_fail(FM_E_WORKSPACE, "fm_parse_fill: workspace %zu < %zu", workspace_bytes, ws.total);
-  const unsigned blocks = (unsigned)((n_lines + kLinesPerBlock - 1) / kLinesPerBlock);
+  unsigned blocks = (unsigned)((n_lines + kLinesPerBlock - 1) / kLinesPerBlock);
+  if (max_blocks > 0 && blocks > (unsigned)max_blocks) blocks = (unsigned)max_blocks;
   parse_fill_kernel<<<blocks, kWarpsPerBlock * 32, 0, stream>>>(text, line_offsets, n_lines, vocab_size,
                                                                 hash_feature_id, feature_poses, labels, feature_ids,
                                                                 feature_vals, capacity, ws.slow_b, ws.slow_count + 1);

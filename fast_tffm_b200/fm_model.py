@@ -221,7 +221,7 @@ class Model(object):
         if after is not None:      # e.g. the event of the H2D copy that brings `packed` in
             side.wait_event(after)
         with torch.cuda.stream(side):
-            self._parse_unique(packed, b, unique=False)
+            self._parse_unique(packed, b, unique=False, max_blocks=self.BACKGROUND_PARSE_BLOCKS)
             done = torch.cuda.Event()
             done.record(side)
         return dict(b=b, done=done, packed=packed)
@@ -269,7 +269,9 @@ class Model(object):
         b["scalars"] = b["status"][6:8].view(torch.float32)  # [loss, -, reg, -]
         return b
 
-    def _parse_unique(self, packed, b, mark=_no_mark, unique=True):
+    BACKGROUND_PARSE_BLOCKS = 2 * 148   # grid cap of the fill pass when it runs ahead on the side stream
+
+    def _parse_unique(self, packed, b, mark=_no_mark, unique=True, max_blocks=0):
         """parse (-> unique) (+ cumsum), all sizes device-resident.
         mark(name) is called after each stage is enqueued (bench.py records CUDA events there)."""
         lib, st = load(), stream()
@@ -282,7 +284,7 @@ class Model(object):
         mark("parse_count")
         check(lib.fm_parse_fill(ptr(packed.text), ptr(packed.offsets), n_lines, self.vocabulary_size, hashed,
                                 ptr(b["poses"]), ptr(b["labels"]), ptr(b["ids"]), ptr(b["vals"]), b["cap"], status,
-                                ptr(b["ws_parse"]), b["ws_parse"].numel(), st), "fm_parse_fill")
+                                ptr(b["ws_parse"]), b["ws_parse"].numel(), max_blocks, st), "fm_parse_fill")
         mark("parse_fill")
         if not unique:
             return

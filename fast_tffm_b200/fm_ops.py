@@ -142,7 +142,7 @@ def _fm_parser_packed(text: Tensor, offsets: Tensor, vocab_size: int, hash_featu
     ids = torch.empty(nnz, dtype=torch.int64, device=dev)
     vals = torch.empty(nnz, dtype=torch.float32, device=dev)
     check(lib.fm_parse_fill(ptr(text), ptr(offsets), n_lines, vocab_size, int(hash_feature_id), ptr(poses),
-                            ptr(labels), ptr(ids), ptr(vals), nnz, ptr(status), ptr(ws), ws.numel(), stream()),
+                            ptr(labels), ptr(ids), ptr(vals), nnz, ptr(status), ptr(ws), ws.numel(), 0, stream()),
           "fm_parse_fill")
     return labels, sizes, ids, vals, status
 

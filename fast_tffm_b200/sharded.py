@@ -91,7 +91,7 @@ class CudaShardKernels:
               "fm_parse_count")
         check(lib.fm_parse_fill(ptr(packed.text), ptr(packed.offsets), n_lines, vocab, int(hashed), ptr(b["poses"]),
                                 ptr(b["labels"]), ptr(b["ids"]), ptr(b["vals"]), b["cap"], status, ptr(b["ws_parse"]),
-                                b["ws_parse"].numel(), st), "fm_parse_fill")
+                                b["ws_parse"].numel(), 0, st), "fm_parse_fill")
         check(lib.fm_unique(ptr(b["ids"]), b["cap"], nnz_dev, ptr(b["ori"]), ptr(b["local"]), nuniq_dev,
                             ptr(b["ws_unique"]), b["ws_unique"].numel(), st), "fm_unique")
         check(lib.fm_shard_bucket(ptr(b["ori"]), b["cap"], nuniq_dev, n_ranks, ptr(b["send_ids"]), ptr(b["pos"]),
@@ -390,12 +390,12 @@ class PeerShardedModel:
         if after is not None:
             side.wait_event(after)
         with torch.cuda.stream(side):
-            packed, b = self._parse(lines, slot=self._ahead_slot)
+            packed, b = self._parse(lines, slot=self._ahead_slot, max_blocks=Model.BACKGROUND_PARSE_BLOCKS)
             done = torch.cuda.Event()
             done.record(side)
         return dict(b=b, packed=packed, done=done)
 
-    def _parse(self, lines, slot=0):
+    def _parse(self, lines, slot=0, max_blocks=0):
         lib, st, cfg = self.lib, stream(), self.cfg
         packed = lines if isinstance(lines, PackedLines) else pack_lines(list(lines))
         if packed.text.device != self.device:
@@ -407,7 +407,8 @@ class PeerShardedModel:
                                  b["ws_parse"].numel(), st), "fm_parse_count")
         check(lib.fm_parse_fill(ptr(packed.text), ptr(packed.offsets), n_lines, cfg.vocabulary_size, hashed,
                                 ptr(b["poses"]), ptr(b["labels"]), ptr(b["ids"]), ptr(b["vals"]), b["cap"],
-                                ptr(b["status"]), ptr(b["ws_parse"]), b["ws_parse"].numel(), st), "fm_parse_fill")
+                                ptr(b["status"]), ptr(b["ws_parse"]), b["ws_parse"].numel(), max_blocks, st),
+              "fm_parse_fill")
         return packed, b
 
     def train_step_async(self, lines, weights=None, global_batch=None, mark=lambda name: None, parsed=None):

@@ -97,11 +97,15 @@ int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, int64_t n_l
 /* Pass 2: labels[n_lines], feature_ids[nnz] (int64, as the op's output),
  * feature_vals[nnz]; `capacity` = elements available in feature_ids/vals.
  * `workspace` is the one given to fm_parse_count for this batch (its contents are
- * still needed: the two passes share their bookkeeping). */
+ * still needed: the two passes share their bookkeeping).
+ * max_blocks: 0 = one thread block per 32 lines; > 0 caps the grid (the blocks then loop),
+ * which turns the pass into a thin background kernel when it runs on a side stream next to
+ * the memory-bound table kernels of the previous batch (2 blocks per SM works well). */
 int fm_parse_fill(const uint8_t* text, const int64_t* line_offsets, int64_t n_lines,
                   int64_t vocab_size, int hash_feature_id, const int32_t* feature_poses,
                   float* labels, int64_t* feature_ids, float* feature_vals, int64_t capacity,
-                  fm_parse_status* status, void* workspace, size_t workspace_bytes, void* stream);
+                  fm_parse_status* status, void* workspace, size_t workspace_bytes, int max_blocks,
+                  void* stream);
 
 /* ---- U1: tf.unique, tffm/fm_model.py:72 ----
  * ori_ids[U] = distinct ids in order of first occurrence; local_ids[n] = index
