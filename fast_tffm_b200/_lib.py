@@ -31,8 +31,9 @@ _SIGNATURES = {
     "fm_split_lines_workspace": (_sz, [_i64]),
     "fm_split_lines": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _vp, _sz, _vp]),
     "fm_parse_workspace": (_sz, [_i64]),
-    "fm_parse_count": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
-    "fm_parse_fill": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _sz, _i32, _vp]),
+    "fm_parse_count": (C.c_int, [_vp, _i64, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "fm_parse_fill": (C.c_int, [_vp, _i64, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _sz, _i32,
+                                _vp]),
     "fm_unique_workspace": (_sz, [_i64]),
     "fm_unique": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "fm_lookup": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp]),

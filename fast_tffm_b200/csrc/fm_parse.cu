@@ -135,13 +135,14 @@ __device__ __forceinline__ T group_sum(T v, unsigned gm) {
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
-parse_count_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ off, int64_t n_lines,
+parse_count_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ begins,
+                   const int64_t* __restrict__ ends, int64_t end_adjust, int64_t n_lines,
                    int32_t* __restrict__ sizes, int32_t* __restrict__ slow_list, int* __restrict__ slow_count) {
   const int lane = threadIdx.x & 31, c = lane % kLPL;
   const unsigned gm = group_mask(lane);
   const int64_t line = ((int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * kLinesPerWarp + lane / kLPL;
   if (line >= n_lines) return;  // the whole lane group leaves together
-  const int64_t s = off[line], e = off[line + 1] - 1;
+  const int64_t s = begins[line], e = ends[line] + end_adjust;
   int spaces = 0;
   uint32_t irregular = 0, trail = 0;
   uint32_t carry = 0x80u;  // "the byte before the line start is a space": a leading space is irregular
@@ -193,13 +194,14 @@ parse_count_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__
 
 // the lines the fast counter could not prove regular: sequential ParseLine, count only
 __global__ void __launch_bounds__(kSlowThreads)
-parse_count_slow_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ off, int64_t vocab, int hash,
+parse_count_slow_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ begins,
+                        const int64_t* __restrict__ ends, int64_t end_adjust, int64_t vocab, int hash,
                         int32_t* __restrict__ sizes, const int32_t* __restrict__ slow_list,
                         const int* __restrict__ slow_count, fm_parse_status* st) {
   const int n = *slow_count;
   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
     const int64_t line = slow_list[t];
-    const int64_t s = off[line], e = off[line + 1] - 1;
+    const int64_t s = begins[line], e = ends[line] + end_adjust;
     int32_t cnt = 0;
     const int rc = parse_line_seq(text + s, e - s, hash, vocab, nullptr, nullptr, nullptr, 0, &cnt);
     if (rc != FM_PARSE_OK) { report_error(st, line, rc); cnt = 0; }
@@ -405,17 +407,17 @@ __device__ __noinline__ int parse_token_bytes(const uint8_t* __restrict__ text, 
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
-parse_fill_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ off, int64_t n_lines,
+parse_fill_kernel(const uint8_t* __restrict__ text, int64_t limit, const int64_t* __restrict__ begins,
+                  const int64_t* __restrict__ ends, int64_t end_adjust, int64_t n_lines,
                   int64_t vocab, int hash, const int32_t* __restrict__ poses, float* __restrict__ labels,
                   int64_t* __restrict__ ids, float* __restrict__ vals, int64_t capacity,
                   int32_t* __restrict__ slow_list, int* __restrict__ slow_count) {
   __shared__ uint8_t s_tok[kWarpsPerBlock][kLinesPerWarp][kChunk + 4];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane / kLPL, c = lane % kLPL;
   const unsigned gm = group_mask(lane);
-  const int64_t limit = (off[n_lines] + 15) & ~(int64_t)15;   // readable extent of the text (header contract)
   for (int64_t line = ((int64_t)blockIdx.x * kWarpsPerBlock + warp) * kLinesPerWarp + g; line < n_lines;
        line += (int64_t)gridDim.x * kLinesPerBlock) {
-  const int64_t s = off[line], e = off[line + 1] - 1;
+  const int64_t s = begins[line], e = ends[line] + end_adjust;
   const int64_t out_base = poses[line];
   const int32_t cnt = poses[line + 1] - poses[line];
   uint8_t* tok = s_tok[warp][g];
@@ -485,14 +487,15 @@ parse_fill_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ 
 
 // the lines the fast path gave up on: sequential ParseLine with outputs and error reporting
 __global__ void __launch_bounds__(kSlowThreads)
-parse_fill_slow_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ off, int64_t vocab, int hash,
+parse_fill_slow_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ begins,
+                       const int64_t* __restrict__ ends, int64_t end_adjust, int64_t vocab, int hash,
                        const int32_t* __restrict__ poses, float* __restrict__ labels, int64_t* __restrict__ ids,
                        float* __restrict__ vals, int64_t capacity, const int32_t* __restrict__ slow_list,
                        const int* __restrict__ slow_count, fm_parse_status* st) {
   const int n = *slow_count;
   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
     const int64_t line = slow_list[t];
-    const int64_t s = off[line], e = off[line + 1] - 1;
+    const int64_t s = begins[line], e = ends[line] + end_adjust;
     const int64_t out_base = poses[line];
     const int32_t cnt = poses[line + 1] - poses[line];
     if (out_base + cnt > capacity) { report_error(st, line, FM_PARSE_E_CAPACITY); continue; }
@@ -574,7 +577,8 @@ FM_EXPORT int fm_split_lines(const uint8_t* text, int64_t text_bytes, int64_t* l
 
 FM_EXPORT size_t fm_parse_workspace(int64_t n_lines) { return parse_ws(nullptr, n_lines < 0 ? 0 : n_lines).total; }
 
-FM_EXPORT int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, int64_t n_lines,
+FM_EXPORT int fm_parse_count(const uint8_t* text, int64_t text_bytes, const int64_t* line_begins,
+                             const int64_t* line_ends, int64_t end_adjust, int64_t n_lines,
                              int64_t vocab_size, int hash_feature_id, int32_t* sizes,
                              int32_t* feature_poses, fm_parse_status* status, void* workspace,
                              size_t workspace_bytes, void* stream_) {
@@ -582,7 +586,8 @@ FM_EXPORT int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, i
   FM_REQUIRE(n_lines >= 0 && vocab_size > 0, "fm_parse_count: n_lines must be >= 0 and vocab_size > 0");
   if (n_lines >= (1ll << 31)) return fm_fail(FM_E_LIMIT, "fm_parse_count: n_lines >= 2^31");
   FM_REQUIRE(feature_poses && status && workspace, "fm_parse_count: null pointer");
-  FM_REQUIRE(n_lines == 0 || (text && line_offsets && sizes), "fm_parse_count: null pointer");
+  FM_REQUIRE(n_lines == 0 || (text && line_begins && line_ends && sizes), "fm_parse_count: null pointer");
+  FM_REQUIRE(text_bytes >= 0, "fm_parse_count: negative text_bytes");
   FM_REQUIRE(((uintptr_t)text & 15) == 0, "fm_parse_count: text must be 16-byte aligned");
   const ParseWs ws = parse_ws(workspace, n_lines);
   if (workspace_bytes < ws.total)
@@ -591,11 +596,12 @@ FM_EXPORT int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, i
   FM_CUDA(cudaMemsetAsync(&status->first_error, 0xff, sizeof(uint64_t), stream));
   if (n_lines > 0) {
     const unsigned blocks = (unsigned)((n_lines + kLinesPerBlock - 1) / kLinesPerBlock);
-    parse_count_kernel<<<blocks, kWarpsPerBlock * 32, 0, stream>>>(text, line_offsets, n_lines, sizes, ws.slow_a,
-                                                                   ws.slow_count);
+    parse_count_kernel<<<blocks, kWarpsPerBlock * 32, 0, stream>>>(text, line_begins, line_ends, end_adjust, n_lines,
+                                                                   sizes, ws.slow_a, ws.slow_count);
     FM_LAUNCH_CHECK();
-    parse_count_slow_kernel<<<kSlowBlocks, kSlowThreads, 0, stream>>>(text, line_offsets, vocab_size, hash_feature_id,
-                                                                      sizes, ws.slow_a, ws.slow_count, status);
+    parse_count_slow_kernel<<<kSlowBlocks, kSlowThreads, 0, stream>>>(text, line_begins, line_ends, end_adjust,
+                                                                      vocab_size, hash_feature_id, sizes, ws.slow_a,
+                                                                      ws.slow_count, status);
     FM_LAUNCH_CHECK();
   }
   SizesIn in{sizes, n_lines};
@@ -606,7 +612,8 @@ FM_EXPORT int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, i
   return FM_OK;
 }
 
-FM_EXPORT int fm_parse_fill(const uint8_t* text, const int64_t* line_offsets, int64_t n_lines,
+FM_EXPORT int fm_parse_fill(const uint8_t* text, int64_t text_bytes, const int64_t* line_begins,
+                            const int64_t* line_ends, int64_t end_adjust, int64_t n_lines,
                             int64_t vocab_size, int hash_feature_id, const int32_t* feature_poses,
                             float* labels, int64_t* feature_ids, float* feature_vals, int64_t capacity,
                             fm_parse_status* status, void* workspace, size_t workspace_bytes, int max_blocks,
@@ -614,7 +621,9 @@ FM_EXPORT int fm_parse_fill(const uint8_t* text, const int64_t* line_offsets, in
   cudaStream_t stream = (cudaStream_t)stream_;
   FM_REQUIRE(n_lines >= 0 && vocab_size > 0 && capacity >= 0, "fm_parse_fill: bad size");
   if (n_lines == 0) return FM_OK;
-  FM_REQUIRE(text && line_offsets && feature_poses && labels && status && workspace, "fm_parse_fill: null pointer");
+  FM_REQUIRE(text && line_begins && line_ends && feature_poses && labels && status && workspace,
+             "fm_parse_fill: null pointer");
+  FM_REQUIRE(text_bytes >= 0, "fm_parse_fill: negative text_bytes");
   FM_REQUIRE(capacity == 0 || (feature_ids && feature_vals), "fm_parse_fill: null output");
   FM_REQUIRE(((uintptr_t)text & 15) == 0, "fm_parse_fill: text must be 16-byte aligned");
   const ParseWs ws = parse_ws(workspace, n_lines);
@@ -622,13 +631,16 @@ FM_EXPORT int fm_parse_fill(const uint8_t* text, const int64_t* line_offsets, in
     return fm_fail(FM_E_WORKSPACE, "fm_parse_fill: workspace %zu < %zu", workspace_bytes, ws.total);
   unsigned blocks = (unsigned)((n_lines + kLinesPerBlock - 1) / kLinesPerBlock);
   if (max_blocks > 0 && blocks > (unsigned)max_blocks) blocks = (unsigned)max_blocks;
-  parse_fill_kernel<<<blocks, kWarpsPerBlock * 32, 0, stream>>>(text, line_offsets, n_lines, vocab_size,
-                                                                hash_feature_id, feature_poses, labels, feature_ids,
-                                                                feature_vals, capacity, ws.slow_b, ws.slow_count + 1);
+  const int64_t limit = (text_bytes + 15) & ~(int64_t)15;  // readable extent of the text (header contract)
+  parse_fill_kernel<<<blocks, kWarpsPerBlock * 32, 0, stream>>>(text, limit, line_begins, line_ends, end_adjust, n_lines,
+                                                                vocab_size, hash_feature_id, feature_poses, labels,
+                                                                feature_ids, feature_vals, capacity, ws.slow_b,
+                                                                ws.slow_count + 1);
   FM_LAUNCH_CHECK();
-  parse_fill_slow_kernel<<<kSlowBlocks, kSlowThreads, 0, stream>>>(text, line_offsets, vocab_size, hash_feature_id,
-                                                                   feature_poses, labels, feature_ids, feature_vals,
-                                                                   capacity, ws.slow_b, ws.slow_count + 1, status);
+  parse_fill_slow_kernel<<<kSlowBlocks, kSlowThreads, 0, stream>>>(text, line_begins, line_ends, end_adjust, vocab_size,
+                                                                   hash_feature_id, feature_poses, labels, feature_ids,
+                                                                   feature_vals, capacity, ws.slow_b, ws.slow_count + 1,
+                                                                   status);
   FM_LAUNCH_CHECK();
   return FM_OK;
 }

@@ -64,3 +64,78 @@ def batches(train_files, weight_files, batch_size, num_epochs, shuffle=True, see
                     yield emit()
     while buf_lines:
         yield emit()
+
+
+class DeviceDataset:
+    """Training files resident in HBM; batches are index selections, the text is never moved.
+
+    The B200 form of the reference's reader + shuffle queue (tffm/fm_model.py:34-126): every
+    file is copied to the device once (pinned host buffer -> H2D), `fm_split_lines` finds the
+    line starts on the device, and a batch is `PackedLines.select(indices)` -- two gathered
+    index arrays over the resident text -- fed straight to the parser.  Shuffling is a device
+    `randperm` over all lines of the epoch (the reference shuffles within a 3-4.5 batch window;
+    a full permutation is the limit of that).  Weight files go through the same parser as
+    label-only lines, so they are read with strtof exactly like `tf.string_to_number` would
+    (tffm/fm_model.py:60).  Smaller final batch allowed (:57).
+    """
+
+    def __init__(self, train_files, weight_files=(), device=None):
+        import numpy as np
+        import torch
+        from . import fm_ops
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        if weight_files and len(weight_files) != len(train_files):
+            raise ValueError('The numbers of train files and weight files do not match.')
+        blobs, counts = [], []
+        for path in train_files:
+            with open(path, "rb") as f:
+                data = f.read()
+            if data and not data.endswith(b"\n"):
+                data += b"\n"
+            blobs.append(data)
+            counts.append(data.count(b"\n"))
+        total = sum((len(b) + 15) // 16 * 16 for b in blobs)
+        host = torch.zeros(total + 16, dtype=torch.uint8).pin_memory()
+        view = host.numpy()
+        bases, pos = [], 0
+        for b in blobs:
+            view[pos:pos + len(b)] = np.frombuffer(b, np.uint8)
+            bases.append(pos)
+            pos += (len(b) + 15) // 16 * 16
+        self.text = host.to(self.device, non_blocking=True)
+        begins, ends = [], []
+        for base, b, n in zip(bases, blobs, counts):
+            off = fm_ops.fm_split_lines(self.text[base:], len(b), n) + base
+            begins.append(off[:-1])
+            ends.append(off[1:])
+        self.begins = torch.cat(begins) if begins else torch.zeros(0, dtype=torch.int64, device=self.device)
+        self.ends = torch.cat(ends) if ends else torch.zeros(0, dtype=torch.int64, device=self.device)
+        self.lines = fm_ops.PackedLines(self.text, begins=self.begins, ends=self.ends)
+        self.weights = None
+        if weight_files:
+            parts = []
+            for path, n in zip(weight_files, counts):
+                with open(path, "rb") as f:
+                    wl = fm_ops.pack_lines(f.read().split(b"\n")[:n])
+                labels, sizes, _, _ = fm_ops.fm_parser(wl.to(self.device, non_blocking=False), 1)
+                if int(sizes.sum()) != 0 or labels.numel() != n:
+                    raise ValueError("%s: expected %d lines holding one number each" % (path, n))
+                parts.append(labels)
+            self.weights = torch.cat(parts)
+
+    def __len__(self):
+        return self.begins.numel()
+
+    def batches(self, batch_size, num_epochs=1, shuffle=True, seed=None):
+        """yields (PackedLines on the device, weights tensor or None)"""
+        import torch
+        gen = torch.Generator(device=self.device)
+        if seed is not None:
+            gen.manual_seed(int(seed))
+        n = len(self)
+        for _ in range(num_epochs):
+            order = torch.randperm(n, device=self.device, generator=gen) if shuffle else \
+                torch.arange(n, device=self.device)
+            for i in range(0, n, batch_size):
+                idx = order[i:i + batch_size]
+                yield self.lines.select(idx), (None if self.weights is None else self.weights[idx])

@@ -278,12 +278,12 @@ class Model(object):
         n_lines = packed.n_lines
         hashed = int(self.hash_feature_id)
         status, nnz_dev, nuniq_dev = ptr(b["status"]), _off(b["status"], 1), _off(b["status"], 4)
-        check(lib.fm_parse_count(ptr(packed.text), ptr(packed.offsets), n_lines, self.vocabulary_size, hashed,
-                                 ptr(b["sizes"]), ptr(b["poses"]), status, ptr(b["ws_parse"]),
-                                 b["ws_parse"].numel(), st), "fm_parse_count")
+        check(lib.fm_parse_count(ptr(packed.text), packed.text_bytes, ptr(packed.begins), ptr(packed.ends), -1, n_lines,
+                                 self.vocabulary_size, hashed, ptr(b["sizes"]), ptr(b["poses"]), status,
+                                 ptr(b["ws_parse"]), b["ws_parse"].numel(), st), "fm_parse_count")
         mark("parse_count")
-        check(lib.fm_parse_fill(ptr(packed.text), ptr(packed.offsets), n_lines, self.vocabulary_size, hashed,
-                                ptr(b["poses"]), ptr(b["labels"]), ptr(b["ids"]), ptr(b["vals"]), b["cap"], status,
+        check(lib.fm_parse_fill(ptr(packed.text), packed.text_bytes, ptr(packed.begins), ptr(packed.ends), -1, n_lines,
+                                self.vocabulary_size, hashed, ptr(b["poses"]), ptr(b["labels"]), ptr(b["ids"]), ptr(b["vals"]), b["cap"], status,
                                 ptr(b["ws_parse"]), b["ws_parse"].numel(), max_blocks, st), "fm_parse_fill")
         mark("parse_fill")
         if not unique:

@@ -43,26 +43,39 @@ class FmParseError(ValueError):
 # text packing (host side of the string tensor the TF op received)
 # --------------------------------------------------------------------------
 class PackedLines:
-    """A batch of lines as one byte buffer + offsets (include/fm_b200.h, "Text layout").
+    """A batch of lines over one byte buffer (include/fm_b200.h, "Text layout").
 
-    line i = text[offsets[i] : offsets[i+1]-1]; one terminator byte after every line.
+    line i = text[begins[i] : ends[i] - 1].  Built from `offsets` (lines back to back, one
+    terminator byte after every line: begins = offsets[:-1], ends = offsets[1:]) or from explicit
+    begins / ends index tensors -- e.g. a shuffled selection of the lines of a file, see select().
     """
 
-    def __init__(self, text: Tensor, offsets: Tensor):
+    def __init__(self, text: Tensor, offsets: Tensor = None, begins: Tensor = None, ends: Tensor = None):
         self.text, self.offsets = text, offsets
+        if offsets is not None:
+            begins, ends = offsets[:-1], offsets[1:]
+        self.begins, self.ends = begins, ends
+        self.text_bytes = text.numel() // 16 * 16     # readable extent handed to the kernels
 
     @property
     def n_lines(self):
-        return self.offsets.numel() - 1
+        return self.begins.numel()
 
     def line(self, i):
-        off = self.offsets[i:i + 2].tolist()
-        raw = bytes(self.text[off[0]:off[1] - 1].cpu().numpy().tobytes())
+        b0, e0 = int(self.begins[i]), int(self.ends[i]) - 1
+        raw = bytes(self.text[b0:e0].cpu().numpy().tobytes())
         return raw.split(b"\0")[0].decode("utf-8", "replace")
 
+    def select(self, index: Tensor):
+        """the lines `index` (any order, e.g. a slice of a random permutation); the text is not copied"""
+        return PackedLines(self.text, begins=self.begins[index].contiguous(), ends=self.ends[index].contiguous())
+
     def to(self, device, non_blocking=True):
-        return PackedLines(self.text.to(device, non_blocking=non_blocking),
-                           self.offsets.to(device, non_blocking=non_blocking))
+        text = self.text.to(device, non_blocking=non_blocking)
+        if self.offsets is not None:
+            return PackedLines(text, self.offsets.to(device, non_blocking=non_blocking))
+        return PackedLines(text, begins=self.begins.to(device, non_blocking=non_blocking),
+                           ends=self.ends.to(device, non_blocking=non_blocking))
 
 
 def pack_lines(lines, pin_memory=False) -> PackedLines:
@@ -127,23 +140,25 @@ def fm_split_lines(text: Tensor, text_bytes: int, max_lines: int) -> Tensor:
 # custom ops
 # --------------------------------------------------------------------------
 @torch.library.custom_op("fast_tffm::fm_parser_packed", mutates_args=(), device_types="cuda")
-def _fm_parser_packed(text: Tensor, offsets: Tensor, vocab_size: int, hash_feature_id: bool) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
+def _fm_parser_packed(text: Tensor, begins: Tensor, ends: Tensor, vocab_size: int, hash_feature_id: bool) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
     lib = load()
     dev = text.device
-    n_lines = offsets.numel() - 1
+    n_lines = begins.numel()
+    text_bytes = text.numel() // 16 * 16
     labels = torch.empty(n_lines, dtype=torch.float32, device=dev)
     sizes = torch.empty(n_lines, dtype=torch.int32, device=dev)
     poses = torch.empty(n_lines + 1, dtype=torch.int32, device=dev)
     status = _status_tensor(dev)
     ws = workspace(lib.fm_parse_workspace(n_lines), dev)
-    check(lib.fm_parse_count(ptr(text), ptr(offsets), n_lines, vocab_size, int(hash_feature_id), ptr(sizes),
-                             ptr(poses), ptr(status), ptr(ws), ws.numel(), stream()), "fm_parse_count")
+    check(lib.fm_parse_count(ptr(text), text_bytes, ptr(begins), ptr(ends), -1, n_lines, vocab_size,
+                             int(hash_feature_id), ptr(sizes), ptr(poses), ptr(status), ptr(ws), ws.numel(), stream()),
+          "fm_parse_count")
     nnz = int(status[1].item())  # output shape is data dependent: one sync, as in any such op
     ids = torch.empty(nnz, dtype=torch.int64, device=dev)
     vals = torch.empty(nnz, dtype=torch.float32, device=dev)
-    check(lib.fm_parse_fill(ptr(text), ptr(offsets), n_lines, vocab_size, int(hash_feature_id), ptr(poses),
-                            ptr(labels), ptr(ids), ptr(vals), nnz, ptr(status), ptr(ws), ws.numel(), 0, stream()),
-          "fm_parse_fill")
+    check(lib.fm_parse_fill(ptr(text), text_bytes, ptr(begins), ptr(ends), -1, n_lines, vocab_size,
+                            int(hash_feature_id), ptr(poses), ptr(labels), ptr(ids), ptr(vals), nnz, ptr(status), ptr(ws),
+                            ws.numel(), 0, stream()), "fm_parse_fill")
     return labels, sizes, ids, vals, status
 
 
@@ -161,7 +176,7 @@ def fm_parser(data_strings, vocab_size, hash_feature_id=False, device=None):
             raise _lib.FmB200Error("fm_parser needs a CUDA device; there is no CPU fallback")
         packed = packed.to(device or torch.device("cuda", torch.cuda.current_device()), non_blocking=False)
     labels, sizes, ids, vals, status = torch.ops.fast_tffm.fm_parser_packed(
-        packed.text, packed.offsets, int(vocab_size), bool(hash_feature_id))
+        packed.text, packed.begins, packed.ends, int(vocab_size), bool(hash_feature_id))
     _raise_on_parse_error(status.cpu(), packed)
     return labels, sizes, ids, vals
 

@@ -86,10 +86,11 @@ class CudaShardKernels:
         lib, dev, n_lines, st = self.lib, packed.text.device, packed.n_lines, stream()
         b = self._buffers(n_lines, packed.text.numel(), n_ranks, dev)
         status, nnz_dev, nuniq_dev = ptr(b["status"]), _at(b["status"], 1), _at(b["status"], 4)
-        check(lib.fm_parse_count(ptr(packed.text), ptr(packed.offsets), n_lines, vocab, int(hashed), ptr(b["sizes"]),
-                                 ptr(b["poses"]), status, ptr(b["ws_parse"]), b["ws_parse"].numel(), st),
-              "fm_parse_count")
-        check(lib.fm_parse_fill(ptr(packed.text), ptr(packed.offsets), n_lines, vocab, int(hashed), ptr(b["poses"]),
+        check(lib.fm_parse_count(ptr(packed.text), packed.text_bytes, ptr(packed.begins), ptr(packed.ends), -1, n_lines,
+                                 vocab, int(hashed), ptr(b["sizes"]), ptr(b["poses"]), status, ptr(b["ws_parse"]),
+                                 b["ws_parse"].numel(), st), "fm_parse_count")
+        check(lib.fm_parse_fill(ptr(packed.text), packed.text_bytes, ptr(packed.begins), ptr(packed.ends), -1, n_lines,
+                                vocab, int(hashed), ptr(b["poses"]),
                                 ptr(b["labels"]), ptr(b["ids"]), ptr(b["vals"]), b["cap"], status, ptr(b["ws_parse"]),
                                 b["ws_parse"].numel(), 0, st), "fm_parse_fill")
         check(lib.fm_unique(ptr(b["ids"]), b["cap"], nnz_dev, ptr(b["ori"]), ptr(b["local"]), nuniq_dev,
@@ -402,11 +403,11 @@ class PeerShardedModel:
             packed = packed.to(self.device, non_blocking=True)
         b = self._buffers(packed.n_lines, packed.text.numel(), slot)
         n_lines, hashed = packed.n_lines, int(cfg.hash_feature_id)
-        check(lib.fm_parse_count(ptr(packed.text), ptr(packed.offsets), n_lines, cfg.vocabulary_size, hashed,
-                                 ptr(b["sizes"]), ptr(b["poses"]), ptr(b["status"]), ptr(b["ws_parse"]),
-                                 b["ws_parse"].numel(), st), "fm_parse_count")
-        check(lib.fm_parse_fill(ptr(packed.text), ptr(packed.offsets), n_lines, cfg.vocabulary_size, hashed,
-                                ptr(b["poses"]), ptr(b["labels"]), ptr(b["ids"]), ptr(b["vals"]), b["cap"],
+        check(lib.fm_parse_count(ptr(packed.text), packed.text_bytes, ptr(packed.begins), ptr(packed.ends), -1, n_lines,
+                                 cfg.vocabulary_size, hashed, ptr(b["sizes"]), ptr(b["poses"]), ptr(b["status"]),
+                                 ptr(b["ws_parse"]), b["ws_parse"].numel(), st), "fm_parse_count")
+        check(lib.fm_parse_fill(ptr(packed.text), packed.text_bytes, ptr(packed.begins), ptr(packed.ends), -1, n_lines,
+                                cfg.vocabulary_size, hashed, ptr(b["poses"]), ptr(b["labels"]), ptr(b["ids"]), ptr(b["vals"]), b["cap"],
                                 ptr(b["status"]), ptr(b["ws_parse"]), b["ws_parse"].numel(), max_blocks, st),
               "fm_parse_fill")
         return packed, b

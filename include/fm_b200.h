@@ -66,12 +66,14 @@ const char* fm_last_error(void);
 
 /* ---- P: FmParser, cc/fm_parser_op.cc:8-15 (op), :29-51 (Compute), :58-109 (ParseLine) ----
  *
- * Text layout: `text` holds the lines back to back; line i is
- * text[line_offsets[i] .. line_offsets[i+1]-1), i.e. every line is followed by
- * exactly one terminator byte ('\n' in a file) that is not part of it.
- * A NUL inside a line ends it (std::string::c_str(), :65).
- * `text` must be 16-byte aligned and readable up to the next multiple of 16
- * past text_bytes (the kernels read whole 16-byte words).
+ * Text layout: line i of the batch is text[line_begins[i] .. line_ends[i] + end_adjust).
+ * For a buffer that holds the lines back to back, each followed by one terminator byte
+ * ('\n' in a file) -- the layout fm_split_lines produces -- pass line_begins = line_offsets,
+ * line_ends = line_offsets + 1, end_adjust = -1.  Any other selection or order of lines
+ * (a shuffled batch) is two gathered index arrays over the same text; the text itself is
+ * never moved.  A NUL inside a line ends it (std::string::c_str(), :65).
+ * `text` must be 16-byte aligned and readable up to the next multiple of 16 past
+ * text_bytes (the kernels read whole 16-byte words).
  */
 
 /* Finds the line starts of a '\n'-separated buffer (the TextLineReader's job,
@@ -89,7 +91,8 @@ int fm_split_lines(const uint8_t* text, int64_t text_bytes, int64_t* line_offset
  * Resets status->first_error first.  Lines the fast counter cannot prove regular are
  * counted by a sequential kernel that follows ParseLine statement by statement. */
 size_t fm_parse_workspace(int64_t n_lines);
-int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, int64_t n_lines,
+int fm_parse_count(const uint8_t* text, int64_t text_bytes, const int64_t* line_begins,
+                   const int64_t* line_ends, int64_t end_adjust, int64_t n_lines,
                    int64_t vocab_size, int hash_feature_id, int32_t* sizes,
                    int32_t* feature_poses /* [n_lines+1] */, fm_parse_status* status,
                    void* workspace, size_t workspace_bytes, void* stream);
@@ -101,7 +104,8 @@ int fm_parse_count(const uint8_t* text, const int64_t* line_offsets, int64_t n_l
  * max_blocks: 0 = one thread block per 32 lines; > 0 caps the grid (the blocks then loop),
  * which turns the pass into a thin background kernel when it runs on a side stream next to
  * the memory-bound table kernels of the previous batch (2 blocks per SM works well). */
-int fm_parse_fill(const uint8_t* text, const int64_t* line_offsets, int64_t n_lines,
+int fm_parse_fill(const uint8_t* text, int64_t text_bytes, const int64_t* line_begins,
+                  const int64_t* line_ends, int64_t end_adjust, int64_t n_lines,
                   int64_t vocab_size, int hash_feature_id, const int32_t* feature_poses,
                   float* labels, int64_t* feature_ids, float* feature_vals, int64_t capacity,
                   fm_parse_status* status, void* workspace, size_t workspace_bytes, int max_blocks,

@@ -44,11 +44,10 @@ def _validation_loss(model, vdata):
     total, n = 0.0, 0
     for lines, weights in vdata:
         pred = model.predict(lines)
-        labels = model._bufs["labels"][:len(lines)].clone()
-        w = None if weights is None else torch.as_tensor(weights, dtype=torch.float32, device=pred.device)
-        loss, _ = fm_ops.fm_loss_grad(pred, labels, w, model.loss_type)
-        total += float(loss) * len(lines)
-        n += len(lines)
+        labels = model._bufs["labels"][:lines.n_lines].clone()
+        loss, _ = fm_ops.fm_loss_grad(pred, labels, weights, model.loss_type)
+        total += float(loss) * lines.n_lines
+        n += lines.n_lines
     return total / max(n, 1)
 
 
@@ -56,23 +55,24 @@ def train(model, monitor, trace):
     vdata = None
     if model.validation_data_files:
         print('Preloading validation data...')
-        vdata = list(fm_data.batches(model.validation_data_files, model.validation_weight_files,
-                                     model.batch_size, 1, shuffle=False))
+        vset = fm_data.DeviceDataset(model.validation_data_files, model.validation_weight_files, model.device)
+        vdata = list(vset.batches(model.batch_size, 1, shuffle=False))
     events = []
     st = time.time()
     start_step = model.global_step
     step_num = start_step
-    for lines, weights in fm_data.batches(model.train_files, model.weight_files, model.batch_size,
-                                          model.num_epochs, shuffle=True, seed=int(st)):
+    # the training files live in HBM; a batch is a shuffled index selection over the resident text
+    dataset = fm_data.DeviceDataset(model.train_files, model.weight_files, model.device)
+    for lines, weights in dataset.batches(model.batch_size, model.num_epochs, shuffle=True, seed=int(st)):
         cur = time.time()
         loss = model.train_step(lines, weights)
         step_num = model.global_step
         tend = time.time()
         if trace and len(events) < 1000:
             events.append({"name": "train_step", "ph": "X", "ts": cur * 1e6, "dur": (tend - cur) * 1e6,
-                           "pid": 0, "tid": 0, "args": {"step": step_num, "examples": len(lines)}})
+                           "pid": 0, "tid": 0, "args": {"step": step_num, "examples": lines.n_lines}})
         if monitor:
-            print('speed:', len(lines) / (tend - cur))
+            print('speed:', lines.n_lines / (tend - cur))
         print('-- Global Step: %d; Avg loss: %.5f;' % (step_num, loss))
         if model.log_dir is not None and step_num % model.save_steps == 0:
             model.save(_ckpt_path(model))

@@ -17,6 +17,7 @@ def _t(a, dtype=None):
 
 class OracleShardKernels:
     def parse_unique_bucket(self, packed, vocab, hashed, n_ranks):
+        assert packed.offsets is not None
         text, off = packed.text.numpy(), packed.offsets.numpy()
         rc = O.parse(text, off, vocab, hashed, raise_on_error=False)
         if len(rc) == 2:   # (kind, line): report it the way the device status word does

@@ -180,6 +180,47 @@ def test_parser_criteo_excerpt(criteo_lines):
     assert_parse_equal(lines, 800000, False)
 
 
+def test_parser_shuffled_selection_of_resident_text(criteo_lines):
+    """a batch = gathered (begin, end) indices over text that stays where it is"""
+    lines, _ = criteo_lines
+    packed = fm_ops.pack_lines(lines[:1000]).to(DEV, False)
+    perm = torch.randperm(1000, generator=torch.Generator().manual_seed(3))[:317]
+    got = fm_ops.fm_parser(packed.select(perm.to(DEV)), 800000)
+    exp = O.parse_lines([lines[i] for i in perm.tolist()], 800000)
+    np.testing.assert_array_equal(got[2].cpu().numpy(), exp[2])
+    np.testing.assert_array_equal(got[1].cpu().numpy(), exp[1])
+    np.testing.assert_array_equal(bits(got[3]), exp[3].view(np.uint32))
+    np.testing.assert_array_equal(bits(got[0]), exp[0].view(np.uint32))
+
+
+def test_device_dataset_epochs(tmp_path, criteo_lines):
+    from fast_tffm_b200.data import DeviceDataset
+    lines, weights = criteo_lines
+    files, wfiles = [], []
+    for i, (lo, hi) in enumerate([(0, 300), (300, 1000)]):
+        f, w = tmp_path / ("train_%d" % i), tmp_path / ("weight_%d" % i)
+        f.write_text("\n".join(lines[lo:hi]) + ("\n" if i == 0 else ""))     # second file: no final newline
+        w.write_text("\n".join("%g" % x for x in weights[lo:hi]) + "\n")
+        files.append(str(f))
+        wfiles.append(str(w))
+    ds = DeviceDataset(files, wfiles, DEV)
+    assert len(ds) == 1000
+    np.testing.assert_array_equal(ds.weights.cpu().numpy(), np.float32(weights[:1000]))
+    seen = []
+    for packed, w in ds.batches(256, num_epochs=1, shuffle=True, seed=5):
+        labels, sizes, ids, vals = fm_ops.fm_parser(packed, 800000)
+        assert w.numel() == packed.n_lines == labels.numel()
+        # weight == label + 1 in the reference's sample files: the pairing survived the shuffle
+        np.testing.assert_array_equal(w.cpu().numpy(), labels.cpu().numpy() + 1)
+        seen.append(sizes.cpu().numpy())
+    assert [len(x) for x in seen] == [256, 256, 256, 232]
+    exp_sizes = O.parse_lines(lines[:1000], 800000)[1]
+    assert sorted(np.concatenate(seen).tolist()) == sorted(exp_sizes.tolist())
+    order = [p for p, _ in ds.batches(1000, shuffle=False)]
+    np.testing.assert_array_equal(fm_ops.fm_parser(order[0], 800000)[2].cpu().numpy(),
+                                  O.parse_lines(lines[:1000], 800000)[2])
+
+
 def test_parser_empty_batch():
     labels, sizes, ids, vals = fm_ops.fm_parser([], 10)
     assert labels.numel() == 0 and sizes.numel() == 0 and ids.numel() == 0 and vals.numel() == 0
