@@ -47,3 +47,25 @@ def test_train_then_predict_cli(tmp_path, loss_type):
     out = subprocess.run([sys.executable, os.path.join(ROOT, "run_tffm.py"), "generate", str(tmp_path / "t.cfg")],
                          capture_output=True, text=True, env=env, cwd=ROOT)
     assert out.returncode == 2
+
+
+def test_validation_and_tolerance_stop_early(tmp_path):
+    """validation_files + tolerance: the loop prints the validation loss every save_steps and stops under it
+    (run_tffm.py:69-77 of the reference)"""
+    for f in ("train_0", "train_1", "weight_0", "weight_1", "test_0"):
+        shutil.copy(os.path.join(ROOT, "data", f), tmp_path / f)
+    cfg = open(os.path.join(ROOT, "sample.cfg")).read()
+    cfg = cfg.replace("./data/", str(tmp_path) + "/").replace("./log", str(tmp_path / "log"))
+    cfg = cfg.replace("batch_size = 50000", "batch_size = 400").replace("epoch_num = 20", "epoch_num = 50")
+    cfg = cfg.replace("factor_num = 100", "factor_num = 8").replace("save_steps = 10", "save_steps = 2")
+    cfg = cfg.replace("#tolerance = 0.2", "tolerance = 1000.0")
+    cfg = cfg.replace("#validation_files = " + str(tmp_path) + "/test_*", "validation_files = " + str(tmp_path) + "/test_*")
+    (tmp_path / "t.cfg").write_text(cfg)
+    assert "\nvalidation_files" in cfg and "\ntolerance" in cfg
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "run_tffm.py"), "train", str(tmp_path / "t.cfg")],
+                         capture_output=True, text=True, env=dict(os.environ, PYTHONPATH=ROOT), cwd=ROOT)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "Preloading validation data..." in out.stdout
+    assert re.search(r"validation loss at step 2: [0-9.]+", out.stdout)
+    assert "Loss on validation data set is below tolerance. Training completed." in out.stdout
+    assert len(re.findall(r"-- Global Step:", out.stdout)) == 2      # stopped at the first check
