@@ -227,26 +227,35 @@ def run_ours(args):
     # ---- device-resident throughput (value) + per-stage CUDA events ----------------
     fused = args.path
     stages = STAGES[fused]
-    for i in range(args.warmup):
-        m.train_step_async(devb[i % len(devb)], path=fused)
+    ahead_on = fused == "claim" and not args.no_parse_ahead
+
+    def run_steps(n_steps, base, ev=None):
+        """the timed loop; the warm-up runs the very same code so that every buffer set, stream and
+        event the pipeline needs exists before the clock starts"""
+        bufs = None
+        ahead = m.parse_ahead(devb[base % len(devb)]) if ahead_on else None
+        for s in range(n_steps):
+            cursor = [0]
+            if ev is not None:
+                ev[s][0].record()
+
+            def mark(name, s=s, cursor=cursor):
+                if ev is not None:
+                    cursor[0] += 1
+                    ev[s][cursor[0]].record()
+            # the parse of batch s+1 runs on a side stream under the table kernels of batch s
+            nxt = m.parse_ahead(devb[(base + s + 1) % len(devb)]) if ahead_on else None
+            bufs = m.train_step_async(devb[(base + s) % len(devb)], mark=mark, path=fused, parsed=ahead)
+            ahead = nxt
+        return bufs
+
+    run_steps(args.warmup, 0)
     torch.cuda.synchronize()
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(stages) + 1)] for _ in range(args.steps)]
     sampler = ClockSampler(local_rank)
     sampler.start()
     torch.cuda.synchronize()
-    ahead_on = fused == "claim" and not args.no_parse_ahead
-    ahead = m.parse_ahead(devb[0]) if ahead_on else None
-    for s in range(args.steps):
-        cursor = [0]
-        ev[s][0].record()
-
-        def mark(name, evs=ev[s], cursor=cursor):
-            cursor[0] += 1
-            evs[cursor[0]].record()
-        # the parse of batch s+1 runs on a side stream under the table kernels of batch s
-        nxt = m.parse_ahead(devb[(s + 1) % len(devb)]) if ahead_on else None
-        bufs = m.train_step_async(devb[s % len(devb)], mark=mark, path=fused, parsed=ahead)
-        ahead = nxt
+    bufs = run_steps(args.steps, args.warmup, ev)
     torch.cuda.synchronize()
     clocks = sampler.stop()
     total_ms = ev[0][0].elapsed_time(ev[-1][-1])

@@ -82,8 +82,7 @@ def run_sharded(args, cfg, workload_config):
             loss = loss[0]
         return float(ms.item()), float(loss[0].item())
 
-    for s in range(args.warmup):
-        m.train_step_async(devb[s % len(devb)], global_batch=b * world)
+    timed(devb, args.warmup, 0)      # warm-up through the same pipelined loop (buffer sets, side stream, NCCL)
     sampler = ClockSampler(local_rank)
     sampler.start()
     total_ms, loss = timed(devb, args.steps, args.warmup, stages=True)
