@@ -351,15 +351,56 @@ class PeerShardedModel:
         dist.barrier(group=self.group)          # every shard is initialised before anyone reads it
         return self
 
-    def gather_full_table(self):
+    def _gather_full(self, shard):
         k, g = self.cfg.factor_num, self.world
-        mine = self.table.contiguous()
+        mine = shard.contiguous()
         parts = [torch.empty_like(mine) for _ in range(g)]
         dist.all_gather(parts, mine, group=self.group)
         full = torch.zeros(self.rows_per_rank() * g, k + 1, dtype=torch.float32, device=self.device)
         for r in range(g):
             full[r::g] = parts[r][:, :k + 1]
         return full[:self.cfg.vocabulary_size]
+
+    def gather_full_table(self):
+        """[V, K+1] on every rank (tests / checkpoints)"""
+        return self._gather_full(self.table)
+
+    # checkpoints in the reference's variable layout (vocab_block_i[id // nb] for id % nb == i), the
+    # same file a single-GPU Model writes and reads: a sharded run can be scored by one GPU and back
+    def save(self, path):
+        """collective; rank 0 writes"""
+        import os
+        nb, v, k = self.cfg.vocabulary_block_num, self.cfg.vocabulary_size, self.cfg.factor_num
+        out = {"global_step": self.global_step}
+        for name, shard in (("", self.table), ("/Adagrad", self.accum)):
+            full = self._gather_full(shard)
+            if self.rank == 0:
+                for i in range(nb):
+                    blk = torch.zeros(v // nb + 1, k + 1, dtype=torch.float32)
+                    part = full[i::nb].cpu()
+                    blk[:part.shape[0]] = part
+                    out["vocab_block_%d%s" % (i, name)] = blk
+            del full
+        if self.rank == 0:
+            os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+            torch.save(out, path)
+        dist.barrier(group=self.group)
+
+    def restore(self, path):
+        """every rank reads the file and keeps its rows"""
+        nb, v, k, g, r = (self.cfg.vocabulary_block_num, self.cfg.vocabulary_size, self.cfg.factor_num, self.world,
+                          self.rank)
+        state = torch.load(path, map_location="cpu")
+        for name, shard in (("", self.table), ("/Adagrad", self.accum)):
+            full = torch.zeros(v, k + 1, dtype=torch.float32)
+            for i in range(nb):
+                n = full[i::nb].shape[0]
+                full[i::nb] = state["vocab_block_%d%s" % (i, name)][:n]
+            mine = full[r::g]
+            shard[:mine.shape[0], :k + 1] = mine.to(self.device)
+        self.global_step = int(state.get("global_step", 0))
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
 
     def _buffers(self, n_lines, text_bytes, slot=0):
         cap = int(text_bytes // 2 + 1)

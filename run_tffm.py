@@ -7,8 +7,13 @@
 Same config file, same stdout lines ("-- Global Step: %d; Avg loss: %.5f;",
 "Average speed: ...  ex/s", "Model saved to ..."), same <file>_score outputs.  Not carried over
 (TensorFlow-runtime features, out of scope): `generate` / --export_path (SavedModel), --dist /
---protocol / --wait-for-workers (gRPC parameter server; multi-GPU runs go through torchrun, see
-DESIGN.md section 6).
+--protocol / --wait-for-workers (gRPC parameter server).  The replacement for --dist is
+
+    python -m torch.distributed.run --nproc-per-node G --master-addr 127.0.0.1 run_tffm.py train sample.cfg
+
+one process per GPU, the table sharded over NVLink peer memory: every rank takes
+its slice of each global batch of `batch_size` lines, rank 0 prints and writes the checkpoint (in the
+single-GPU layout, so `predict` runs on one GPU afterwards).
 """
 from __future__ import print_function
 
@@ -49,6 +54,74 @@ def _validation_loss(model, vdata):
         total += float(loss) * lines.n_lines
         n += lines.n_lines
     return total / max(n, 1)
+
+
+def train_sharded(cfg, monitor):
+    """`train` under torchrun: synchronous data-parallel steps on the peer-sharded table"""
+    import torch.distributed as dist
+    from fast_tffm_b200.sharded import PeerShardedModel
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    device = torch.device("cuda", torch.cuda.current_device())
+    dist.init_process_group("nccl", device_id=device)
+    model = PeerShardedModel(cfg, device=device).build(seed=int(time.time()) // 60)
+    ckpt = None if cfg.log_dir is None else _ckpt_path(cfg)
+    if ckpt is not None and os.path.exists(ckpt):
+        model.restore(ckpt)
+    say = print if rank == 0 else (lambda *a, **k: None)
+
+    def cut(lines, weights):
+        n = lines.n_lines
+        lo, hi = rank * n // world, (rank + 1) * n // world
+        return lines.select(torch.arange(lo, hi, device=device)), None if weights is None else weights[lo:hi]
+
+    def validation_loss(vdata):
+        acc = torch.zeros(2, dtype=torch.float64, device=device)
+        for lines, weights in vdata:
+            mine, w = cut(lines, weights)
+            if mine.n_lines:
+                pred = model.predict(mine)
+                loss, _ = fm_ops.fm_loss_grad(pred, model._slots[0]["labels"][:mine.n_lines].clone(), w, cfg.loss_type)
+                acc += torch.stack([loss.double() * mine.n_lines, torch.tensor(float(mine.n_lines), device=device)])
+        dist.all_reduce(acc)
+        return float(acc[0] / acc[1].clamp(min=1))
+
+    vdata = None
+    if cfg.validation_data_files:
+        say('Preloading validation data...')
+        vset = fm_data.DeviceDataset(cfg.validation_data_files, cfg.validation_weight_files, device)
+        vdata = list(vset.batches(cfg.batch_size, 1, shuffle=False))
+    say("========", "train", "(%d GPUs)" % world, "========")
+    # every rank holds the files and walks the same shuffled order; a global batch is cut into equal slices
+    seed = torch.tensor([int(time.time())], dtype=torch.int64, device=device)
+    dist.broadcast(seed, 0)
+    dataset = fm_data.DeviceDataset(cfg.train_files, cfg.weight_files, device)
+    st = time.time()
+    start_step = step_num = model.global_step
+    for lines, weights in dataset.batches(cfg.batch_size, cfg.num_epochs, shuffle=True, seed=int(seed.item())):
+        n = lines.n_lines
+        if n < world:           # a tail shorter than the number of GPUs cannot be cut into non-empty slices
+            continue
+        cur = time.time()
+        loss = model.train_step(*cut(lines, weights), global_batch=n)
+        step_num = model.global_step
+        if monitor:
+            say('speed:', n / (time.time() - cur))
+        say('-- Global Step: %d; Avg loss: %.5f;' % (step_num, loss))
+        if ckpt is not None and step_num % cfg.save_steps == 0:
+            model.save(ckpt)
+        if vdata is not None and step_num % cfg.save_steps == 0:
+            v_loss = validation_loss(vdata)          # the same number on every rank: all stop together
+            say('validation loss at step %d: %.8f' % (step_num, v_loss))
+            if v_loss < cfg.tolerance:
+                say('Loss on validation data set is below tolerance. Training completed.')
+                break
+    total = time.time() - st
+    say('Average speed: ', (step_num - start_step) * cfg.batch_size / total, ' ex/s')
+    if ckpt is not None:
+        model.save(ckpt)
+    say('Model saved to ', cfg.log_dir)
+    dist.destroy_process_group()
 
 
 def train(model, monitor, trace):
@@ -110,7 +183,8 @@ def main():
 
     if args.task == 'generate' or args.dist is not None:
         print("This build replaces the hot path only: 'generate' (TF SavedModel) and --dist (TF parameter "
-              "server) are not provided. Multi-GPU training: torchrun bench.py / fast_tffm_b200.sharded.")
+              "server) are not provided. Multi-GPU training: python -m torch.distributed.run --nproc-per-node G "
+              "--master-addr 127.0.0.1 run_tffm.py train <cfg>.")
         sys.exit(2)
 
     model = Model(args.config_file)
@@ -120,6 +194,12 @@ def main():
     if not torch.cuda.is_available():
         print("No CUDA device: the B200 build has no CPU fallback.")
         sys.exit(3)
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        if args.task != 'train':
+            print("predict runs on one GPU (the checkpoint of a sharded run is in the single-GPU layout).")
+            sys.exit(2)
+        train_sharded(model, args.monitor)
+        return
     model.build(seed=int(time.time()))
     if model.log_dir is not None and os.path.exists(_ckpt_path(model)):
         model.restore(_ckpt_path(model))     # MonitoredTrainingSession(checkpoint_dir=log_dir) restores

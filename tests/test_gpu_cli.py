@@ -69,3 +69,35 @@ def test_validation_and_tolerance_stop_early(tmp_path):
     assert re.search(r"validation loss at step 2: [0-9.]+", out.stdout)
     assert "Loss on validation data set is below tolerance. Training completed." in out.stdout
     assert len(re.findall(r"-- Global Step:", out.stdout)) == 2      # stopped at the first check
+
+
+def test_train_under_torchrun_then_predict_on_one_gpu(tmp_path):
+    """the replacement of the reference's --dist mode: torchrun, table sharded over peer memory;
+    the checkpoint it writes is read back by the single-GPU predict"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    for f in ("train_0", "train_1", "weight_0", "weight_1", "test_0"):
+        shutil.copy(os.path.join(ROOT, "data", f), tmp_path / f)
+    cfg = open(os.path.join(ROOT, "sample.cfg")).read()
+    cfg = cfg.replace("./data/", str(tmp_path) + "/").replace("./log", str(tmp_path / "log"))
+    cfg = cfg.replace("batch_size = 50000", "batch_size = 400").replace("epoch_num = 20", "epoch_num = 3")
+    cfg = cfg.replace("factor_num = 100", "factor_num = 16").replace("learning_rate = 0.01", "learning_rate = 0.05")
+    cfg = cfg.replace("#validation_files = " + str(tmp_path) + "/test_*", "validation_files = " + str(tmp_path) + "/test_*")
+    cfg = cfg.replace("save_steps = 10", "save_steps = 5").replace("#tolerance = 0.2", "tolerance = 0.000001")
+    (tmp_path / "t.cfg").write_text(cfg)
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29655", os.path.join(ROOT, "run_tffm.py"),
+                          "train", str(tmp_path / "t.cfg")], capture_output=True, text=True, env=env, cwd=ROOT)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    losses = [float(x) for x in re.findall(r"-- Global Step: \d+; Avg loss: ([0-9.]+);", out.stdout)]
+    assert len(losses) == 15 and np.mean(losses[-3:]) < np.mean(losses[:3])     # printed once (rank 0), and learning
+    v = [float(x) for x in re.findall(r"validation loss at step \d+: ([0-9.]+)", out.stdout)]
+    assert len(v) == 3 and v[-1] < v[0]
+    assert (tmp_path / "log" / "model.ckpt.pt").exists()
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "run_tffm.py"), "predict", str(tmp_path / "t.cfg")],
+                         capture_output=True, text=True, env=env, cwd=ROOT)
+    assert out.returncode == 0, out.stdout + out.stderr
+    scores = [float(x) for x in open(tmp_path / "test_0_score")]
+    assert len(scores) == 500 and np.isfinite(scores).all() and np.std(scores) > 0
