@@ -3,6 +3,9 @@
 
     python bench_configs.py cfg4            mse + per-example weights, ragged rows (1-512 nnz), K=32
     python bench_configs.py cfg5 [--quick]  predict-only sweep: batch 4K-1M x factor 8-128, 1 GPU
+    python -m torch.distributed.run --nproc-per-node G --master-addr 127.0.0.1 bench_configs.py cfg5 [--quick]
+                                            the same sweep on G GPUs, every rank scoring its own batch (weak
+                                            scaling): table sharded over NVLink peer memory, then replicated
 
 Prints one JSON line per measurement (CUDA events, device-resident inputs, >= 3 warm-up runs).
 cfg3 (2^27 vocab, K=64, 8 GPUs) is `bench.py --gpus 8 --workload cfg3` under torchrun.
@@ -78,7 +81,62 @@ def cfg4(args):
                       "loss": float(st[6:8].view(torch.float32)[0]), "data_gen_s": round(gen_s, 1)}))
 
 
+def cfg5_multi(args):
+    """cfg5 at G > 1: (a) the table row-partitioned id % G, rows read over NVLink; (b) one full table per GPU"""
+    import os
+    import torch.distributed as dist
+    from fast_tffm_b200.sharded import PeerShardedModel
+    world, rank = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"])
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    dev = torch.device("cuda", torch.cuda.current_device())
+    dist.init_process_group("nccl", device_id=dev)
+    vocab = 1 << 24
+    sizes = [65536, 1048576] if args.quick else [4096, 16384, 65536, 262144, 1048576]
+    ks = [16, 64] if args.quick else [8, 16, 32, 64, 128]
+    data = {}
+    for b in sizes:
+        text, off, _ = bench_data.criteo_batch(b, 5 + 100 * rank)
+        data[b] = PackedLines(torch.from_numpy(bench_data.pad16(text)).to(dev), torch.from_numpy(off).to(dev))
+    for mode in ("sharded", "replicated"):
+        for k in ks:
+            cfg = Model(vocabulary_size=vocab, factor_num=k, batch_size=65536, hash_feature_id=True)
+            if mode == "sharded":
+                m = PeerShardedModel(cfg, device=dev, max_nnz_per_line=39).build(seed=0)
+                run, status = (lambda b: m.predict_async(data[b])), (lambda: m._slots[0]["status"])
+            else:
+                m = cfg.build(dev, seed=0, max_nnz_per_line=39, layout="split")
+                run, status = (lambda b: m.predict_async(data[b])), (lambda: m._bufs["status"])
+            for b in sizes:
+                steps = max(3, min(args.steps, int(2e6 // b) + 3))
+                for _ in range(3):
+                    run(b)
+                dist.barrier()
+                torch.cuda.synchronize()
+                t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0.record()
+                for _ in range(steps):
+                    run(b)
+                t1.record()
+                torch.cuda.synchronize()
+                assert int(status().cpu()[0]) == -1
+                ms = torch.tensor([t0.elapsed_time(t1) / steps], device=dev)
+                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+                if rank == 0:
+                    print(json.dumps({"config": "cfg5: predict-only, 39 nnz, V=2^24, %dxB200, table %s" % (world, mode),
+                                      "metric": "fm_predict_examples_per_sec", "n_gpus": world, "table": mode,
+                                      "batch_per_gpu": b, "factor_num": k, "value": b * world / (float(ms) * 1e-3),
+                                      "ms_per_batch": float(ms)}))
+                    sys.stdout.flush()
+            del m, run, status
+            torch.cuda.empty_cache()
+            dist.barrier()
+    dist.destroy_process_group()
+
+
 def cfg5(args):
+    import os
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        return cfg5_multi(args)
     dev = torch.device("cuda", 0)
     vocab = 1 << 24
     sizes = [4096, 65536] if args.quick else [4096, 16384, 65536, 262144, 1048576]

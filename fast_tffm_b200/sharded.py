@@ -510,7 +510,8 @@ class PeerShardedModel:
             raise FmParseError(first & 7, first >> 3, line)
         return float(out[0].item())
 
-    def predict(self, lines):
+    def predict_async(self, lines):
+        """scores of this rank's lines in b["pred"], rows read from whichever GPU owns them; no host sync"""
         lib, st, cfg, k, g = self.lib, stream(), self.cfg, self.cfg.factor_num, self.world
         packed, b = self._parse(lines)
         check(lib.fm_peer_score_scatter(
@@ -518,6 +519,10 @@ class PeerShardedModel:
             self.ld, None, self.gld, None, cfg.factor_lambda, cfg.bias_lambda, 0, 0, ptr(b["pred"]), ptr(b["scal"]),
             _at(b["scal"], 1), ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st),
             "fm_peer_score_scatter")
+        return packed, b
+
+    def predict(self, lines):
+        packed, b = self.predict_async(lines)
         host = b["status"].cpu()
         first = int(host[0]) & 0xFFFFFFFFFFFFFFFF
         if first != _lib.NO_ERROR:
