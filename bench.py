@@ -215,6 +215,10 @@ def run_ours(args):
         rt.cudaDeviceGetLimit(ctypes.byref(got), 5)
         print("l2 fetch granularity ->", args.l2_fetch, "rc", rc, "now", got.value, file=sys.stderr)
 
+    # pinned staging buffers on the GPU's own NUMA node (the CPU baseline later gets every core back)
+    from fast_tffm_b200.data import bind_host_to_gpu
+    all_cpus = os.sched_getaffinity(0)
+    affinity = "off" if args.no_numa_bind else bind_host_to_gpu(local_rank)
     host, devb = [], []
     for i in range(args.batches):
         text, off, nnz = bench_data.criteo_batch(b, 1 + i, args.dist)
@@ -357,6 +361,7 @@ def run_ours(args):
     assert int(pinned_status[-1, 0]) == -1
     e2e_value = args.steps * b / (e2e_ms * 1e-3)
 
+    os.sched_setaffinity(0, all_cpus)
     base = cpu_baseline(2, 1, 16384, args.dist, os.cpu_count() or 1) if not args.no_cpu_baseline else None
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
@@ -368,7 +373,7 @@ def run_ours(args):
                 "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": KERNELS_PER_STEP[fused] * args.steps,
         "path": fused, "layout": args.layout, "unique_per_step": n_unique, "parse_ahead": ahead_on,
-        "clocks": clocks,
+        "host_affinity": affinity, "clocks": clocks,
         "final_loss": loss, "nnz_per_step": nnz,
     }
     print(json.dumps(line))
@@ -395,6 +400,8 @@ def main():
     ap.add_argument("--shard-mode", default="peer", choices=["peer", "exchange"],
                     help="N > 1: peer = rows and gradients move by NVLink loads / atomics inside the kernels; "
                          "exchange = NCCL all-to-all of ids, rows and accumulator rows")
+    ap.add_argument("--no-numa-bind", action="store_true",
+                    help="do not bind the process to the CPUs of the GPU's NUMA node before allocating pinned buffers")
     ap.add_argument("--ld", type=int, default=None, help="experiment: table row stride in floats")
     ap.add_argument("--l2-fetch", type=int, default=0, help="experiment: cudaLimitMaxL2FetchGranularity")
     args = ap.parse_args()

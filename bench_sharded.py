@@ -27,6 +27,8 @@ def run_sharded(args, cfg, workload_config):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     dist.init_process_group("nccl", device_id=dev)
+    from fast_tffm_b200.data import bind_host_to_gpu
+    affinity = "off" if args.no_numa_bind else bind_host_to_gpu(local_rank)   # before the pinned staging buffers
     b, k = cfg["batch"], cfg["factor_num"]
     model = Model(vocabulary_size=cfg["vocab"], factor_num=k, batch_size=b * world, hash_feature_id=True,
                   loss_type=cfg["loss_type"], learning_rate=cfg["learning_rate"],
@@ -185,7 +187,7 @@ def run_sharded(args, cfg, workload_config):
                     "d2h_bytes_per_step": 8 * world, "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": (9 if peer else 20) * args.steps, "shard_mode": args.shard_mode, "parse_ahead": ahead_on,
             "stage_ms_rank0": {k_: round(v, 4) for k_, v in stage_ms.items()},
-            "clocks": clocks, "final_loss": loss, "nnz_per_rank": nnz, "unique_per_rank": nuniq,
+            "host_affinity_rank0": affinity, "clocks": clocks, "final_loss": loss, "nnz_per_rank": nnz, "unique_per_rank": nuniq,
         }
         print(json.dumps(line))
     dist.barrier()

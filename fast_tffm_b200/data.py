@@ -139,3 +139,33 @@ class DeviceDataset:
             for i in range(0, n, batch_size):
                 idx = order[i:i + batch_size]
                 yield self.lines.select(idx), (None if self.weights is None else self.weights[idx])
+
+
+def bind_host_to_gpu(index=None):
+    """Pin the calling thread (and the threads it starts later) to the CPUs of the NUMA node the GPU hangs
+    off, so that pinned staging buffers allocated afterwards are local to the GPU's PCIe root and the
+    H2D copies of one process per GPU do not all cross the socket interconnect.  Call it before the
+    first pinned allocation.  Returns a one-line description of what was done (nothing is done, and
+    the reason returned, when the topology is not visible -- e.g. inside some containers)."""
+    import os
+    import torch
+    index = torch.cuda.current_device() if index is None else index
+    try:
+        p = torch.cuda.get_device_properties(index)
+        bus = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        with open("/sys/bus/pci/devices/%s/numa_node" % bus) as f:
+            node = int(f.read())
+        if node < 0:
+            return "gpu %s: numa node not reported" % bus
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = os.sched_getaffinity(0) & cpus
+        if not allowed:
+            return "gpu %s: none of numa node %d's cpus are available to this process" % (bus, node)
+        os.sched_setaffinity(0, allowed)
+        return "gpu %s: bound to %d cpus of numa node %d" % (bus, len(allowed), node)
+    except (OSError, ValueError, AttributeError) as e:
+        return "not bound (%s)" % e
