@@ -408,6 +408,187 @@ fused_adagrad_claim_kernel(float* __restrict__ table, float* __restrict__ accum,
   }
 }
 
+// ---- rows wider than 96 float4 chunks (factor_num > 378) -------------------------------------
+// The same arithmetic with plain loops: one warp per example (scorer) or per row (update), lane
+// l owns chunks l, l + 32, ...; an example's column totals sit in shared memory (one float4 per
+// chunk per warp) instead of registers.  Correctness first: such widths are rare and every id
+// then moves kilobytes, so the walk is bandwidth-bound anyway.
+constexpr size_t kWideSmemMax = 200 * 1024;
+
+template <bool PEER>
+__global__ void __launch_bounds__(kWarps * 32)
+fused_score_scatter_wide_kernel(const int64_t* __restrict__ ids, const int32_t* __restrict__ local,
+                                const float* __restrict__ vals, const int32_t* __restrict__ poses,
+                                const float* __restrict__ labels, const float* __restrict__ weights, int64_t batch,
+                                int K, const float* __restrict__ table, int64_t ld, float lam_f, float lam_b,
+                                int loss_kind, float inv_batch, float* __restrict__ pred, float* __restrict__ gacc,
+                                int64_t gacc_ld, float* __restrict__ partials,
+                                const unsigned long long* __restrict__ guard, const PeerPtrs peers) {
+  extern __shared__ float4 s_tot[];   // [warps][vc_acc]
+  __shared__ float s_loss[kWarps], s_reg[kWarps];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+  const int vc_table = (K + 4) >> 2, vc_acc = (K + 6) >> 2;
+  float4* S = s_tot + (size_t)warp * vc_acc;
+  const bool active = !(guard && *guard != kNoError);
+  float loss_acc = 0.f, reg_acc = 0.f;
+
+  for (int64_t i = (int64_t)blockIdx.x * warps + warp; active && i < batch; i += (int64_t)gridDim.x * warps) {
+    const int start = poses[i], end = poses[i + 1];
+    for (int chunk = lane; chunk < vc_acc; chunk += 32) S[chunk] = make_float4(0.f, 0.f, 0.f, 0.f);
+    float q = 0.f, bias_dot = 0.f, bias_sq = 0.f, fac_sq = 0.f;
+    for (int j = start; j < end; ++j) {
+      const float x = vals[j];
+      const float* rowp;
+      if (PEER) {
+        int owner; int64_t row;
+        split_id(ids[j], peers.n, &owner, &row);
+        rowp = peers.table[owner] + row * ld;
+      } else {
+        rowp = table + ids[j] * ld;
+      }
+      for (int chunk = lane; chunk < vc_table; chunk += 32) {
+        float4 v = ldg4(rowp + 4 * chunk);
+        if (chunk == 0) {
+          bias_dot = fmaf(x, v.x, bias_dot);
+          bias_sq = fmaf(v.x, v.x, bias_sq);
+          v.x = 0.f;
+        }
+        const float a0 = x * v.x, a1 = x * v.y, a2 = x * v.z, a3 = x * v.w;
+        float4 t = S[chunk];
+        t.x += a0; t.y += a1; t.z += a2; t.w += a3;
+        S[chunk] = t;
+        q = fmaf(a0, a0, fmaf(a1, a1, fmaf(a2, a2, fmaf(a3, a3, q))));
+        fac_sq = fmaf(v.x, v.x, fmaf(v.y, v.y, fmaf(v.z, v.z, fmaf(v.w, v.w, fac_sq))));
+      }
+    }
+    float second = 0.f;
+    for (int chunk = lane; chunk < vc_table; chunk += 32) {
+      const float4 t = S[chunk];
+      second += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w;
+    }
+    const float p = warp_sum(bias_dot + 0.5f * (second - q));
+    reg_acc += warp_sum(0.5f * lam_f * fac_sq + 0.5f * lam_b * bias_sq);
+    if (labels == nullptr) {
+      if (lane == 0) pred[i] = p;
+      continue;
+    }
+    const float y = labels[i], w = weights ? weights[i] : 1.0f;
+    float l, d;
+    if (loss_kind == FM_LOSS_LOGISTIC) {
+      l = fmaxf(p, 0.f) - p * y + log1pf(expf(-fabsf(p)));
+      d = 1.0f / (1.0f + expf(-p)) - y;
+    } else {
+      l = (p - y) * (p - y);
+      d = 2.0f * (p - y);
+    }
+    const float pg = w * d * inv_batch;
+    if (lane == 0) {
+      pred[i] = p;
+      loss_acc += w * l;
+    }
+    for (int j = start; j < end; ++j) {
+      const float x = vals[j], pgx = pg * x;
+      float* arow;
+      if (PEER) {
+        int owner; int64_t row;
+        split_id(ids[j], peers.n, &owner, &row);
+        arow = peers.gtab[owner] + row * gacc_ld;
+        if (lane == 0) red_or_sys(peers.touched[owner] + (row >> 5), 1u << (row & 31));
+      } else {
+        arow = gacc + (local ? (int64_t)local[j] : ids[j]) * gacc_ld;
+      }
+      for (int chunk = lane; chunk < vc_acc; chunk += 32) {
+        const int col = 4 * chunk;
+        if (col > K + 2) continue;
+        const float4 t = S[chunk];   // chunks past the table row hold zeros
+        float o[4] = {pgx * t.x, pgx * t.y, pgx * t.z, pgx * t.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int cc = col + e;
+          if (cc == 0) o[e] = pgx;                 // C
+          else if (cc == K + 1) o[e] = pgx * x;    // D
+          else if (cc == K + 2) o[e] = 1.0f;       // cnt
+          else if (cc > K + 2) o[e] = 0.f;
+        }
+        if (PEER) red_add_v4_sys(arow + col, o[0], o[1], o[2], o[3]);
+        else red_add_v4(arow + col, o[0], o[1], o[2], o[3]);
+      }
+    }
+  }
+  if (lane == 0) { s_loss[warp] = loss_acc; s_reg[warp] = reg_acc; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, b = 0.f;
+    for (int w = 0; w < warps; ++w) { a += s_loss[w]; b += s_reg[w]; }
+    partials[blockIdx.x] = a;
+    partials[gridDim.x + blockIdx.x] = b;
+  }
+  if (PEER) __threadfence_system();
+}
+
+// CLAIM: `rows` are occurrences, accumulator row = g + id * g_ld, first to swap cnt to zero applies it;
+// otherwise `rows` are distinct ids and accumulator row u belongs to rows[u]
+template <bool CLAIM>
+__global__ void __launch_bounds__(256)
+fused_adagrad_wide_kernel(float* __restrict__ table, float* __restrict__ accum, int64_t ld,
+                          const int64_t* __restrict__ rows, int64_t n_max, const int64_t* __restrict__ n_dev, int K,
+                          float* __restrict__ g, int64_t g_ld, float lr, float rf, float rb,
+                          const unsigned long long* __restrict__ guard, int discard_on_guard) {
+  const bool tripped = guard && *guard != kNoError;
+  if (tripped && !(CLAIM && discard_on_guard)) return;
+  const int64_t n = n_dev ? min(*n_dev, n_max) : n_max;
+  const int lane = threadIdx.x & 31;
+  const int vc_table = (K + 4) >> 2, vc_acc = (K + 6) >> 2;
+  const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
+  for (int64_t u = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); u < n; u += warps_total) {
+    const int64_t id = rows[u];
+    const int64_t row = id * ld, grow = (CLAIM ? id : u) * g_ld;
+    float cnt = 0.f, D = 0.f;
+    if (lane == 0) {
+      cnt = g[grow + K + 2];
+      if (CLAIM && cnt != 0.f) cnt = atomicExch(g + grow + K + 2, 0.f);
+      D = g[grow + K + 1];
+    }
+    cnt = __shfl_sync(kFull, cnt, 0);
+    D = __shfl_sync(kFull, D, 0);
+    if (CLAIM && cnt == 0.f) continue;   // another occurrence of this row got there first
+    const float fac_scale = cnt * rf - D, bias_scale = cnt * rb;
+    for (int chunk = lane; chunk < vc_acc; chunk += 32) {
+      const float4 a = *reinterpret_cast<const float4*>(g + grow + 4 * chunk);
+      if (chunk < vc_table && !tripped) {
+        const float4 w = *reinterpret_cast<const float4*>(table + row + 4 * chunk);
+        const float4 h = *reinterpret_cast<const float4*>(accum + row + 4 * chunk);
+        const float av[4] = {a.x, a.y, a.z, a.w};
+        float wv[4] = {w.x, w.y, w.z, w.w};
+        float hv[4] = {h.x, h.y, h.z, h.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int col = 4 * chunk + e;
+          float gr = 0.f;
+          if (col == 0) gr = fmaf(bias_scale, wv[e], av[e]);
+          else if (col <= K) gr = fmaf(wv[e], fac_scale, av[e]);
+          hv[e] = fmaf(gr, gr, hv[e]);
+          wv[e] = fmaf(-lr * gr, rsqrtf(hv[e]), wv[e]);
+        }
+        *reinterpret_cast<float4*>(table + row + 4 * chunk) = make_float4(wv[0], wv[1], wv[2], wv[3]);
+        *reinterpret_cast<float4*>(accum + row + 4 * chunk) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+      }
+      if (4 * chunk <= K + 2) *reinterpret_cast<float4*>(g + grow + 4 * chunk) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+}
+
+// warps per block such that the column totals fit in shared memory; 0 = the row does not fit at all
+static inline int wide_warps(int64_t factor_num, size_t* smem) {
+  const size_t per_warp = (size_t)((factor_num + 6) / 4) * sizeof(float4);
+  if (per_warp > kWideSmemMax) return 0;
+  size_t w = (64 * 1024) / per_warp;
+  if (w > (size_t)kWarps) w = kWarps;
+  if (w < 1) w = 1;
+  *smem = w * per_warp;
+  return (int)w;
+}
+
 // bitmap of touched rows -> list of row numbers (and the bitmap is cleared on the way)
 struct TouchedIn {
   unsigned* bits; int64_t n_words;
@@ -489,11 +670,25 @@ FM_EXPORT int fm_fused_score_scatter(const int64_t* feature_ids, const int32_t* 
   const int64_t chunks = (factor_num + 6) / 4;
   const int gs = chunks <= 32 ? (int)chunks : 32;
   const int t = (int)((chunks + gs - 1) / gs);
-  if (t > 3) return fm_fail(FM_E_LIMIT, "fm_fused_score_scatter: factor_num %lld too large", (long long)factor_num);
   const int blocks = fused_blocks(batch);
   float* partials = reinterpret_cast<float*>(workspace);
   const int64_t denom = loss_batch > 0 ? loss_batch : batch;
   const float inv_batch = denom > 0 ? 1.0f / (float)denom : 0.f;
+  if (t > 3) {  // wider than 96 chunks: the generic kernel
+    size_t smem = 0;
+    const int warps = wide_warps(factor_num, &smem);
+    if (warps == 0) return fm_fail(FM_E_LIMIT, "fm_fused_score_scatter: factor_num %lld too large", (long long)factor_num);
+    FM_CUDA(cudaFuncSetAttribute(fused_score_scatter_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kWideSmemMax));
+    fused_score_scatter_wide_kernel<false><<<blocks, warps * 32, smem, stream>>>(
+        feature_ids, local_ids, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, table, table_ld,
+        factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, gacc, gacc_ld, partials,
+        reinterpret_cast<const unsigned long long*>(guard), PeerPtrs());
+    FM_LAUNCH_CHECK();
+    reduce2_kernel<<<1, 256, 0, stream>>>(partials, blocks, inv_batch, loss, reg_score);
+    FM_LAUNCH_CHECK();
+    return FM_OK;
+  }
 #define CALL(T)                                                                                                   \
   fused_score_scatter_kernel<T, false><<<blocks, kWarps * 32, 0, stream>>>(                                       \
       feature_ids, local_ids, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, table, table_ld, \
@@ -519,8 +714,15 @@ FM_EXPORT int fm_fused_adagrad(float* table, float* accum, int64_t table_ld, con
   FM_REQUIRE(table && accum && ori_ids && gacc, "fm_fused_adagrad: null pointer");
   FM_REQUIRE((((uintptr_t)table | (uintptr_t)accum | (uintptr_t)gacc) & 15) == 0, "fm_fused_adagrad: 16-byte alignment required");
   Shape sh;
-  if (!pick_shape((factor_num + 6) / 4, &sh))
-    return fm_fail(FM_E_LIMIT, "fm_fused_adagrad: factor_num %lld too large", (long long)factor_num);
+  if (!pick_shape((factor_num + 6) / 4, &sh)) {  // wider than 96 chunks: the generic kernel, a warp per row
+    int64_t wide_blocks = (n_unique + 7) / 8;
+    if (wide_blocks > 148 * 16) wide_blocks = 148 * 16;
+    fused_adagrad_wide_kernel<false><<<(unsigned)wide_blocks, 256, 0, stream>>>(
+        table, accum, table_ld, ori_ids, n_unique, n_unique_dev, (int)factor_num, gacc, gacc_ld, learning_rate,
+        reg_grad * factor_lambda, reg_grad * bias_lambda, reinterpret_cast<const unsigned long long*>(guard), 0);
+    FM_LAUNCH_CHECK();
+    return FM_OK;
+  }
   const int64_t groups_per_block = 256 / sh.lpr;
   int64_t blocks = (n_unique + groups_per_block - 1) / groups_per_block;
   if (blocks > 148 * 16) blocks = 148 * 16;
@@ -549,7 +751,16 @@ FM_EXPORT int fm_fused_adagrad_claim(float* table, float* accum, int64_t table_l
   const int64_t chunks = (factor_num + 6) / 4;
   const int gs = chunks <= 32 ? (int)chunks : 32;
   const int t = (int)((chunks + gs - 1) / gs);
-  if (t > 3) return fm_fail(FM_E_LIMIT, "fm_fused_adagrad_claim: factor_num %lld too large", (long long)factor_num);
+  if (t > 3) {  // wider than 96 chunks: the generic kernel, a warp per occurrence
+    int64_t wide_blocks = (n + 7) / 8;
+    if (wide_blocks > 148 * 16) wide_blocks = 148 * 16;
+    fused_adagrad_wide_kernel<true><<<(unsigned)wide_blocks, 256, 0, stream>>>(
+        table, accum, table_ld, rows, n, n_dev, (int)factor_num, gtab, gtab_ld, learning_rate,
+        reg_grad * factor_lambda, reg_grad * bias_lambda, reinterpret_cast<const unsigned long long*>(guard),
+        discard_on_guard);
+    FM_LAUNCH_CHECK();
+    return FM_OK;
+  }
   const int64_t rows_per_block = 8 * (32 / gs);
   int64_t blocks = (n + rows_per_block - 1) / rows_per_block;
   if (blocks > 148 * 16) blocks = 148 * 16;
@@ -600,13 +811,27 @@ FM_EXPORT int fm_peer_score_scatter(const int64_t* feature_ids, const float* fea
   const int64_t chunks = (factor_num + 6) / 4;
   const int gs = chunks <= 32 ? (int)chunks : 32;
   const int t = (int)((chunks + gs - 1) / gs);
-  if (t > 3) return fm_fail(FM_E_LIMIT, "fm_peer_score_scatter: factor_num %lld too large", (long long)factor_num);
   const int blocks = fused_blocks(batch);
   float* partials = reinterpret_cast<float*>(workspace);
   const int64_t denom = loss_batch > 0 ? loss_batch : batch;
   const float inv_batch = denom > 0 ? 1.0f / (float)denom : 0.f;
   // gacc != NULL tells the kernel to scatter; the real targets come from `peers`
   float* scatter_flag = training ? peers.gtab[0] : nullptr;
+  if (t > 3) {  // wider than 96 chunks: the generic kernel
+    size_t smem = 0;
+    const int warps = wide_warps(factor_num, &smem);
+    if (warps == 0) return fm_fail(FM_E_LIMIT, "fm_peer_score_scatter: factor_num %lld too large", (long long)factor_num);
+    FM_CUDA(cudaFuncSetAttribute(fused_score_scatter_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kWideSmemMax));
+    fused_score_scatter_wide_kernel<true><<<blocks, warps * 32, smem, stream>>>(
+        feature_ids, nullptr, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, peers.table[0],
+        table_ld, factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, scatter_flag, gtab_ld, partials,
+        reinterpret_cast<const unsigned long long*>(guard), peers);
+    FM_LAUNCH_CHECK();
+    reduce2_kernel<<<1, 256, 0, stream>>>(partials, blocks, inv_batch, loss, reg_score);
+    FM_LAUNCH_CHECK();
+    return FM_OK;
+  }
 #define CALL(T)                                                                                                     \
   fused_score_scatter_kernel<T, true><<<blocks, kWarps * 32, 0, stream>>>(                                          \
       feature_ids, nullptr, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, peers.table[0],   \

@@ -89,15 +89,21 @@ score_kernel(const int32_t* __restrict__ fids, const float* __restrict__ params,
   const int64_t i = (int64_t)blockIdx.x * kWarps + warp;
   float reg = 0.f;
   if (i < batch) {
-    float S[T], Q[T], bias_dot, bias_sq, fac_sq;
-    accumulate_example<LPR, T>(fids, params, ld, vals, poses[i], poses[i + 1], K, lane, S, Q, bias_dot,
-                               bias_sq, fac_sq);
-    float second = 0.f;
+    // the second-order term is a sum over factor columns, so any K is walked in slabs of LPR * T columns
+    // (one slab for every K <= 256; the rows are re-walked per slab beyond that)
+    float S[T], Q[T], bias_dot = 0.f, bias_sq = 0.f, fac_sq = 0.f, second = 0.f;
+    for (int k0 = 0; k0 < K || k0 == 0; k0 += LPR * T) {
+      float bd, bs, fs;
+      accumulate_example<LPR, T>(fids, params + k0, ld, vals, poses[i], poses[i + 1], min(K - k0, LPR * T), lane, S, Q,
+                                 bd, bs, fs);
+      if (k0 == 0) { bias_dot = bd; bias_sq = bs; }   // column k0 of the row is the bias only in the first slab
+      fac_sq += fs;
 #pragma unroll
-    for (int t = 0; t < T; ++t) {
-      const float s = reduce_row_groups<LPR>(S[t]);
-      const float q = reduce_row_groups<LPR>(Q[t]);
-      second += s * s - q;
+      for (int t = 0; t < T; ++t) {
+        const float s = reduce_row_groups<LPR>(S[t]);
+        const float q = reduce_row_groups<LPR>(Q[t]);
+        second += s * s - q;
+      }
     }
     if (lane >= LPR) second = 0.f;  // every row group now holds the same totals: count them once
     const float p = warp_sum(bias_dot + 0.5f * second);
@@ -129,35 +135,39 @@ grad_kernel(const int32_t* __restrict__ fids, const float* __restrict__ params, 
   const int64_t i = (int64_t)blockIdx.x * kWarps + warp;
   if (i >= batch) return;
   const int start = poses[i], end = poses[i + 1];
-  float S[T], Q[T], bias_dot, bias_sq, fac_sq;
-  accumulate_example<LPR, T>(fids, params, ld, vals, start, end, K, lane, S, Q, bias_dot, bias_sq, fac_sq);
-#pragma unroll
-  for (int t = 0; t < T; ++t) S[t] = reduce_row_groups<LPR>(S[t]);
   const float pg = pred_grad[i];
   const float reg_grad = reg_grad_dev ? __ldg(reg_grad_dev) : reg_grad_host;
   const float rf = reg_grad * lam_f, rb = reg_grad * lam_b;
-  for (int base = start; base < end; base += 32) {
-    const int j = base + lane;
-    const int my_fid = j < end ? fids[j] : 0;
-    const float my_x = j < end ? vals[j] : 0.f;
-    const int rows_here = min(32, end - base);
-#pragma unroll 4
-    for (int s = 0; s < LPR; ++s) {
-      const int jj = s * RPW + r;
-      if (s * RPW >= rows_here) break;
-      const int fid = __shfl_sync(kFull, my_fid, jj);
-      const float x = __shfl_sync(kFull, my_x, jj);
-      if (jj < rows_here) {
-        const float* row = params + (int64_t)fid * ld;
-        float* grow = grad + (int64_t)fid * ld;
-        if (c == 0) atomicAdd(grow, fmaf(pg, x, rb * __ldg(row)));          // :88-89
+  // column k's gradient needs only column k's factor sum: any K is walked in slabs of LPR * T columns
+  for (int k0 = 0; k0 < K || k0 == 0; k0 += LPR * T) {
+    const int kk = min(K - k0, LPR * T);
+    float S[T], Q[T], bias_dot, bias_sq, fac_sq;
+    accumulate_example<LPR, T>(fids, params + k0, ld, vals, start, end, kk, lane, S, Q, bias_dot, bias_sq, fac_sq);
 #pragma unroll
-        for (int t = 0; t < T; ++t) {
-          const int k = c + t * LPR;
-          if (k < K) {
-            const float v = __ldg(row + 1 + k);
-            // reg_grad*lf*t - pg*x*x*t + pg*x*s_k                           // :96-97
-            atomicAdd(grow + 1 + k, rf * v - pg * x * x * v + pg * x * S[t]);
+    for (int t = 0; t < T; ++t) S[t] = reduce_row_groups<LPR>(S[t]);
+    for (int base = start; base < end; base += 32) {
+      const int j = base + lane;
+      const int my_fid = j < end ? fids[j] : 0;
+      const float my_x = j < end ? vals[j] : 0.f;
+      const int rows_here = min(32, end - base);
+#pragma unroll 4
+      for (int s = 0; s < LPR; ++s) {
+        const int jj = s * RPW + r;
+        if (s * RPW >= rows_here) break;
+        const int fid = __shfl_sync(kFull, my_fid, jj);
+        const float x = __shfl_sync(kFull, my_x, jj);
+        if (jj < rows_here) {
+          const float* row = params + (int64_t)fid * ld + k0;
+          float* grow = grad + (int64_t)fid * ld + k0;
+          if (c == 0 && k0 == 0) atomicAdd(grow, fmaf(pg, x, rb * __ldg(row)));          // :88-89
+#pragma unroll
+          for (int t = 0; t < T; ++t) {
+            const int k = c + t * LPR;
+            if (k < kk) {
+              const float v = __ldg(row + 1 + k);
+              // reg_grad*lf*t - pg*x*x*t + pg*x*s_k                           // :96-97
+              atomicAdd(grow + 1 + k, rf * v - pg * x * x * v + pg * x * S[t]);
+            }
           }
         }
       }
@@ -184,8 +194,7 @@ int dispatch(int64_t K, Args... args) {
   if (K <= 96) return Launcher<32, 3>::run(args...);
   if (K <= 128) return Launcher<32, 4>::run(args...);
   if (K <= 192) return Launcher<32, 6>::run(args...);
-  if (K <= 256) return Launcher<32, 8>::run(args...);
-  return fm_fail(FM_E_LIMIT, "factor_num %lld > 256 is not supported", (long long)K);
+  return Launcher<32, 8>::run(args...);   // K > 256: the kernels walk the columns in slabs of 256
 }
 
 template <int LPR, int T>

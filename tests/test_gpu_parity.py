@@ -456,6 +456,39 @@ def test_train_steps_match_reference_model(criteo_lines, loss_type, hashed, path
         assert not m.gtab.any()
 
 
+@pytest.mark.parametrize("k", [0, 1, 2, 5, 13, 29, 30, 61, 100, 122, 123, 128, 250, 257, 378, 379, 500, 1030])
+def test_train_steps_any_factor_num(k):
+    """the reference takes any factor_num: lane-group shapes (K+3 = 1..32 chunks), the 2- and 3-chunk-per-lane
+    shapes, the 256-column slabs of fm_scorer / fm_grad and the wide-row kernels (K > 378), all paths and both
+    table layouts against the oracle model; ids repeat inside an example and across examples"""
+    rng = np.random.default_rng(100 + k)
+    vocab, bs = 997, 64
+    lines = []
+    for i in range(2 * bs):
+        n = int(rng.integers(0, 12))
+        ids = rng.integers(0, 40 if i % 3 else vocab, n)        # a hot set: many repeats
+        toks = ["%d:%s" % (t, "%.3f" % rng.normal()) if rng.random() < 0.7 else "%d" % t for t in ids]
+        lines.append(("%d " % rng.integers(0, 2) + " ".join(toks)).rstrip().encode())
+    flat = rng.uniform(-0.05, 0.05, (vocab, k + 1)).astype(np.float32)
+    kw = dict(factor_lambda=3e-3, bias_lambda=2e-3, loss_type="logistic")
+    w = rng.uniform(0.5, 2.0, bs).astype(np.float32)
+    for path, layout in (("claim", "interleaved"), ("claim", "split"), ("fused", "split"), ("composed", "split")):
+        ref = O.RefModel(vocab, 7, k, flat, batch_size=bs, lr=0.05, init_acc=0.1, **kw)
+        m = Model(vocabulary_size=vocab, vocabulary_block_num=7, factor_num=k, batch_size=bs, learning_rate=0.05,
+                  adagrad_init_accumulator=0.1, **kw).build(DEV, init_table=flat, layout=layout)
+        for step in range(2):
+            sl = slice(step * bs, (step + 1) * bs)
+            e = ref.train_step(lines[sl], w if step else None)
+            got = m.train_step(lines[sl], w if step else None, path=path)
+            np.testing.assert_allclose(got, e["loss"], rtol=RTOL, err_msg="%s %s" % (path, layout))
+            np.testing.assert_allclose(m._bufs["pred"][:bs].cpu().numpy(), e["pred"], rtol=1e-4, atol=1e-6)
+        np.testing.assert_allclose(m.table[:, :k + 1].cpu().numpy(), ref.flat_table(), rtol=1e-4, atol=1e-7,
+                                   err_msg="%s %s" % (path, layout))
+        np.testing.assert_allclose(m.accum[:, :k + 1].cpu().numpy(), ref.flat_acc(), rtol=1e-4, atol=1e-9)
+        pred = m.predict(lines[:bs], path="composed" if path == "composed" else "claim")
+        np.testing.assert_allclose(pred.cpu().numpy(), ref.predict(lines[:bs]), rtol=1e-4, atol=1e-6)
+
+
 def test_parse_ahead_pipeline_matches_inline_steps(criteo_lines):
     """parse of batch t+1 on a side stream under batch t's kernels: same table as step-by-step"""
     lines, _ = criteo_lines

@@ -32,6 +32,26 @@ def test_nccl_ranks_equal_single_process(criteo_lines, tmp_path, world, mode):
     np.testing.assert_allclose(got, ref.predict(lines[:400]), rtol=1e-4, atol=1e-6)
 
 
+@pytest.mark.parametrize("mode,k", [("peer", 5), ("peer", 100), ("peer", 400), ("exchange", 100), ("exchange", 400)])
+def test_sharded_steps_other_factor_nums(criteo_lines, tmp_path, mode, k):
+    """row widths beyond the benchmark's: 2 and 26 chunks per row, and the wide-row kernels (K > 378)"""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    lines, weights = criteo_lines
+    rng = np.random.default_rng(50 + k)
+    cfg_kw = dict(vocabulary_size=170003, factor_num=k, batch_size=200, hash_feature_id=False, factor_lambda=2e-3,
+                  bias_lambda=1e-3, learning_rate=0.05, adagrad_init_accumulator=0.1, loss_type="mse")
+    init = rng.uniform(-0.01, 0.01, (cfg_kw["vocabulary_size"], k + 1)).astype(np.float32)
+    port = 29820 + (k % 97) + (100 if mode == "peer" else 0)
+    mp.spawn(shard_worker.run, args=(2, port, "nccl", lines, weights, cfg_kw, init, 2, str(tmp_path), mode),
+             nprocs=2, join=True)
+    ref, exp_losses = _reference(lines, weights, cfg_kw, init, 2, 2)
+    np.testing.assert_allclose(np.load(tmp_path / "losses.npy"), exp_losses, rtol=1e-5)
+    np.testing.assert_allclose(np.load(tmp_path / "table.npy"), ref.flat_table(), rtol=1e-4, atol=1e-7)
+    got = np.concatenate([np.load(tmp_path / ("pred%d.npy" % r)) for r in range(2)])
+    np.testing.assert_allclose(got, ref.predict(lines[:200]), rtol=1e-4, atol=1e-6)
+
+
 @pytest.mark.parametrize("mode", ["exchange", "peer"])
 def test_parse_error_on_one_rank_voids_the_step_everywhere(criteo_lines, tmp_path, mode):
     if torch.cuda.device_count() < 2:
