@@ -247,6 +247,10 @@ class Model(object):
         if b is not None and b["lines"] >= n_lines and b["cap"] >= cap:
             return b
         lib, dev = load(), self.device
+        if b is not None:
+            # growing: work enqueued on either stream may still use the old set, whose memory goes back to
+            # the allocator below (it only tracks the stream that allocated it)
+            torch.cuda.synchronize(dev)
         lines = max(n_lines, b["lines"] if b else 0)
         cap = max(cap, b["cap"] if b else 0)
         f32, i32, i64 = torch.float32, torch.int32, torch.int64

@@ -410,6 +410,8 @@ class PeerShardedModel:
         if b is not None and b["lines"] >= n_lines and b["cap"] >= cap:
             return b
         lib, dev = self.lib, self.device
+        if b is not None:   # growing: the side stream may still be using the old set (see Model._buffers_one)
+            torch.cuda.synchronize(dev)
         lines, cap = max(n_lines, b["lines"] if b else 0), max(cap, b["cap"] if b else 0)
         f32, i32, i64 = torch.float32, torch.int32, torch.int64
         e = lambda n, dt: torch.empty(n, dtype=dt, device=dev)

@@ -513,6 +513,49 @@ def test_parse_ahead_pipeline_matches_inline_steps(criteo_lines):
     np.testing.assert_allclose(a.table[:, :k + 1].cpu().numpy(), b.table[:, :k + 1].cpu().numpy(), rtol=1e-5, atol=1e-8)
 
 
+def test_host_batch_pipeline_matches_step_by_step(criteo_lines):
+    """copy | parse | train pipeline over host batches (pinned and not, growing sizes, weights on some, one
+    batch that does not parse): same losses and the same table as train_step on each batch in turn"""
+    from fast_tffm_b200.pipeline import HostBatchPipeline
+    lines, weights = criteo_lines
+    rng = np.random.default_rng(44)
+    vocab, k = 200003, 16
+    flat = rng.uniform(-0.01, 0.01, (vocab, k + 1)).astype(np.float32)
+    kw = dict(vocabulary_size=vocab, factor_num=k, batch_size=300, learning_rate=0.05, loss_type="logistic",
+              factor_lambda=1e-3, bias_lambda=1e-3)
+    a = Model(**kw).build(DEV, init_table=flat)
+    b = Model(**kw).build(DEV, init_table=flat)
+    sizes = [100, 300, 250, 700, 300, 50, 1, 150, 149]
+    cuts = np.concatenate([[0], np.cumsum(sizes)])
+    batches = []
+    for i, n in enumerate(sizes):
+        ls = list(lines[cuts[i]:cuts[i + 1]])
+        if i == 4:
+            ls[17] = ls[17] + " 12:oops"
+        w = torch.from_numpy(np.float32(weights[cuts[i]:cuts[i + 1]])) if i % 2 else None
+        batches.append((fm_ops.pack_lines(ls, pin_memory=(i % 3 != 0)), w, ls))
+    pipe = HostBatchPipeline(a)
+    results = list(pipe.run((p, w) for p, w, _ in batches))
+    assert [r.n_lines for r in results] == sizes
+    for i, (p, w, ls) in enumerate(batches):
+        if i == 4:
+            with pytest.raises(fm_ops.FmParseError, match="Invalid feature value") as e:
+                results[i].loss()
+            assert "12:oops" in str(e.value)
+            with pytest.raises(fm_ops.FmParseError):
+                b.train_step(ls, w)
+            continue
+        np.testing.assert_allclose(results[i].loss(), b.train_step(ls, None if w is None else w.numpy()), rtol=1e-6)
+    pipe.drain()
+    np.testing.assert_allclose(a.table[:, :k + 1].cpu().numpy(), b.table[:, :k + 1].cpu().numpy(), rtol=1e-5, atol=1e-8)
+    assert a.global_step == len(sizes)
+    # a second run on the same pipeline reuses the staging slots
+    more = list(pipe.run((p, w) for p, w, _ in batches[:3]))
+    for i, r in enumerate(more):
+        np.testing.assert_allclose(r.loss(), b.train_step(batches[i][2], None if batches[i][1] is None else batches[i][1].numpy()),
+                                   rtol=1e-6)
+
+
 def test_failed_parse_leaves_the_table_untouched():
     m = Model(vocabulary_size=100, factor_num=4, batch_size=2).build(DEV, seed=0)
     before = m.table.clone()
