@@ -141,6 +141,159 @@ class DeviceDataset:
                 yield self.lines.select(idx), (None if self.weights is None else self.weights[idx])
 
 
+class SegmentedDataset:
+    """DeviceDataset for training files that do not fit in HBM (or should not sit there): the files are
+    streamed through the device in segments of about `segment_bytes` of text.
+
+    A segment is read straight into pinned host memory (cut at its last newline; the cut-off tail opens
+    the next segment; files follow each other inside a segment), copied into one half of a device arena,
+    split into lines there (`fm_split_lines`) and shuffled by a device `randperm`; batches are index
+    selections over the arena, exactly `batch_size` lines each -- the lines a segment leaves over open the
+    next segment's first batch, which is why the arena has two halves -- and only the very last batch of
+    the run may be smaller (tffm/fm_model.py:57).  The shuffle window is a segment (>= the reference's
+    3 - 4.5 batches whenever a segment holds that many lines).  Weight files are read per file through
+    the parser, as in DeviceDataset.
+    """
+
+    def __init__(self, train_files, weight_files=(), device=None, segment_bytes=256 << 20):
+        import torch
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        if weight_files and len(weight_files) != len(train_files):
+            raise ValueError('The numbers of train files and weight files do not match.')
+        self.train_files, self.weight_files = list(train_files), list(weight_files)
+        self.segment_bytes = (int(segment_bytes) + 15) // 16 * 16
+        self._arena = self._pinned = None
+
+    def _file_weights(self, path):
+        import torch
+        from . import fm_ops
+        with open(path, "rb") as f:
+            lines = f.read().split(b"\n")
+        if lines and lines[-1] == b"":
+            lines.pop()
+        labels, sizes, _, _ = fm_ops.fm_parser(fm_ops.pack_lines(lines).to(self.device, non_blocking=False), 1)
+        if int(sizes.sum()) != 0:
+            raise ValueError("%s: expected one number per line" % path)
+        return labels
+
+    def _segments(self, order):
+        """yields (n_bytes, [(file index, complete lines of that file in this segment are counted later)]):
+        fills self._pinned with whole lines of the files in `order`, one segment at a time"""
+        import numpy as np
+        cap = self.segment_bytes
+        view = self._pinned.numpy()
+        fill, parts = 0, []          # parts: [file index, bytes of that file in this segment]
+        for fi in order:
+            with open(self.train_files[fi], "rb") as f:
+                last = 10
+                while True:
+                    if fill == cap:   # full: cut at the last newline, the tail opens the next segment
+                        tail = view[max(0, cap - (1 << 20)):cap].tobytes()
+                        pos = tail.rfind(b"\n")
+                        if pos < 0:
+                            tail = view[:cap].tobytes()
+                            pos = tail.rfind(b"\n")
+                            if pos < 0:
+                                raise ValueError("a line of %s is longer than the segment (%d bytes)"
+                                                 % (self.train_files[fi], cap))
+                        keep = cap - len(tail) + pos + 1
+                        carry = view[keep:cap].copy()
+                        parts[-1][1] -= cap - keep
+                        yield keep, parts
+                        view[:carry.size] = carry
+                        fill, parts = carry.size, [[fi, carry.size]]
+                    got = f.readinto(memoryview(view[fill:cap]))
+                    if not got:
+                        break
+                    last = int(view[fill + got - 1])
+                    if parts and parts[-1][0] == fi:
+                        parts[-1][1] += got
+                    else:
+                        parts.append([fi, got])
+                    fill += got
+                if last != 10:        # a final line without newline gets one (room: the arena half is cap + 16)
+                    if fill == cap:
+                        raise ValueError("%s: the last line does not end with a newline at a segment boundary; "
+                                         "end the file with a newline" % self.train_files[fi])
+                    view[fill] = 10
+                    parts[-1][1] += 1
+                    fill += 1
+        if fill:
+            yield fill, parts
+
+    def batches(self, batch_size, num_epochs=1, shuffle=True, seed=None):
+        """yields (PackedLines on the device, weights tensor or None)"""
+        import torch
+        from . import fm_ops
+        dev, cap = self.device, self.segment_bytes
+        if self._arena is None:
+            self._arena = torch.zeros(2 * (cap + 16), dtype=torch.uint8, device=dev)
+            self._pinned = torch.zeros(cap + 16, dtype=torch.uint8).pin_memory()
+        arena = self._arena
+        gen = torch.Generator(device=dev)
+        if seed is not None:
+            gen.manual_seed(int(seed))
+        rnd = random.Random(seed)
+        i64 = dict(dtype=torch.int64, device=dev)
+        pend_b, pend_e = torch.zeros(0, **i64), torch.zeros(0, **i64)
+        pend_w = torch.zeros(0, dtype=torch.float32, device=dev) if self.weight_files else None
+        wcache, wpos = {}, {}
+        seg_no = 0
+        copied = None
+        for _ in range(num_epochs):
+            order = list(range(len(self.train_files)))
+            if shuffle:
+                rnd.shuffle(order)
+            wpos = {fi: 0 for fi in order}
+            for n_bytes, parts in self._segments(order):
+                base = (seg_no % 2) * (cap + 16)
+                seg_no += 1
+                half = arena[base:base + cap + 16]
+                padded = (n_bytes + 15) // 16 * 16
+                # whatever still reads this half (a consumer may parse on a side stream) is through first
+                torch.cuda.synchronize(dev)
+                half[:n_bytes].copy_(self._pinned[:n_bytes], non_blocking=True)
+                half[n_bytes:padded + 16].zero_()
+                n_lines = int((half[:n_bytes] == 10).sum())      # also: the copy is done, the pinned buffer is free
+                off = fm_ops.fm_split_lines(half, n_bytes, n_lines)
+                begins, ends = off[:-1] + base, off[1:] + base
+                w = None
+                if self.weight_files:
+                    # lines of each file in this segment: newlines inside that file's byte range
+                    ws, at = [], 0
+                    for fi, nb in parts:
+                        cnt = int(torch.searchsorted(off, at + nb, right=True) - torch.searchsorted(off, at, right=True))
+                        if fi not in wcache:
+                            wcache.clear()          # one file's weights at a time
+                            wcache[fi] = self._file_weights(self.weight_files[fi])
+                        if wpos[fi] + cnt > wcache[fi].numel():
+                            raise ValueError("%s has fewer lines than %s" % (self.weight_files[fi], self.train_files[fi]))
+                        ws.append(wcache[fi][wpos[fi]:wpos[fi] + cnt])
+                        wpos[fi] += cnt
+                        at += nb
+                    w = torch.cat(ws)
+                if shuffle:
+                    perm = torch.randperm(n_lines, device=dev, generator=gen)
+                    begins, ends = begins[perm], ends[perm]
+                    w = None if w is None else w[perm]
+                if pend_b.numel() and pend_b.numel() + n_lines < batch_size:
+                    raise ValueError("a segment of %d bytes holds fewer than batch_size = %d lines: raise segment_bytes"
+                                     % (cap, batch_size))
+                all_b, all_e = torch.cat([pend_b, begins]), torch.cat([pend_e, ends])
+                all_w = None if w is None else torch.cat([pend_w, w])
+                k = 0
+                while all_b.numel() - k >= batch_size:
+                    sl = slice(k, k + batch_size)
+                    yield (fm_ops.PackedLines(arena, begins=all_b[sl].contiguous(), ends=all_e[sl].contiguous()),
+                           None if all_w is None else all_w[sl].contiguous())
+                    k += batch_size
+                pend_b, pend_e = all_b[k:], all_e[k:]
+                pend_w = None if all_w is None else all_w[k:]
+        if pend_b.numel():
+            yield (fm_ops.PackedLines(arena, begins=pend_b.contiguous(), ends=pend_e.contiguous()),
+                   None if pend_w is None else pend_w.contiguous())
+
+
 def bind_host_to_gpu(index=None):
     """Pin the calling thread (and the threads it starts later) to the CPUs of the NUMA node the GPU hangs
     off, so that pinned staging buffers allocated afterwards are local to the GPU's PCIe root and the

@@ -35,6 +35,16 @@ def _ckpt_path(model):
     return os.path.join(model.log_dir, "model.ckpt.pt")
 
 
+def _training_set(cfg, device, stream_mb):
+    """training files resident in HBM when they fit comfortably, else streamed through it in segments"""
+    total = sum(os.path.getsize(f) for f in cfg.train_files)
+    free, _ = torch.cuda.mem_get_info(device)
+    if stream_mb is None and total < free // 2:
+        return fm_data.DeviceDataset(cfg.train_files, cfg.weight_files, device)
+    return fm_data.SegmentedDataset(cfg.train_files, cfg.weight_files, device,
+                                    segment_bytes=(stream_mb if stream_mb else 256) << 20)
+
+
 def predict(model):
     for data_file in model.predict_files:
         lines = fm_data._read_lines(data_file)
@@ -56,7 +66,7 @@ def _validation_loss(model, vdata):
     return total / max(n, 1)
 
 
-def train_sharded(cfg, monitor):
+def train_sharded(cfg, monitor, stream_mb=None):
     """`train` under torchrun: synchronous data-parallel steps on the peer-sharded table"""
     import torch.distributed as dist
     from fast_tffm_b200.sharded import PeerShardedModel
@@ -95,7 +105,7 @@ def train_sharded(cfg, monitor):
     # every rank holds the files and walks the same shuffled order; a global batch is cut into equal slices
     seed = torch.tensor([int(time.time())], dtype=torch.int64, device=device)
     dist.broadcast(seed, 0)
-    dataset = fm_data.DeviceDataset(cfg.train_files, cfg.weight_files, device)
+    dataset = _training_set(cfg, device, stream_mb)
     st = time.time()
     start_step = step_num = model.global_step
     for lines, weights in dataset.batches(cfg.batch_size, cfg.num_epochs, shuffle=True, seed=int(seed.item())):
@@ -124,7 +134,7 @@ def train_sharded(cfg, monitor):
     dist.destroy_process_group()
 
 
-def train(model, monitor, trace):
+def train(model, monitor, trace, stream_mb=None):
     vdata = None
     if model.validation_data_files:
         print('Preloading validation data...')
@@ -135,7 +145,7 @@ def train(model, monitor, trace):
     start_step = model.global_step
     step_num = start_step
     # the training files live in HBM; a batch is a shuffled index selection over the resident text
-    dataset = fm_data.DeviceDataset(model.train_files, model.weight_files, model.device)
+    dataset = _training_set(model, model.device, stream_mb)
     for lines, weights in dataset.batches(model.batch_size, model.num_epochs, shuffle=True, seed=int(st)):
         cur = time.time()
         loss = model.train_step(lines, weights)
@@ -179,6 +189,9 @@ def main():
                         help="Stores per-step timings as a chrome trace file")
     parser.add_argument("-m,", "--monitor", action="store_true", help="Prints execution speed to screen")
     parser.add_argument("--export_path", help="(SavedModel export: not available in this build)")
+    parser.add_argument("--stream-mb", type=int, default=None, metavar='MB',
+                        help="Stream the training files through the GPU in segments of MB megabytes instead of "
+                             "keeping them resident (automatic when they exceed half of the free GPU memory)")
     args = parser.parse_args()
 
     if args.task == 'generate' or args.dist is not None:
@@ -198,7 +211,7 @@ def main():
         if args.task != 'train':
             print("predict runs on one GPU (the checkpoint of a sharded run is in the single-GPU layout).")
             sys.exit(2)
-        train_sharded(model, args.monitor)
+        train_sharded(model, args.monitor, args.stream_mb)
         return
     model.build(seed=int(time.time()))
     if model.log_dir is not None and os.path.exists(_ckpt_path(model)):
@@ -208,7 +221,7 @@ def main():
         sys.exit(1)
     print("========", args.task, "========")
     if args.task == 'train':
-        train(model, args.monitor, args.trace)
+        train(model, args.monitor, args.trace, args.stream_mb)
     else:
         predict(model)
 

@@ -23,8 +23,10 @@ def test_train_then_predict_cli(tmp_path, loss_type):
     cfg = cfg.replace("learning_rate = 0.01", "learning_rate = 0.05")
     (tmp_path / "t.cfg").write_text(cfg)
     env = dict(os.environ, PYTHONPATH=ROOT)
+    # logistic run: the files stream through the GPU in segments (--stream-mb) instead of sitting in HBM
+    extra = ["--stream-mb", "1"] if loss_type == "logistic" else []
     out = subprocess.run([sys.executable, os.path.join(ROOT, "run_tffm.py"), "train", str(tmp_path / "t.cfg"), "-m",
-                          "-t", str(tmp_path / "trace")], capture_output=True, text=True, env=env, cwd=ROOT)
+                          "-t", str(tmp_path / "trace")] + extra, capture_output=True, text=True, env=env, cwd=ROOT)
     assert out.returncode == 0, out.stdout + out.stderr
     losses = [float(x) for x in re.findall(r"-- Global Step: \d+; Avg loss: ([0-9.]+);", out.stdout)]
     assert len(losses) == 15                                   # 3 epochs x 2000 lines / 400

@@ -221,6 +221,47 @@ def test_device_dataset_epochs(tmp_path, criteo_lines):
                                   O.parse_lines(lines[:1000], 800000)[2])
 
 
+def test_segmented_dataset_streams_files_through_the_arena(tmp_path, criteo_lines):
+    """files larger than a segment: every line arrives exactly once per epoch with its own weight, batches
+    have batch_size lines except the last of the run, lines cross segment and file boundaries"""
+    from fast_tffm_b200.data import SegmentedDataset
+    lines, weights = criteo_lines
+    cuts = [0, 700, 741, 741, 2000]                       # four files, one of them empty
+    files, wfiles = [], []
+    for i in range(4):
+        part = lines[cuts[i]:cuts[i + 1]]
+        text = "\n".join(part) + ("\n" if part and i != 1 else "")     # file 1: no newline at the end
+        (tmp_path / ("d%d" % i)).write_text(text)
+        (tmp_path / ("w%d" % i)).write_text("".join("%g\n" % w for w in weights[cuts[i]:cuts[i + 1]]))
+        files.append(str(tmp_path / ("d%d" % i)))
+        wfiles.append(str(tmp_path / ("w%d" % i)))
+    ds = SegmentedDataset(files, wfiles, DEV, segment_bytes=48 * 1024)      # ~220 lines per segment
+    # in order
+    got, got_w, sizes = [], [], []
+    for packed, w in ds.batches(128, num_epochs=2, shuffle=False):
+        sizes.append(packed.n_lines)
+        got += [packed.line(i) for i in range(packed.n_lines)]
+        got_w += w.cpu().tolist()
+    assert sizes == [128] * (4000 // 128) + [4000 % 128]
+    assert got == lines + lines
+    np.testing.assert_array_equal(np.float32(got_w), np.float32(weights + weights))
+    # shuffled: a permutation per epoch (within segments), weights travel with their lines
+    seen = []
+    for packed, w in ds.batches(128, num_epochs=1, shuffle=True, seed=5):
+        wl = w.cpu().tolist()
+        seen += [(packed.line(i), wl[i]) for i in range(packed.n_lines)]
+    assert [l for l, _ in seen] != lines
+    assert sorted(seen) == sorted(zip(lines, [float(np.float32(x)) for x in weights]))
+    # the parser accepts what the dataset yields (begins / ends over the two-half arena)
+    packed, w = next(iter(ds.batches(300, 1, shuffle=False)))
+    e = O.parse_lines(lines[:300], 1 << 20, False)
+    labels, szs, ids, vals = fm_ops.fm_parser(packed, 1 << 20)
+    np.testing.assert_array_equal(ids.cpu().numpy(), e[2])
+    np.testing.assert_array_equal(szs.cpu().numpy(), e[1])
+    with pytest.raises(ValueError, match="raise segment_bytes"):
+        list(SegmentedDataset(files, (), DEV, segment_bytes=8 * 1024).batches(1000, 1, shuffle=False))
+
+
 def test_parser_empty_batch():
     labels, sizes, ids, vals = fm_ops.fm_parser([], 10)
     assert labels.numel() == 0 and sizes.numel() == 0 and ids.numel() == 0 and vals.numel() == 0
