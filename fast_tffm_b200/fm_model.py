@@ -82,7 +82,7 @@ class Model(object):
         self.global_step = 0
         self._bufs = None
         self._slots = {}
-        self._ahead_slot = 0
+        self._ahead_slot = 2     # parse_ahead alternates between buffer sets 1 and 2; set 0 serves inline steps / predict
         self._parse_stream = None
 
     # ---- INI config, same sections / keys as tffm/fm_model.py:367-475 -----------------
@@ -212,7 +212,7 @@ class Model(object):
         parser is instruction-bound while the table kernels are memory-bound, so the two overlap."""
         if self._parse_stream is None:
             self._parse_stream = torch.cuda.Stream(device=self.device)
-        self._ahead_slot ^= 1
+        self._ahead_slot = 3 - self._ahead_slot
         slot = self._ahead_slot
         b = self._buffers(packed.n_lines, packed.text.numel(), slot=slot)
         main = torch.cuda.current_stream(self.device)

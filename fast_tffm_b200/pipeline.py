@@ -48,9 +48,11 @@ class StepResult:
 class HostBatchPipeline:
     """pipe = HostBatchPipeline(model); for res in pipe.run(batches): ...
 
-    batches yields (host PackedLines, weights or None[, global_batch]); pinned host tensors make the
-    copies asynchronous.  `global_batch` (PeerShardedModel only) is the number of lines of the whole
-    step over all ranks; default: this rank's lines x world size.
+    batches yields (PackedLines, weights or None[, global_batch]).  Host batches are copied in (pinned
+    host tensors make the copies asynchronous); device-resident batches (DeviceDataset, SegmentedDataset)
+    skip the copy stage and still get the parse of batch s+1 under the table kernels of batch s.
+    `global_batch` (PeerShardedModel only) is the number of lines of the whole step over all ranks;
+    default: this rank's lines x world size.
     """
 
     SLOTS = 3
@@ -69,6 +71,10 @@ class HostBatchPipeline:
 
     # ---- stage 1: host -> device staging slot (copy stream) ------------------------
     def _stage(self, index, host, weights):
+        if host.text.is_cuda:       # already resident (DeviceDataset / SegmentedDataset batches): nothing to copy
+            if weights is not None and not (isinstance(weights, torch.Tensor) and weights.is_cuda):
+                weights = torch.as_tensor(weights, dtype=torch.float32).to(self.device)
+            return dict(index=index, host=host, packed=host, weights=weights, slot=dict(ready=None, free=None))
         slot = self._slots[index % self.SLOTS]
         n_text, n_off = host.text.numel(), host.offsets.numel()
         grow = slot["text"] is None or slot["text"].numel() < n_text or slot["offsets"].numel() < n_off

@@ -308,7 +308,7 @@ class PeerShardedModel:
         self.lib = load()
         self.global_step = 0
         self._slots = {}
-        self._ahead_slot = 0
+        self._ahead_slot = 2     # parse_ahead alternates between buffer sets 1 and 2; set 0 serves inline steps / predict
         self._parse_stream = None
 
     def rows_per_rank(self):
@@ -427,7 +427,7 @@ class PeerShardedModel:
         """parse of the next batch on a side stream (see Model.parse_ahead)"""
         if self._parse_stream is None:
             self._parse_stream = torch.cuda.Stream(device=self.device)
-        self._ahead_slot ^= 1
+        self._ahead_slot = 3 - self._ahead_slot
         main, side = torch.cuda.current_stream(self.device), self._parse_stream
         b = self._slots.get(self._ahead_slot)
         side.wait_stream(main) if b is None or b.get("free") is None else side.wait_event(b["free"])

@@ -29,29 +29,33 @@ import torch
 from tffm.fm_model import Model
 from fast_tffm_b200 import data as fm_data
 from fast_tffm_b200 import fm_ops
+from fast_tffm_b200.pipeline import HostBatchPipeline
 
 
 def _ckpt_path(model):
     return os.path.join(model.log_dir, "model.ckpt.pt")
 
 
-def _training_set(cfg, device, stream_mb):
-    """training files resident in HBM when they fit comfortably, else streamed through it in segments"""
-    total = sum(os.path.getsize(f) for f in cfg.train_files)
+def _dataset(files, weight_files, device, stream_mb):
+    """files resident in HBM when they fit comfortably, else streamed through it in segments"""
+    total = sum(os.path.getsize(f) for f in files)
     free, _ = torch.cuda.mem_get_info(device)
     if stream_mb is None and total < free // 2:
-        return fm_data.DeviceDataset(cfg.train_files, cfg.weight_files, device)
-    return fm_data.SegmentedDataset(cfg.train_files, cfg.weight_files, device,
-                                    segment_bytes=(stream_mb if stream_mb else 256) << 20)
+        return fm_data.DeviceDataset(files, weight_files, device)
+    return fm_data.SegmentedDataset(files, weight_files, device, segment_bytes=(stream_mb if stream_mb else 256) << 20)
 
 
-def predict(model):
+def _training_set(cfg, device, stream_mb):
+    return _dataset(cfg.train_files, cfg.weight_files, device, stream_mb)
+
+
+def predict(model, stream_mb=None):
     for data_file in model.predict_files:
-        lines = fm_data._read_lines(data_file)
+        lines = _dataset([data_file], (), model.device, stream_mb)      # split into lines on the device
         with open(data_file + '_score', 'w') as f:
-            for i in range(0, len(lines), model.batch_size):
-                for score in model.predict(lines[i:i + model.batch_size]).cpu().numpy():
-                    f.write(str(score) + '\n')
+            for batch, _ in lines.batches(model.batch_size, 1, shuffle=False):
+                scores = model.predict(batch).cpu().numpy()
+                f.write(''.join(s + '\n' for s in scores.astype(str).tolist()))   # str(np.float32), as run_tffm.py:14
     print('Done. Scores saved to same directory as predict files')
 
 
@@ -108,24 +112,45 @@ def train_sharded(cfg, monitor, stream_mb=None):
     dataset = _training_set(cfg, device, stream_mb)
     st = time.time()
     start_step = step_num = model.global_step
-    for lines, weights in dataset.batches(cfg.batch_size, cfg.num_epochs, shuffle=True, seed=int(seed.item())):
-        n = lines.n_lines
-        if n < world:           # a tail shorter than the number of GPUs cannot be cut into non-empty slices
-            continue
-        cur = time.time()
-        loss = model.train_step(*cut(lines, weights), global_batch=n)
-        step_num = model.global_step
+
+    def slices():
+        for lines, weights in dataset.batches(cfg.batch_size, cfg.num_epochs, shuffle=True, seed=int(seed.item())):
+            n = lines.n_lines
+            if n < world:       # a tail shorter than the number of GPUs cannot be cut into non-empty slices
+                continue
+            global_lines.append(n)
+            yield cut(lines, weights) + (n,)
+
+    # as in train(): results are read one step late, except at save / validation steps
+    pipe = HostBatchPipeline(model)
+    global_lines, pending = [], []
+
+    def report(res, cur):
+        loss = res.loss()
         if monitor:
-            say('speed:', n / (time.time() - cur))
-        say('-- Global Step: %d; Avg loss: %.5f;' % (step_num, loss))
-        if ckpt is not None and step_num % cfg.save_steps == 0:
-            model.save(ckpt)
-        if vdata is not None and step_num % cfg.save_steps == 0:
-            v_loss = validation_loss(vdata)          # the same number on every rank: all stop together
-            say('validation loss at step %d: %.8f' % (step_num, v_loss))
-            if v_loss < cfg.tolerance:
-                say('Loss on validation data set is below tolerance. Training completed.')
-                break
+            say('speed:', global_lines[res.index] / (time.time() - cur))
+        say('-- Global Step: %d; Avg loss: %.5f;' % (start_step + res.index + 1, loss))
+
+    cur = time.time()
+    for res in pipe.run(slices()):
+        step_num = model.global_step
+        for old in pending:
+            report(*old)
+        pending = [(res, cur)]
+        cur = time.time()
+        if step_num % cfg.save_steps == 0:
+            report(*pending.pop())
+            cur = time.time()
+            if ckpt is not None:
+                model.save(ckpt)
+            if vdata is not None:
+                v_loss = validation_loss(vdata)          # the same number on every rank: all stop together
+                say('validation loss at step %d: %.8f' % (step_num, v_loss))
+                if v_loss < cfg.tolerance:
+                    say('Loss on validation data set is below tolerance. Training completed.')
+                    break
+    for old in pending:
+        report(*old)
     total = time.time() - st
     say('Average speed: ', (step_num - start_step) * cfg.batch_size / total, ' ex/s')
     if ckpt is not None:
@@ -146,25 +171,42 @@ def train(model, monitor, trace, stream_mb=None):
     step_num = start_step
     # the training files live in HBM; a batch is a shuffled index selection over the resident text
     dataset = _training_set(model, model.device, stream_mb)
-    for lines, weights in dataset.batches(model.batch_size, model.num_epochs, shuffle=True, seed=int(st)):
-        cur = time.time()
-        loss = model.train_step(lines, weights)
-        step_num = model.global_step
+    # steps are enqueued ahead of their results: the parse of batch s+1 runs under the table kernels of batch
+    # s, and the line of step s is printed while step s+1 runs -- except at save / validation steps, which
+    # need the table exactly as step s left it
+    pipe = HostBatchPipeline(model)
+    pending = []
+
+    def report(res, cur):
+        loss = res.loss()                       # raises FmParseError like the op would
         tend = time.time()
         if trace and len(events) < 1000:
             events.append({"name": "train_step", "ph": "X", "ts": cur * 1e6, "dur": (tend - cur) * 1e6,
-                           "pid": 0, "tid": 0, "args": {"step": step_num, "examples": lines.n_lines}})
+                           "pid": 0, "tid": 0, "args": {"step": start_step + res.index + 1, "examples": res.n_lines}})
         if monitor:
-            print('speed:', lines.n_lines / (tend - cur))
-        print('-- Global Step: %d; Avg loss: %.5f;' % (step_num, loss))
-        if model.log_dir is not None and step_num % model.save_steps == 0:
-            model.save(_ckpt_path(model))
-        if vdata is not None and step_num % model.save_steps == 0:
-            v_loss = _validation_loss(model, vdata)
-            print('validation loss at step %d: %.8f' % (step_num, v_loss))
-            if v_loss < model.tolerance:
-                print('Loss on validation data set is below tolerance. Training completed.')
-                break
+            print('speed:', res.n_lines / (tend - cur))
+        print('-- Global Step: %d; Avg loss: %.5f;' % (start_step + res.index + 1, loss))
+
+    cur = time.time()
+    for res in pipe.run(dataset.batches(model.batch_size, model.num_epochs, shuffle=True, seed=int(st))):
+        step_num = model.global_step
+        for old in pending:
+            report(*old)
+        pending = [(res, cur)]
+        cur = time.time()
+        if step_num % model.save_steps == 0:
+            report(*pending.pop())
+            cur = time.time()
+            if model.log_dir is not None:
+                model.save(_ckpt_path(model))
+            if vdata is not None:
+                v_loss = _validation_loss(model, vdata)
+                print('validation loss at step %d: %.8f' % (step_num, v_loss))
+                if v_loss < model.tolerance:
+                    print('Loss on validation data set is below tolerance. Training completed.')
+                    break
+    for old in pending:
+        report(*old)
     total = time.time() - st
     print('Average speed: ', (step_num - start_step) * model.batch_size / total, ' ex/s')
     if model.log_dir is not None:
@@ -223,7 +265,7 @@ def main():
     if args.task == 'train':
         train(model, args.monitor, args.trace, args.stream_mb)
     else:
-        predict(model)
+        predict(model, args.stream_mb)
 
 
 if __name__ == '__main__':
