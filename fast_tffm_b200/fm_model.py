@@ -475,9 +475,79 @@ class Model(object):
                 dst[i::nb, :k + 1] = state["vocab_block_%d%s" % (i, name)][:n].to(self.device)
         self.global_step = int(state.get("global_step", 0))
 
-    def save(self, path):
+    def _blocks_snapshot(self):
+        """device copy of the table and the accumulator, already in block order: f32[2, nb, V//nb+1, K+1];
+        None when HBM has no room for it"""
+        nb, v, k = self.vocabulary_block_num, self.vocabulary_size, self.factor_num
+        rows = v // nb + 1
+        need = 2 * 2 * nb * rows * (k + 1) * 4          # the copy + the transposed copy
+        if torch.cuda.mem_get_info(self.device)[0] < need + (1 << 30):
+            return None
+        dense = torch.zeros(2, rows * nb, k + 1, dtype=torch.float32, device=self.device)
+        dense[0, :v] = self.table[:, :k + 1]
+        dense[1, :v] = self.accum[:, :k + 1]
+        return dense.view(2, rows, nb, k + 1).transpose(1, 2).contiguous()   # [which, id % nb, id // nb, :]
+
+    @staticmethod
+    def _write_blocks(path, host, global_step):
+        nb = host.shape[1]
+        out = {"global_step": global_step}
+        for w, name in enumerate(("", "/Adagrad")):
+            for i in range(nb):
+                out["vocab_block_%d%s" % (i, name)] = host[w, i]       # views of one storage: written once
         os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
-        torch.save(self.blocks_state(), path)
+        torch.save(out, path + ".tmp")
+        os.replace(path + ".tmp", path)                  # a reader never sees a half-written file
+
+    def save(self, path, wait=True, skip_if_busy=False):
+        """Writes the checkpoint (reference variable layout, see blocks_state).  wait=False: the table is
+        snapshotted on the device now (one strided device copy) and the D2H copy + file write run on a
+        background thread while training goes on.  One save is in flight at a time: a new one waits for it,
+        or -- skip_if_busy, for periodic saves that must never hold training up -- is dropped (returns False)."""
+        import threading
+        t = getattr(self, "_save_thread", None)
+        if skip_if_busy and t is not None and t.is_alive():
+            return False
+        self.wait_for_save()
+        snap = self._blocks_snapshot()
+        if snap is None:                                 # no room for a snapshot: block by block, synchronously
+            os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+            torch.save(self.blocks_state(), path + ".tmp")
+            os.replace(path + ".tmp", path)
+            return True
+        if getattr(self, "_save_stream", None) is None:
+            self._save_stream = torch.cuda.Stream(device=self.device)
+        ready = torch.cuda.Event()
+        ready.record(torch.cuda.current_stream(self.device))
+        snap.record_stream(self._save_stream)
+        step, stream = self.global_step, self._save_stream
+
+        def work():
+            try:
+                with torch.cuda.stream(stream):
+                    stream.wait_event(ready)
+                    host = snap.to("cpu")                # pageable: no page-locking of a table-sized buffer
+                self._write_blocks(path, host, step)
+            except BaseException as e:       # surfaces in wait_for_save()
+                self._save_error = e
+                if wait:
+                    raise
+
+        if wait:
+            work()
+        else:
+            self._save_thread = threading.Thread(target=work, name="fm-checkpoint")
+            self._save_thread.start()
+        return True
+
+    def wait_for_save(self):
+        t = getattr(self, "_save_thread", None)
+        if t is not None:
+            t.join()
+            self._save_thread = None
+        err, self._save_error = getattr(self, "_save_error", None), None
+        if err is not None:
+            raise RuntimeError("writing the checkpoint failed: %r" % (err,))
 
     def restore(self, path):
         self.load_blocks_state(torch.load(path, map_location="cpu"))

@@ -166,11 +166,11 @@ def train(model, monitor, trace, stream_mb=None):
         vset = fm_data.DeviceDataset(model.validation_data_files, model.validation_weight_files, model.device)
         vdata = list(vset.batches(model.batch_size, 1, shuffle=False))
     events = []
-    st = time.time()
-    start_step = model.global_step
-    step_num = start_step
     # the training files live in HBM; a batch is a shuffled index selection over the resident text
     dataset = _training_set(model, model.device, stream_mb)
+    st = time.time()
+    start_step = model.global_step
+    step_num = saved_step = start_step
     # steps are enqueued ahead of their results: the parse of batch s+1 runs under the table kernels of batch
     # s, and the line of step s is printed while step s+1 runs -- except at save / validation steps, which
     # need the table exactly as step s left it
@@ -198,7 +198,9 @@ def train(model, monitor, trace, stream_mb=None):
             report(*pending.pop())
             cur = time.time()
             if model.log_dir is not None:
-                model.save(_ckpt_path(model))
+                # device snapshot now, file written in the background; dropped if the last one is still being written
+                if model.save(_ckpt_path(model), wait=False, skip_if_busy=True):
+                    saved_step = step_num
             if vdata is not None:
                 v_loss = _validation_loss(model, vdata)
                 print('validation loss at step %d: %.8f' % (step_num, v_loss))
@@ -210,7 +212,9 @@ def train(model, monitor, trace, stream_mb=None):
     total = time.time() - st
     print('Average speed: ', (step_num - start_step) * model.batch_size / total, ' ex/s')
     if model.log_dir is not None:
-        model.save(_ckpt_path(model))
+        if saved_step != step_num:
+            model.save(_ckpt_path(model), wait=False)
+        model.wait_for_save()
     print('Model saved to ', model.log_dir)
     if trace:
         if not trace.endswith('.json'):

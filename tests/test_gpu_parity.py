@@ -554,6 +554,34 @@ def test_parse_ahead_pipeline_matches_inline_steps(criteo_lines):
     np.testing.assert_allclose(a.table[:, :k + 1].cpu().numpy(), b.table[:, :k + 1].cpu().numpy(), rtol=1e-5, atol=1e-8)
 
 
+def test_background_checkpoint_is_a_consistent_snapshot(tmp_path, criteo_lines):
+    """save(wait=False): the file holds the table as it was when save() was called, in the reference's
+    vocab_block_i layout, although training went on while it was being written"""
+    lines, _ = criteo_lines
+    vocab, nb, k = 170003, 7, 9
+    kw = dict(vocabulary_size=vocab, vocabulary_block_num=nb, factor_num=k, batch_size=200, learning_rate=0.05)
+    m = Model(**kw).build(DEV, seed=1)
+    m.train_step(lines[:200])
+    table, accum, blocks = m.table[:, :k + 1].clone(), m.accum[:, :k + 1].clone(), m.blocks_state()
+    path = str(tmp_path / "ckpt" / "model.ckpt.pt")
+    m.save(path, wait=False)
+    for i in range(1, 6):
+        m.train_step(lines[200 * i:200 * (i + 1)])
+    m.wait_for_save()
+    assert not torch.equal(m.table[:, :k + 1], table)
+    st = torch.load(path)
+    assert st["global_step"] == 1 and st["vocab_block_3"].shape == (vocab // nb + 1, k + 1)
+    for key, val in blocks.items():
+        if key != "global_step":
+            assert torch.equal(st[key], val), key
+    m2 = Model(**kw).build(DEV, seed=2)
+    m2.restore(path)
+    assert torch.equal(m2.table[:, :k + 1], table) and torch.equal(m2.accum[:, :k + 1], accum) and m2.global_step == 1
+    m.save(path)                                             # synchronous form, same file name
+    m2.restore(path)
+    assert torch.equal(m2.table[:, :k + 1], m.table[:, :k + 1]) and m2.global_step == 6
+
+
 def test_host_batch_pipeline_matches_step_by_step(criteo_lines):
     """copy | parse | train pipeline over host batches (pinned and not, growing sizes, weights on some, one
     batch that does not parse): same losses and the same table as train_step on each batch in turn"""
