@@ -515,18 +515,33 @@ class Model(object):
             torch.save(self.blocks_state(), path + ".tmp")
             os.replace(path + ".tmp", path)
             return True
-        if getattr(self, "_save_stream", None) is None:
-            self._save_stream = torch.cuda.Stream(device=self.device)
+        self.prepare_save()
         ready = torch.cuda.Event()
         ready.record(torch.cuda.current_stream(self.device))
         snap.record_stream(self._save_stream)
-        step, stream = self.global_step, self._save_stream
+        step, stream, bounce = self.global_step, self._save_stream, self._save_bounce
 
         def work():
+            # D2H through two pinned bounce buffers (asynchronous DMA: a pageable cudaMemcpy from this thread
+            # would hold the driver's lock and stall the training thread's launches), then the file
             try:
+                host = torch.empty(snap.shape, dtype=torch.float32)
+                src, dst, chunk = snap.view(-1), host.view(-1), bounce.shape[1]
+                prev = None
                 with torch.cuda.stream(stream):
                     stream.wait_event(ready)
-                    host = snap.to("cpu")                # pageable: no page-locking of a table-sized buffer
+                    for i, lo in enumerate(range(0, src.numel(), chunk)):
+                        hi = min(src.numel(), lo + chunk)
+                        bounce[i % 2, :hi - lo].copy_(src[lo:hi], non_blocking=True)
+                        ev = torch.cuda.Event()
+                        ev.record(stream)
+                        if prev is not None:
+                            prev[0].synchronize()
+                            dst[prev[1]:prev[2]].copy_(bounce[prev[3], :prev[2] - prev[1]])
+                        prev = (ev, lo, hi, i % 2)
+                    if prev is not None:
+                        prev[0].synchronize()
+                        dst[prev[1]:prev[2]].copy_(bounce[prev[3], :prev[2] - prev[1]])
                 self._write_blocks(path, host, step)
             except BaseException as e:       # surfaces in wait_for_save()
                 self._save_error = e
@@ -539,6 +554,13 @@ class Model(object):
             self._save_thread = threading.Thread(target=work, name="fm-checkpoint")
             self._save_thread.start()
         return True
+
+    def prepare_save(self):
+        """stream and pinned bounce buffers of the background checkpoint writer (page-locking memory stalls
+        other CUDA calls: do it before the training loop starts)"""
+        if getattr(self, "_save_stream", None) is None:
+            self._save_stream = torch.cuda.Stream(device=self.device)
+            self._save_bounce = torch.empty(2, 8 << 20, dtype=torch.float32).pin_memory()     # 2 x 32 MiB
 
     def wait_for_save(self):
         t = getattr(self, "_save_thread", None)

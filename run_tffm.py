@@ -168,6 +168,8 @@ def train(model, monitor, trace, stream_mb=None):
     events = []
     # the training files live in HBM; a batch is a shuffled index selection over the resident text
     dataset = _training_set(model, model.device, stream_mb)
+    if model.log_dir is not None:
+        model.prepare_save()
     st = time.time()
     start_step = model.global_step
     step_num = saved_step = start_step
