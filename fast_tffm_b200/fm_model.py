@@ -47,6 +47,120 @@ def _ld_for(factor_num):
     return _stride_for(factor_num + 1)
 
 
+class CheckpointWriter:
+    """Writes checkpoint files off the training thread: a device-side snapshot is drained through two pinned
+    32 MiB bounce buffers on its own stream (asynchronous DMA -- a pageable cudaMemcpy or a table-sized
+    cudaHostAlloc from another thread holds the driver's lock and stalls every launch of the training
+    thread), turned into a state dict and written with torch.save + an atomic rename.  One file in flight."""
+
+    def __init__(self, device):
+        self.device = device
+        self._stream = self._bounce = self._thread = self._error = None
+
+    def prepare(self):
+        """page-locks the bounce buffers (do it before the training loop: it stalls other CUDA calls)"""
+        if self._stream is None:
+            self._stream = torch.cuda.Stream(device=self.device)
+            self._bounce = torch.empty(2, 8 << 20, dtype=torch.float32).pin_memory()
+
+    def busy(self):
+        return self._thread is not None and self._thread.is_alive()
+
+    def wait(self):
+        if self._thread is not None:
+            self._thread.join()
+            self._thread = None
+        err, self._error = self._error, None
+        if err is not None:
+            raise RuntimeError("writing the checkpoint failed: %r" % (err,))
+
+    def write(self, path, snap, make_state, wait=True, after=None):
+        """snap: contiguous f32 device tensor holding the snapshot; make_state(host copy of snap) -> the dict
+        to save; after(): called once the file is in place (e.g. removes files it supersedes)"""
+        import threading
+        self.wait()
+        self.prepare()
+        ready = torch.cuda.Event()
+        ready.record(torch.cuda.current_stream(self.device))
+        snap.record_stream(self._stream)
+        stream, bounce = self._stream, self._bounce
+
+        def work():
+            try:
+                host = torch.empty(snap.shape, dtype=torch.float32)
+                src, dst, chunk = snap.view(-1), host.view(-1), bounce.shape[1]
+                prev = None
+                with torch.cuda.stream(stream):
+                    stream.wait_event(ready)
+                    for i, lo in enumerate(range(0, src.numel(), chunk)):
+                        hi = min(src.numel(), lo + chunk)
+                        bounce[i % 2, :hi - lo].copy_(src[lo:hi], non_blocking=True)
+                        ev = torch.cuda.Event()
+                        ev.record(stream)
+                        if prev is not None:
+                            prev[0].synchronize()
+                            dst[prev[1]:prev[2]].copy_(bounce[prev[3], :prev[2] - prev[1]])
+                        prev = (ev, lo, hi, i % 2)
+                    if prev is not None:
+                        prev[0].synchronize()
+                        dst[prev[1]:prev[2]].copy_(bounce[prev[3], :prev[2] - prev[1]])
+                os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+                torch.save(make_state(host), path + ".tmp")
+                os.replace(path + ".tmp", path)          # a reader never sees a half-written file
+                if after is not None:
+                    after()
+            except BaseException as e:                   # surfaces in wait()
+                self._error = e
+                if wait:
+                    raise
+
+        if wait:
+            work()
+            self._error = None
+        else:
+            self._thread = threading.Thread(target=work, name="fm-checkpoint")
+            self._thread.start()
+
+
+def shard_sets(path):
+    """complete sharded checkpoint sets next to `path`: {g: [file of rank 0, ..., file of rank g-1]}"""
+    sets = {}
+    for f in glob.glob(glob.escape(path) + ".shard-*-of-*"):
+        try:
+            r, g = f[len(path) + len(".shard-"):].split("-of-")
+            sets.setdefault(int(g), {})[int(r)] = f
+        except ValueError:
+            continue
+    return {g: [files[r] for r in range(g)] for g, files in sets.items()
+            if len(files) == g and all(r in files for r in range(g))}
+
+
+def _step_of(path):
+    return int(torch.load(path, map_location="cpu", mmap=True).get("global_step", 0))
+
+
+def latest_checkpoint(path):
+    """(global_step, [files]) of the newest checkpoint at `path`: the single file Model.save writes, or a
+    sharded set of a multi-GPU run (`path.shard-r-of-g`, file r = block r of a mod-g partition); None if none"""
+    found = [(_step_of(path), [path])] if os.path.exists(path) else []
+    for g, files in shard_sets(path).items():
+        steps = {_step_of(f) for f in files}
+        if len(steps) == 1:                              # a set caught half-way through a save is not a checkpoint
+            found.append((steps.pop(), files))
+    return max(found, key=lambda c: c[0]) if found else None
+
+
+def load_checkpoint(path):
+    """merged state dict of latest_checkpoint(path)"""
+    best = latest_checkpoint(path)
+    if best is None:
+        raise IOError("no checkpoint at %s" % path)
+    state = {}
+    for f in best[1]:
+        state.update(torch.load(f, map_location="cpu"))
+    return state
+
+
 class Model(object):
     # defaults of the reference class attributes (tffm/fm_model.py:10-32)
     vocabulary_size = 8000000
@@ -468,7 +582,10 @@ class Model(object):
         return out
 
     def load_blocks_state(self, state):
-        nb, k = self.vocabulary_block_num, self.factor_num
+        """any mod partition: the number of blocks is the file's, not the config's (a sharded run of G GPUs
+        writes G blocks)"""
+        k = self.factor_num
+        nb = sum(1 for key in state if key.startswith("vocab_block_") and not key.endswith("/Adagrad"))
         for name, dst in (("", self.table), ("/Adagrad", self.accum)):
             for i in range(nb):
                 n = dst[i::nb].shape[0]
@@ -489,90 +606,47 @@ class Model(object):
         return dense.view(2, rows, nb, k + 1).transpose(1, 2).contiguous()   # [which, id % nb, id // nb, :]
 
     @staticmethod
-    def _write_blocks(path, host, global_step):
-        nb = host.shape[1]
+    def _blocks_dict(host, global_step):
         out = {"global_step": global_step}
         for w, name in enumerate(("", "/Adagrad")):
-            for i in range(nb):
+            for i in range(host.shape[1]):
                 out["vocab_block_%d%s" % (i, name)] = host[w, i]       # views of one storage: written once
-        os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
-        torch.save(out, path + ".tmp")
-        os.replace(path + ".tmp", path)                  # a reader never sees a half-written file
+        return out
+
+    def _writer(self):
+        if getattr(self, "_ckpt_writer", None) is None:
+            self._ckpt_writer = CheckpointWriter(self.device)
+        return self._ckpt_writer
 
     def save(self, path, wait=True, skip_if_busy=False):
         """Writes the checkpoint (reference variable layout, see blocks_state).  wait=False: the table is
         snapshotted on the device now (one strided device copy) and the D2H copy + file write run on a
-        background thread while training goes on.  One save is in flight at a time: a new one waits for it,
-        or -- skip_if_busy, for periodic saves that must never hold training up -- is dropped (returns False)."""
-        import threading
-        t = getattr(self, "_save_thread", None)
-        if skip_if_busy and t is not None and t.is_alive():
+        background thread while training goes on (CheckpointWriter).  One save is in flight at a time: a new
+        one waits for it, or -- skip_if_busy, for periodic saves that must never hold training up -- is
+        dropped (returns False)."""
+        w = self._writer()
+        if skip_if_busy and w.busy():
             return False
-        self.wait_for_save()
+        w.wait()
         snap = self._blocks_snapshot()
         if snap is None:                                 # no room for a snapshot: block by block, synchronously
             os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
             torch.save(self.blocks_state(), path + ".tmp")
             os.replace(path + ".tmp", path)
             return True
-        self.prepare_save()
-        ready = torch.cuda.Event()
-        ready.record(torch.cuda.current_stream(self.device))
-        snap.record_stream(self._save_stream)
-        step, stream, bounce = self.global_step, self._save_stream, self._save_bounce
-
-        def work():
-            # D2H through two pinned bounce buffers (asynchronous DMA: a pageable cudaMemcpy from this thread
-            # would hold the driver's lock and stall the training thread's launches), then the file
-            try:
-                host = torch.empty(snap.shape, dtype=torch.float32)
-                src, dst, chunk = snap.view(-1), host.view(-1), bounce.shape[1]
-                prev = None
-                with torch.cuda.stream(stream):
-                    stream.wait_event(ready)
-                    for i, lo in enumerate(range(0, src.numel(), chunk)):
-                        hi = min(src.numel(), lo + chunk)
-                        bounce[i % 2, :hi - lo].copy_(src[lo:hi], non_blocking=True)
-                        ev = torch.cuda.Event()
-                        ev.record(stream)
-                        if prev is not None:
-                            prev[0].synchronize()
-                            dst[prev[1]:prev[2]].copy_(bounce[prev[3], :prev[2] - prev[1]])
-                        prev = (ev, lo, hi, i % 2)
-                    if prev is not None:
-                        prev[0].synchronize()
-                        dst[prev[1]:prev[2]].copy_(bounce[prev[3], :prev[2] - prev[1]])
-                self._write_blocks(path, host, step)
-            except BaseException as e:       # surfaces in wait_for_save()
-                self._save_error = e
-                if wait:
-                    raise
-
-        if wait:
-            work()
-        else:
-            self._save_thread = threading.Thread(target=work, name="fm-checkpoint")
-            self._save_thread.start()
+        step = self.global_step
+        w.write(path, snap, lambda host: self._blocks_dict(host, step), wait=wait)
         return True
 
     def prepare_save(self):
-        """stream and pinned bounce buffers of the background checkpoint writer (page-locking memory stalls
-        other CUDA calls: do it before the training loop starts)"""
-        if getattr(self, "_save_stream", None) is None:
-            self._save_stream = torch.cuda.Stream(device=self.device)
-            self._save_bounce = torch.empty(2, 8 << 20, dtype=torch.float32).pin_memory()     # 2 x 32 MiB
+        self._writer().prepare()
 
     def wait_for_save(self):
-        t = getattr(self, "_save_thread", None)
-        if t is not None:
-            t.join()
-            self._save_thread = None
-        err, self._save_error = getattr(self, "_save_error", None), None
-        if err is not None:
-            raise RuntimeError("writing the checkpoint failed: %r" % (err,))
+        self._writer().wait()
 
     def restore(self, path):
-        self.load_blocks_state(torch.load(path, map_location="cpu"))
+        """a file written by Model.save, or the sharded set of a multi-GPU run at the same path"""
+        self.load_blocks_state(load_checkpoint(path))
 
 
 def _off(t, index):

@@ -36,7 +36,7 @@ import torch.distributed as dist
 
 from . import _lib
 from ._lib import check, load, ptr, stream
-from .fm_model import Model, _ld_for, _stride_for
+from .fm_model import CheckpointWriter, Model, latest_checkpoint, load_checkpoint, _ld_for, _stride_for
 from .fm_ops import FmParseError, PackedLines, pack_lines
 
 INFO_NNZ, INFO_UNIQUE, INFO_ERROR, INFO_COUNTS = 0, 1, 2, 3   # layout of the per-rank info vector
@@ -365,40 +365,66 @@ class PeerShardedModel:
         """[V, K+1] on every rank (tests / checkpoints)"""
         return self._gather_full(self.table)
 
-    # checkpoints in the reference's variable layout (vocab_block_i[id // nb] for id % nb == i), the
-    # same file a single-GPU Model writes and reads: a sharded run can be scored by one GPU and back
-    def save(self, path):
-        """collective; rank 0 writes"""
-        import os
-        nb, v, k = self.cfg.vocabulary_block_num, self.cfg.vocabulary_size, self.cfg.factor_num
-        out = {"global_step": self.global_step}
-        for name, shard in (("", self.table), ("/Adagrad", self.accum)):
-            full = self._gather_full(shard)
-            if self.rank == 0:
-                for i in range(nb):
-                    blk = torch.zeros(v // nb + 1, k + 1, dtype=torch.float32)
-                    part = full[i::nb].cpu()
-                    blk[:part.shape[0]] = part
-                    out["vocab_block_%d%s" % (i, name)] = blk
-            del full
-        if self.rank == 0:
-            os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
-            torch.save(out, path)
+    # Checkpoints: rank r's shard IS block r of the reference's variable layout with vocabulary_block_num = G
+    # (vocab_block_r[id // G] for id % G == r), so every rank writes its own file `path.shard-r-of-G` --
+    # no gather, written in the background like Model.save -- and any reader (a single-GPU Model, a run on a
+    # different number of GPUs) merges the set with the same mod arithmetic (fm_model.load_checkpoint).
+    def _writer(self):
+        if getattr(self, "_ckpt_writer", None) is None:
+            self._ckpt_writer = CheckpointWriter(self.device)
+        return self._ckpt_writer
+
+    def prepare_save(self):
+        self._writer().prepare()
+
+    def wait_for_save(self):
+        self._writer().wait()
         dist.barrier(group=self.group)
 
+    def save(self, path, wait=True, skip_if_busy=False):
+        """collective (every rank at the same step).  skip_if_busy: dropped on all ranks if any rank's writer
+        is still busy with the previous set (returns False)."""
+        w, k, r, g = self._writer(), self.cfg.factor_num, self.rank, self.world
+        if skip_if_busy:
+            busy = torch.tensor([1 if w.busy() else 0], dtype=torch.int32, device=self.device)
+            dist.all_reduce(busy, op=dist.ReduceOp.MAX, group=self.group)
+            if int(busy.item()):
+                return False
+        w.wait()
+        snap = torch.stack([self.table[:, :k + 1], self.accum[:, :k + 1]]).contiguous()
+        step = self.global_step
+
+        def state(host):
+            return {"global_step": step, "vocab_block_%d" % r: host[0], "vocab_block_%d/Adagrad" % r: host[1]}
+
+        w.write("%s.shard-%d-of-%d" % (path, r, g), snap, state, wait=wait)
+        if wait:
+            dist.barrier(group=self.group)
+        return True
+
     def restore(self, path):
-        """every rank reads the file and keeps its rows"""
-        nb, v, k, g, r = (self.cfg.vocabulary_block_num, self.cfg.vocabulary_size, self.cfg.factor_num, self.world,
-                          self.rank)
-        state = torch.load(path, map_location="cpu")
-        for name, shard in (("", self.table), ("/Adagrad", self.accum)):
-            full = torch.zeros(v, k + 1, dtype=torch.float32)
-            for i in range(nb):
-                n = full[i::nb].shape[0]
-                full[i::nb] = state["vocab_block_%d%s" % (i, name)][:n]
-            mine = full[r::g]
-            shard[:mine.shape[0], :k + 1] = mine.to(self.device)
-        self.global_step = int(state.get("global_step", 0))
+        """the newest checkpoint at `path`: this rank's own file if the set was written by as many GPUs,
+        else (single-GPU file, other GPU count) the merged table, of which the rank keeps its rows"""
+        v, k, g, r = self.cfg.vocabulary_size, self.cfg.factor_num, self.world, self.rank
+        best = latest_checkpoint(path)
+        if best is None:
+            raise IOError("no checkpoint at %s" % path)
+        if len(best[1]) == g and best[1][0] != path:      # a set written by as many GPUs
+            state = torch.load(best[1][r], map_location="cpu")
+            for name, shard in (("", self.table), ("/Adagrad", self.accum)):
+                blk = state["vocab_block_%d%s" % (r, name)]
+                shard[:blk.shape[0], :k + 1] = blk.to(self.device)
+        else:
+            state = load_checkpoint(path)
+            nb = sum(1 for key in state if key.startswith("vocab_block_") and not key.endswith("/Adagrad"))
+            for name, shard in (("", self.table), ("/Adagrad", self.accum)):
+                full = torch.zeros(v, k + 1, dtype=torch.float32)
+                for i in range(nb):
+                    n = full[i::nb].shape[0]
+                    full[i::nb] = state["vocab_block_%d%s" % (i, name)][:n]
+                mine = full[r::g]
+                shard[:mine.shape[0], :k + 1] = mine.to(self.device)
+        self.global_step = int(best[0])
         torch.cuda.synchronize(self.device)
         dist.barrier(group=self.group)
 

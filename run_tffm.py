@@ -29,6 +29,7 @@ import torch
 from tffm.fm_model import Model
 from fast_tffm_b200 import data as fm_data
 from fast_tffm_b200 import fm_ops
+from fast_tffm_b200.fm_model import latest_checkpoint
 from fast_tffm_b200.pipeline import HostBatchPipeline
 
 
@@ -80,7 +81,7 @@ def train_sharded(cfg, monitor, stream_mb=None):
     dist.init_process_group("nccl", device_id=device)
     model = PeerShardedModel(cfg, device=device).build(seed=int(time.time()) // 60)
     ckpt = None if cfg.log_dir is None else _ckpt_path(cfg)
-    if ckpt is not None and os.path.exists(ckpt):
+    if ckpt is not None and latest_checkpoint(ckpt) is not None:
         model.restore(ckpt)
     say = print if rank == 0 else (lambda *a, **k: None)
 
@@ -110,8 +111,10 @@ def train_sharded(cfg, monitor, stream_mb=None):
     seed = torch.tensor([int(time.time())], dtype=torch.int64, device=device)
     dist.broadcast(seed, 0)
     dataset = _training_set(cfg, device, stream_mb)
+    if ckpt is not None:
+        model.prepare_save()
     st = time.time()
-    start_step = step_num = model.global_step
+    start_step = step_num = saved_step = model.global_step
 
     def slices():
         for lines, weights in dataset.batches(cfg.batch_size, cfg.num_epochs, shuffle=True, seed=int(seed.item())):
@@ -141,8 +144,8 @@ def train_sharded(cfg, monitor, stream_mb=None):
         if step_num % cfg.save_steps == 0:
             report(*pending.pop())
             cur = time.time()
-            if ckpt is not None:
-                model.save(ckpt)
+            if ckpt is not None and model.save(ckpt, wait=False, skip_if_busy=True):   # every rank its own shard file
+                saved_step = step_num
             if vdata is not None:
                 v_loss = validation_loss(vdata)          # the same number on every rank: all stop together
                 say('validation loss at step %d: %.8f' % (step_num, v_loss))
@@ -154,7 +157,9 @@ def train_sharded(cfg, monitor, stream_mb=None):
     total = time.time() - st
     say('Average speed: ', (step_num - start_step) * cfg.batch_size / total, ' ex/s')
     if ckpt is not None:
-        model.save(ckpt)
+        if saved_step != step_num:
+            model.save(ckpt, wait=False)
+        model.wait_for_save()
     say('Model saved to ', cfg.log_dir)
     dist.destroy_process_group()
 
@@ -262,7 +267,7 @@ def main():
         train_sharded(model, args.monitor, args.stream_mb)
         return
     model.build(seed=int(time.time()))
-    if model.log_dir is not None and os.path.exists(_ckpt_path(model)):
+    if model.log_dir is not None and latest_checkpoint(_ckpt_path(model)) is not None:
         model.restore(_ckpt_path(model))     # MonitoredTrainingSession(checkpoint_dir=log_dir) restores
     elif args.task == 'predict':
         print("No checkpoint in", model.log_dir)

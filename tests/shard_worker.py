@@ -67,3 +67,33 @@ def run_bad_line(rank, world, port, lines, cfg_kw, init, out_dir, mode):
         np.save(os.path.join(out_dir, "after_good.npy"), after_good)
     dist.barrier()
     dist.destroy_process_group()
+
+
+def run_checkpoint(rank, world, port, lines, cfg_kw, init, out_dir):
+    """save in the background after step 2, keep training, restore into a fresh sharded model"""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    device = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world)
+    from fast_tffm_b200.fm_model import Model
+    from fast_tffm_b200.sharded import PeerShardedModel
+    m = PeerShardedModel(Model(**cfg_kw), device=device).build(init_table=init)
+    per = cfg_kw["batch_size"] // world
+    path = os.path.join(out_dir, "ckpt", "model.ckpt.pt")
+    for s in range(3):
+        lo = s * cfg_kw["batch_size"] + rank * per
+        m.train_step(lines[lo:lo + per])
+        if s == 1:
+            at_save = m.gather_full_table().cpu().numpy()
+            assert m.save(path, wait=False)
+            assert m.save(path, wait=False, skip_if_busy=True) in (True, False)     # never blocks, never corrupts
+    m.wait_for_save()
+    m2 = PeerShardedModel(Model(**cfg_kw), device=device).build(seed=9)
+    m2.restore(path)
+    restored = m2.gather_full_table().cpu().numpy()
+    if rank == 0:
+        np.save(os.path.join(out_dir, "at_save.npy"), at_save)
+        np.save(os.path.join(out_dir, "restored.npy"), restored)
+        np.save(os.path.join(out_dir, "step.npy"), np.int64([m2.global_step]))
+    dist.barrier()
+    dist.destroy_process_group()

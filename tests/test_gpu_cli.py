@@ -97,9 +97,18 @@ def test_train_under_torchrun_then_predict_on_one_gpu(tmp_path):
     assert len(losses) == 15 and np.mean(losses[-3:]) < np.mean(losses[:3])     # printed once (rank 0), and learning
     v = [float(x) for x in re.findall(r"validation loss at step \d+: ([0-9.]+)", out.stdout)]
     assert len(v) == 3 and v[-1] < v[0]
-    assert (tmp_path / "log" / "model.ckpt.pt").exists()
+    # every rank wrote its shard (= block r of a mod-2 partition); one GPU reads the set back
+    assert all((tmp_path / "log" / ("model.ckpt.pt.shard-%d-of-2" % r)).exists() for r in range(2))
     out = subprocess.run([sys.executable, os.path.join(ROOT, "run_tffm.py"), "predict", str(tmp_path / "t.cfg")],
                          capture_output=True, text=True, env=env, cwd=ROOT)
     assert out.returncode == 0, out.stdout + out.stderr
     scores = [float(x) for x in open(tmp_path / "test_0_score")]
     assert len(scores) == 500 and np.isfinite(scores).all() and np.std(scores) > 0
+    # a single-GPU run continues from the set and supersedes it with its own (newer) file
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "run_tffm.py"), "train", str(tmp_path / "t.cfg")],
+                         capture_output=True, text=True, env=env, cwd=ROOT)
+    assert out.returncode == 0, out.stdout + out.stderr
+    steps = [int(x) for x in re.findall(r"-- Global Step: (\d+);", out.stdout)]
+    assert steps == list(range(16, 31)) and (tmp_path / "log" / "model.ckpt.pt").exists()
+    from fast_tffm_b200.fm_model import latest_checkpoint
+    assert latest_checkpoint(str(tmp_path / "log" / "model.ckpt.pt"))[0] == 30

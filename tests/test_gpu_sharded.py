@@ -70,3 +70,25 @@ def test_parse_error_on_one_rank_voids_the_step_everywhere(criteo_lines, tmp_pat
     ref, exp = _reference(lines, [1.0] * len(lines), cfg_kw, init, 0, 2)
     e = ref.train_step(lines[:200])
     np.testing.assert_allclose(np.load(tmp_path / "after_good.npy"), ref.flat_table(), rtol=1e-4, atol=1e-7)
+
+
+def test_sharded_checkpoint_set(criteo_lines, tmp_path):
+    """every rank writes block r of a mod-G partition in the background; a sharded model and a single-GPU
+    Model both restore the table as it was when save() was called"""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    lines, _ = criteo_lines
+    rng = np.random.default_rng(8)
+    cfg_kw = dict(vocabulary_size=170003, factor_num=10, batch_size=200, hash_feature_id=False, factor_lambda=1e-3,
+                  bias_lambda=1e-3, learning_rate=0.05, adagrad_init_accumulator=0.1, loss_type="logistic",
+                  vocabulary_block_num=7)
+    init = rng.uniform(-0.01, 0.01, (cfg_kw["vocabulary_size"], 11)).astype(np.float32)
+    mp.spawn(shard_worker.run_checkpoint, args=(2, 29871, lines, cfg_kw, init, str(tmp_path)), nprocs=2, join=True)
+    at_save = np.load(tmp_path / "at_save.npy")
+    assert not np.array_equal(at_save, init)
+    np.testing.assert_array_equal(np.load(tmp_path / "restored.npy"), at_save)
+    assert int(np.load(tmp_path / "step.npy")[0]) == 2
+    from fast_tffm_b200.fm_model import Model
+    m = Model(**cfg_kw).build("cuda:0", seed=3)
+    m.restore(str(tmp_path / "ckpt" / "model.ckpt.pt"))
+    np.testing.assert_array_equal(m.table[:, :11].cpu().numpy(), at_save)
