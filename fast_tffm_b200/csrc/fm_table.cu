@@ -70,6 +70,36 @@ adagrad_kernel(float* __restrict__ table, float* __restrict__ accum, int64_t tab
   }
 }
 
+// float4 flavour: thread per (row, 16-byte chunk); columns >= width (row padding) pass through untouched
+__global__ void __launch_bounds__(256)
+adagrad_vec_kernel(float* __restrict__ table, float* __restrict__ accum, int64_t table_ld,
+                   const int64_t* __restrict__ ori_ids, int64_t n_max, const int64_t* __restrict__ n_dev,
+                   int width, int chunks, const float* __restrict__ grad, int64_t grad_ld, float lr,
+                   const unsigned long long* __restrict__ guard) {
+  if (guard && *guard != 0xffffffffffffffffull) return;
+  const int64_t total = dev_count(n_max, n_dev) * chunks;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t u = t / chunks;
+    const int c = (int)(t - u * chunks);
+    const int64_t at = ori_ids[u] * table_ld + 4 * c;
+    const float4 g4 = __ldg(reinterpret_cast<const float4*>(grad + u * grad_ld + 4 * c));
+    const float4 a4 = *reinterpret_cast<const float4*>(accum + at);
+    const float4 w4 = *reinterpret_cast<const float4*>(table + at);
+    const float g[4] = {g4.x, g4.y, g4.z, g4.w};
+    float a[4] = {a4.x, a4.y, a4.z, a4.w};
+    float w[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      if (4 * c + e < width) {
+        a[e] = fmaf(g[e], g[e], a[e]);
+        w[e] -= __fdiv_rn(lr * g[e], __fsqrt_rn(a[e]));
+      }
+    }
+    *reinterpret_cast<float4*>(accum + at) = make_float4(a[0], a[1], a[2], a[3]);
+    *reinterpret_cast<float4*>(table + at) = make_float4(w[0], w[1], w[2], w[3]);
+  }
+}
+
 template <template <int> class L, class... Args>
 void dispatch_width(int width, Args... args) {
   if (width <= 4) L<4>::run(args...);
@@ -173,9 +203,19 @@ FM_EXPORT int fm_sparse_adagrad(float* table, float* accum, int64_t table_ld, co
   FM_REQUIRE(n_unique >= 0 && factor_num >= 0 && table_ld >= width && grad_ld >= width, "fm_sparse_adagrad: bad shape");
   if (n_unique == 0) return FM_OK;
   FM_REQUIRE(table && accum && ori_ids && grad, "fm_sparse_adagrad: null pointer");
-  dispatch_width<AdagradLaunch>((int)width, table, accum, table_ld, ori_ids, n_unique, n_unique_dev, (int)width,
-                                grad, grad_ld, learning_rate, reinterpret_cast<const unsigned long long*>(guard),
-                                stream);
+  const int64_t chunks = (width + 3) / 4;
+  if (table_ld % 4 == 0 && grad_ld % 4 == 0 && table_ld >= 4 * chunks && grad_ld >= 4 * chunks &&
+      (((uintptr_t)table | (uintptr_t)accum | (uintptr_t)grad) & 15) == 0) {
+    int64_t blocks = (n_unique * chunks + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    adagrad_vec_kernel<<<(unsigned)blocks, 256, 0, stream>>>(table, accum, table_ld, ori_ids, n_unique, n_unique_dev,
+                                                            (int)width, (int)chunks, grad, grad_ld, learning_rate,
+                                                            reinterpret_cast<const unsigned long long*>(guard));
+  } else {
+    dispatch_width<AdagradLaunch>((int)width, table, accum, table_ld, ori_ids, n_unique, n_unique_dev, (int)width,
+                                  grad, grad_ld, learning_rate, reinterpret_cast<const unsigned long long*>(guard),
+                                  stream);
+  }
   FM_LAUNCH_CHECK();
   return FM_OK;
 }
