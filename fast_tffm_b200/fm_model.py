@@ -14,6 +14,7 @@ small status block per step.
 What is NOT here (TF runtime machinery, out of scope per SURVEY.md section 8):
 queue runners, the gRPC parameter server, SavedModel export, summaries.
 """
+import collections
 import configparser
 import glob
 import os
@@ -198,6 +199,7 @@ class Model(object):
         self._slots = {}
         self._ahead_slot = 2     # parse_ahead alternates between buffer sets 1 and 2; set 0 serves inline steps / predict
         self._parse_stream = None
+        self._bg_blocks, self._late, self._late_q = None, 0.0, collections.deque()
 
     # ---- INI config, same sections / keys as tffm/fm_model.py:367-475 -----------------
     def _get_config(self, config_file, verbose=True):
@@ -334,11 +336,28 @@ class Model(object):
         side.wait_stream(main) if b.get("free") is None else side.wait_event(b["free"])
         if after is not None:      # e.g. the event of the H2D copy that brings `packed` in
             side.wait_event(after)
+        if self._bg_blocks is None:
+            self._bg_blocks = self.BACKGROUND_PARSE_BLOCKS
         with torch.cuda.stream(side):
-            self._parse_unique(packed, b, unique=False, max_blocks=self.BACKGROUND_PARSE_BLOCKS)
-            done = torch.cuda.Event()
+            self._parse_unique(packed, b, unique=False, max_blocks=self._bg_blocks)
+            done = torch.cuda.Event(enable_timing=True)
             done.record(side)
         return dict(b=b, done=done, packed=packed)
+
+    def _adapt_parse_grid(self, need, done):
+        """The run-ahead parse is a thin background kernel (BACKGROUND_PARSE_BLOCKS blocks) so that it takes
+        little from the memory-bound table kernels.  When those are short (few distinct ids per batch) the
+        thin parse finishes after the step needs it: `need` (main stream, just before it waits) then precedes
+        `done` (side stream, end of the parse).  Read a few steps later, without blocking; if the parse keeps
+        being late its grid is doubled, up to the full grid."""
+        q = self._late_q
+        q.append((need, done))
+        while q and q[0][0].query() and q[0][1].query():
+            n, d = q.popleft()
+            self._late = 0.8 * self._late + 0.2 * n.elapsed_time(d)      # ms, > 0: the step waited
+        if self._late > 0.02 and self._bg_blocks:
+            self._bg_blocks = self._bg_blocks * 2 if self._bg_blocks < 1024 else 0    # 0 = no cap
+            self._late = 0.0
 
     def _gtab(self):
         if self.gtab is None:
@@ -458,7 +477,11 @@ class Model(object):
         if path == "claim":
             gtab = self._gtab()
             if parsed is not None:
-                torch.cuda.current_stream(self.device).wait_event(parsed["done"])
+                main = torch.cuda.current_stream(self.device)
+                need = torch.cuda.Event(enable_timing=True)
+                need.record(main)
+                main.wait_event(parsed["done"])
+                self._adapt_parse_grid(need, parsed["done"])
                 mark("parse_count")
                 mark("parse_fill")
             else:
