@@ -376,7 +376,7 @@ def run_ours(args):
     e2e_value = args.steps * b / (e2e_ms * 1e-3)
 
     os.sched_setaffinity(0, all_cpus)
-    base = cpu_baseline(2, 1, 16384, args.dist, os.cpu_count() or 1) if not args.no_cpu_baseline else None
+    base = cpu_baseline(16, 1, 65536, args.dist, os.cpu_count() or 1) if not args.no_cpu_baseline else None
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
