@@ -320,5 +320,5 @@ def bind_host_to_gpu(index=None):
             return "gpu %s: none of numa node %d's cpus are available to this process" % (bus, node)
         os.sched_setaffinity(0, allowed)
         return "gpu %s: bound to %d cpus of numa node %d" % (bus, len(allowed), node)
-    except (OSError, ValueError, AttributeError) as e:
+    except (OSError, ValueError, AttributeError, RuntimeError, AssertionError) as e:
         return "not bound (%s)" % e
