@@ -116,6 +116,8 @@ __device__ __forceinline__ uint32_t flag_eq(uint32_t w, uint32_t c) {   // byte 
 __device__ __forceinline__ uint32_t flag_ctrl(uint32_t w) {             // byte < 0x20
   return ~(((w & 0x7f7f7f7fu) + 0x60606060u) | w | 0x7f7f7f7fu);
 }
+// the four byte flags (bit 7 of each byte) of a word gathered into bits 0..3
+__device__ __forceinline__ uint32_t flag_bits(uint32_t f) { return (((f >> 7) * 0x00204081u) >> 21) & 0xfu; }
 __device__ __forceinline__ uint32_t flag_first_bytes(int n) {           // bytes 0..n-1 (n clipped to 0..4)
   return n <= 0 ? 0u : n >= 4 ? 0x80808080u : (0x80808080u >> (8 * (4 - n)));
 }
@@ -429,15 +431,17 @@ parse_fill_kernel(const uint8_t* __restrict__ text, int64_t limit, const int64_t
     if (p < e) { const uint4 v = load16(text + p); w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w; }
     const int lo = s > p ? (int)(s - p) : 0;
     const int hi = e - p >= 16 ? 16 : (e - p > 0 ? (int)(e - p) : 0);
-    uint32_t sp[4];
-    int n_here = 0;
+    // one bit per byte of the lane's 16: spaces and NULs inside [lo, hi)
+    const uint32_t in_line = hi > lo ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
+    uint32_t sp16 = 0, nul16 = 0;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const uint32_t v = flag_valid(k, lo, hi);
-      sp[k] = flag_eq(w[k], ' ') & v;
-      bad |= (flag_eq(w[k], 0) & v) != 0;  // a NUL ends the line early: sequential path
-      n_here += __popc(sp[k]);
+      sp16 |= flag_bits(flag_eq(w[k], ' ')) << (4 * k);
+      nul16 |= flag_bits(flag_eq(w[k], 0)) << (4 * k);
     }
+    sp16 &= in_line;
+    bad |= (nul16 & in_line) != 0;  // a NUL ends the line early: sequential path
+    int n_here = __popc(sp16);
     const bool first = pos <= s;                  // the chunk that holds the line start also lists the label
     if (first && c == 0) n_here += 1;
     int incl = n_here;
@@ -449,9 +453,7 @@ parse_fill_kernel(const uint8_t* __restrict__ text, int64_t limit, const int64_t
     const int tot = __shfl_sync(gm, incl, kLPL - 1, kLPL);
     int wpos = incl - n_here;
     if (first && c == 0) tok[wpos++] = (uint8_t)(s - pos);
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-      for (uint32_t f = sp[k]; f; f &= f - 1) tok[wpos++] = (uint8_t)(c * 16 + 4 * k + (__ffs(f) >> 3));
+    for (uint32_t f = sp16; f; f &= f - 1) tok[wpos++] = (uint8_t)(c * 16 + __ffs(f));  // the byte after the space
     __syncwarp(gm);
     for (int t = c; t < tot; t += kLPL) {
       // tok[] holds 0..128 (128 = the byte after a space that ends the chunk)
