@@ -175,6 +175,167 @@ grad_kernel(const int32_t* __restrict__ fids, const float* __restrict__ params, 
   }
 }
 
+// ---- float4 flavour (rows 16-byte aligned, ld a multiple of 4) --------------------------------
+// gs lanes share a row (gs = the float4 chunks of a K+1 wide row, at most 32; lane c of a group owns
+// chunks c, c + gs, ... T of them), a warp walks 32 / gs rows per step.  Columns past K (row padding)
+// are read but masked out.
+__device__ __forceinline__ float4 row_chunk(const float* row, int chunk, int K) {
+  float4 v = __ldg(reinterpret_cast<const float4*>(row + 4 * chunk));
+  const int col = 4 * chunk;
+  if (col + 1 > K) v.y = 0.f;
+  if (col + 2 > K) v.z = 0.f;
+  if (col + 3 > K) v.w = 0.f;
+  return v;
+}
+
+template <int T>
+__device__ __forceinline__ void gather_example_vec(const int32_t* __restrict__ fids, const float* __restrict__ params,
+                                                   int64_t ld, const float* __restrict__ vals, int start, int end,
+                                                   int K, int lane, int gs, float4 (&S)[T], float& q,
+                                                   float& bias_dot, float& bias_sq, float& fac_sq) {
+  const int RPW = 32 / gs, r = lane / gs, c = lane - r * gs;
+  const bool lane_on = r < RPW;
+  const int vc = (K + 4) >> 2;
+#pragma unroll
+  for (int t = 0; t < T; ++t) S[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+  q = bias_dot = bias_sq = fac_sq = 0.f;
+  for (int base = start; base < end; base += 32) {
+    const int j = base + lane;
+    const int my_fid = j < end ? fids[j] : 0;
+    const float my_x = j < end ? vals[j] : 0.f;
+    const int rows_here = min(32, end - base);
+#pragma unroll 4
+    for (int s = 0; s * RPW < rows_here; ++s) {  // warp-uniform
+      const int jj = s * RPW + r;
+      const int fid = __shfl_sync(kFull, my_fid, jj & 31);
+      const float x = __shfl_sync(kFull, my_x, jj & 31);
+      if (lane_on && jj < rows_here) {
+        const float* row = params + (int64_t)fid * ld;
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+          const int chunk = c + t * gs;
+          if (chunk < vc) {
+            float4 v = row_chunk(row, chunk, K);
+            if (chunk == 0) {  // column 0 is the bias
+              bias_dot = fmaf(x, v.x, bias_dot);
+              bias_sq = fmaf(v.x, v.x, bias_sq);
+              v.x = 0.f;
+            }
+            const float a0 = x * v.x, a1 = x * v.y, a2 = x * v.z, a3 = x * v.w;
+            S[t].x += a0; S[t].y += a1; S[t].z += a2; S[t].w += a3;
+            q = fmaf(a0, a0, fmaf(a1, a1, fmaf(a2, a2, fmaf(a3, a3, q))));
+            fac_sq = fmaf(v.x, v.x, fmaf(v.y, v.y, fmaf(v.z, v.z, fmaf(v.w, v.w, fac_sq))));
+          }
+        }
+      }
+    }
+  }
+  // column totals over the row groups (lanes c, c + gs, ...): every lane ends up with its columns' totals
+#pragma unroll
+  for (int t = 0; t < T; ++t) {
+    float4 tot = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int g2 = 0; g2 < RPW; ++g2) {
+      const int src = c + g2 * gs;
+      tot.x += __shfl_sync(kFull, S[t].x, src);
+      tot.y += __shfl_sync(kFull, S[t].y, src);
+      tot.z += __shfl_sync(kFull, S[t].z, src);
+      tot.w += __shfl_sync(kFull, S[t].w, src);
+    }
+    S[t] = tot;
+  }
+}
+
+template <int T>
+__global__ void __launch_bounds__(kWarps * 32)
+score_vec_kernel(const int32_t* __restrict__ fids, const float* __restrict__ params, int64_t ld,
+                 const float* __restrict__ vals, const int32_t* __restrict__ poses, int64_t batch, int K,
+                 float lam_f, float lam_b, float* __restrict__ pred, float* __restrict__ reg_partials, int gs) {
+  __shared__ float s_reg[kWarps];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t i = (int64_t)blockIdx.x * kWarps + warp;
+  float reg = 0.f;
+  if (i < batch) {
+    float4 S[T];
+    float q, bias_dot, bias_sq, fac_sq;
+    gather_example_vec<T>(fids, params, ld, vals, poses[i], poses[i + 1], K, lane, gs, S, q, bias_dot, bias_sq, fac_sq);
+    float second = 0.f;
+#pragma unroll
+    for (int t = 0; t < T; ++t) second += S[t].x * S[t].x + S[t].y * S[t].y + S[t].z * S[t].z + S[t].w * S[t].w;
+    if (lane >= gs) second = 0.f;  // every row group holds the same totals: count them once
+    const float p = warp_sum(bias_dot + 0.5f * (second - q));
+    reg = warp_sum(0.5f * lam_f * fac_sq + 0.5f * lam_b * bias_sq);
+    if (lane == 0) pred[i] = p;
+  }
+  if (lane == 0) s_reg[warp] = reg;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) t += s_reg[w];
+    reg_partials[blockIdx.x] = t;
+  }
+}
+
+__device__ __forceinline__ void red_add_v4f(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// FmGrad on float4 chunks: the factor sums of pass A, then one 16-byte vector atomic per chunk and occurrence
+template <int T>
+__global__ void __launch_bounds__(kWarps * 32)
+grad_vec_kernel(const int32_t* __restrict__ fids, const float* __restrict__ params, int64_t ld,
+                const float* __restrict__ vals, const int32_t* __restrict__ poses, int64_t batch, int K,
+                float lam_f, float lam_b, const float* __restrict__ pred_grad, float reg_grad_host,
+                const float* __restrict__ reg_grad_dev, float* __restrict__ grad, int gs) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t i = (int64_t)blockIdx.x * kWarps + warp;
+  if (i >= batch) return;
+  const int RPW = 32 / gs, r = lane / gs, c = lane - r * gs;
+  const bool lane_on = r < RPW;
+  const int vc = (K + 4) >> 2;
+  const int start = poses[i], end = poses[i + 1];
+  float4 S[T];
+  float q, bias_dot, bias_sq, fac_sq;
+  gather_example_vec<T>(fids, params, ld, vals, start, end, K, lane, gs, S, q, bias_dot, bias_sq, fac_sq);
+  const float pg = pred_grad[i];
+  const float reg_grad = reg_grad_dev ? __ldg(reg_grad_dev) : reg_grad_host;
+  const float rf = reg_grad * lam_f, rb = reg_grad * lam_b;
+  for (int base = start; base < end; base += 32) {
+    const int j = base + lane;
+    const int my_fid = j < end ? fids[j] : 0;
+    const float my_x = j < end ? vals[j] : 0.f;
+    const int rows_here = min(32, end - base);
+#pragma unroll 4
+    for (int s = 0; s * RPW < rows_here; ++s) {
+      const int jj = s * RPW + r;
+      const int fid = __shfl_sync(kFull, my_fid, jj & 31);
+      const float x = __shfl_sync(kFull, my_x, jj & 31);
+      if (lane_on && jj < rows_here) {
+        const float* row = params + (int64_t)fid * ld;
+        float* grow = grad + (int64_t)fid * ld;
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+          const int chunk = c + t * gs;
+          if (chunk < vc) {
+            const float4 v = row_chunk(row, chunk, K);
+            const float rv[4] = {v.x, v.y, v.z, v.w};
+            const float sv[4] = {S[t].x, S[t].y, S[t].z, S[t].w};
+            float o[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int col = 4 * chunk + e;
+              if (col == 0) o[e] = fmaf(pg, x, rb * rv[e]);                              // fm_grad_op.h:88-89
+              else if (col <= K) o[e] = rf * rv[e] - pg * x * x * rv[e] + pg * x * sv[e];  // :96-97
+              else o[e] = 0.f;
+            }
+            red_add_v4f(grow + 4 * chunk, o[0], o[1], o[2], o[3]);
+          }
+        }
+      }
+    }
+  }
+}
+
 // zero-fill of the first *rows_dev rows when the row count lives on the device
 __global__ void __launch_bounds__(256)
 zero_rows_kernel(float4* __restrict__ p, int64_t max_vec, int64_t ld, const int64_t* __restrict__ rows_dev) {
@@ -218,6 +379,16 @@ struct GradLaunch {
   }
 };
 
+// can the rows be walked as float4 chunks?  (ld a multiple of 4 covering the padded row, 16-byte aligned
+// bases, at most 3 chunks per lane)
+static inline bool vec_shape(int64_t K, int64_t ld, const void* a, const void* b, int* gs, int* t) {
+  const int64_t chunks = (K + 4) / 4;
+  if (ld % 4 != 0 || ld < 4 * chunks || (((uintptr_t)a | (uintptr_t)b) & 15) != 0) return false;
+  *gs = chunks <= 32 ? (int)chunks : 32;
+  *t = (int)((chunks + *gs - 1) / *gs);
+  return *t <= 3;
+}
+
 }  // namespace
 }  // namespace fm
 
@@ -241,10 +412,20 @@ FM_EXPORT int fm_score(const int32_t* feature_ids, const float* params, int64_t 
   const unsigned blocks = (unsigned)((batch + kWarps - 1) / kWarps);
   float* partials = reinterpret_cast<float*>(workspace);
   if (batch > 0) {
-    const int rc = dispatch<ScoreLaunch>(factor_num, feature_ids, params, params_ld, feature_vals, feature_poses,
-                                         batch, (int)factor_num, factor_lambda, bias_lambda, pred_score,
-                                         partials, blocks, stream);
-    if (rc != FM_OK) return rc;
+    int gs, t;
+    if (vec_shape(factor_num, params_ld, params, nullptr, &gs, &t)) {  // rows as 16-byte chunks
+#define CALL(T)                                                                                                  \
+  score_vec_kernel<T><<<blocks, kWarps * 32, 0, stream>>>(feature_ids, params, params_ld, feature_vals,          \
+                                                          feature_poses, batch, (int)factor_num, factor_lambda,  \
+                                                          bias_lambda, pred_score, partials, gs)
+      if (t == 1) { CALL(1); } else if (t == 2) { CALL(2); } else { CALL(3); }
+#undef CALL
+    } else {
+      const int rc = dispatch<ScoreLaunch>(factor_num, feature_ids, params, params_ld, feature_vals, feature_poses,
+                                           batch, (int)factor_num, factor_lambda, bias_lambda, pred_score,
+                                           partials, blocks, stream);
+      if (rc != FM_OK) return rc;
+    }
     FM_LAUNCH_CHECK();
   }
   reduce_partials_kernel<<<1, 256, 0, stream>>>(partials, (int)blocks, 1.0f, reg_score);
@@ -274,10 +455,21 @@ FM_EXPORT int fm_grad(const int32_t* feature_ids, const float* params, int64_t p
   }
   if (batch == 0) return FM_OK;
   const unsigned blocks = (unsigned)((batch + kWarps - 1) / kWarps);
-  const int rc = dispatch<GradLaunch>(factor_num, feature_ids, params, params_ld, feature_vals, feature_poses,
-                                      batch, (int)factor_num, factor_lambda, bias_lambda, pred_grad, reg_grad,
-                                      reg_grad_dev, params_grad, blocks, stream);
-  if (rc != FM_OK) return rc;
+  int gs, t;
+  if (vec_shape(factor_num, params_ld, params, params_grad, &gs, &t)) {
+#define CALL(T)                                                                                                 \
+  grad_vec_kernel<T><<<blocks, kWarps * 32, 0, stream>>>(feature_ids, params, params_ld, feature_vals,          \
+                                                         feature_poses, batch, (int)factor_num, factor_lambda,  \
+                                                         bias_lambda, pred_grad, reg_grad, reg_grad_dev,        \
+                                                         params_grad, gs)
+    if (t == 1) { CALL(1); } else if (t == 2) { CALL(2); } else { CALL(3); }
+#undef CALL
+  } else {
+    const int rc = dispatch<GradLaunch>(factor_num, feature_ids, params, params_ld, feature_vals, feature_poses,
+                                        batch, (int)factor_num, factor_lambda, bias_lambda, pred_grad, reg_grad,
+                                        reg_grad_dev, params_grad, blocks, stream);
+    if (rc != FM_OK) return rc;
+  }
   FM_LAUNCH_CHECK();
   return FM_OK;
 }
