@@ -30,7 +30,10 @@ constexpr int kWarpsPerBlock = 8;
 constexpr int kLPL = 8;                    // lanes per line
 constexpr int kLinesPerWarp = 32 / kLPL;
 constexpr int kLinesPerBlock = kWarpsPerBlock * kLinesPerWarp;
-constexpr int kChunk = kLPL * 16;          // bytes per group iteration
+constexpr int kChunk = kLPL * 16;          // bytes per group iteration (count pass)
+constexpr int kFillChunk = kLPL * 32;      // fill pass: 32 bytes per lane, so that a chunk's ~18 tokens fill the
+                                           // group's 8 lanes three times (a 128-byte chunk's ~9 left the second
+                                           // round nearly empty)
 constexpr int kSlowThreads = 128, kSlowBlocks = 148;
 
 struct ParseWs {
@@ -414,7 +417,7 @@ parse_fill_kernel(const uint8_t* __restrict__ text, int64_t limit, const int64_t
                   int64_t vocab, int hash, const int32_t* __restrict__ poses, float* __restrict__ labels,
                   int64_t* __restrict__ ids, float* __restrict__ vals, int64_t capacity,
                   int32_t* __restrict__ slow_list, int* __restrict__ slow_count) {
-  __shared__ uint8_t s_tok[kWarpsPerBlock][kLinesPerWarp][kChunk + 4];
+  __shared__ uint16_t s_tok[kWarpsPerBlock][kLinesPerWarp][kFillChunk + 4];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane / kLPL, c = lane % kLPL;
   const unsigned gm = group_mask(lane);
   for (int64_t line = ((int64_t)blockIdx.x * kWarpsPerBlock + warp) * kLinesPerWarp + g; line < n_lines;
@@ -422,26 +425,28 @@ parse_fill_kernel(const uint8_t* __restrict__ text, int64_t limit, const int64_t
   const int64_t s = begins[line], e = ends[line] + end_adjust;
   const int64_t out_base = poses[line];
   const int32_t cnt = poses[line + 1] - poses[line];
-  uint8_t* tok = s_tok[warp][g];
+  uint16_t* tok = s_tok[warp][g];
   bool bad = out_base + cnt > capacity || e <= s;
   int32_t ord_base = -1;  // token -1 is the label
-  for (int64_t pos = s & ~(int64_t)15; pos < e && !bad; pos += kChunk) {
-    const int64_t p = pos + c * 16;
-    uint32_t w[4] = {0, 0, 0, 0};
+  for (int64_t pos = s & ~(int64_t)15; pos < e && !bad; pos += kFillChunk) {
+    const int64_t p = pos + c * 32;
+    uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (p < e) { const uint4 v = load16(text + p); w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w; }
-    const int lo = s > p ? (int)(s - p) : 0;
-    const int hi = e - p >= 16 ? 16 : (e - p > 0 ? (int)(e - p) : 0);
-    // one bit per byte of the lane's 16: spaces and NULs inside [lo, hi)
-    const uint32_t in_line = hi > lo ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
-    uint32_t sp16 = 0, nul16 = 0;
+    if (p + 16 < e) { const uint4 v = load16(text + p + 16); w[4] = v.x; w[5] = v.y; w[6] = v.z; w[7] = v.w; }
+    const int lo = s > p ? (int)(s - p) : 0;      // < 16: only the first chunk starts before the line
+    const int hi = e - p >= 32 ? 32 : (e - p > 0 ? (int)(e - p) : 0);
+    // one bit per byte of the lane's 32: spaces and NULs inside [lo, hi)
+    const uint32_t below_hi = hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u);
+    const uint32_t in_line = hi > lo ? (below_hi & ~((1u << lo) - 1u)) : 0u;
+    uint32_t sp32 = 0, nul32 = 0;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      sp16 |= flag_bits(flag_eq(w[k], ' ')) << (4 * k);
-      nul16 |= flag_bits(flag_eq(w[k], 0)) << (4 * k);
+    for (int k = 0; k < 8; ++k) {
+      sp32 |= flag_bits(flag_eq(w[k], ' ')) << (4 * k);
+      nul32 |= flag_bits(flag_eq(w[k], 0)) << (4 * k);
     }
-    sp16 &= in_line;
-    bad |= (nul16 & in_line) != 0;  // a NUL ends the line early: sequential path
-    int n_here = __popc(sp16);
+    sp32 &= in_line;
+    bad |= (nul32 & in_line) != 0;  // a NUL ends the line early: sequential path
+    int n_here = __popc(sp32);
     const bool first = pos <= s;                  // the chunk that holds the line start also lists the label
     if (first && c == 0) n_here += 1;
     int incl = n_here;
@@ -452,11 +457,11 @@ parse_fill_kernel(const uint8_t* __restrict__ text, int64_t limit, const int64_t
     }
     const int tot = __shfl_sync(gm, incl, kLPL - 1, kLPL);
     int wpos = incl - n_here;
-    if (first && c == 0) tok[wpos++] = (uint8_t)(s - pos);
-    for (uint32_t f = sp16; f; f &= f - 1) tok[wpos++] = (uint8_t)(c * 16 + __ffs(f));  // the byte after the space
+    if (first && c == 0) tok[wpos++] = (uint16_t)(s - pos);
+    for (uint32_t f = sp32; f; f &= f - 1) tok[wpos++] = (uint16_t)(c * 32 + __ffs(f));  // the byte after the space
     __syncwarp(gm);
     for (int t = c; t < tot; t += kLPL) {
-      // tok[] holds 0..128 (128 = the byte after a space that ends the chunk)
+      // tok[] holds 0..256 (256 = the byte after a space that ends the chunk)
       const int64_t q = pos + tok[t];
       const int32_t ordinal = ord_base + t;
       const bool is_label = ordinal < 0;
