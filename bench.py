@@ -50,27 +50,48 @@ def measured_peak_gbs():
 
 
 def algorithmic_bytes(n, u, b, k, text_bytes, fused):
-    """compulsory bytes per stage (fp32; ids i64 at the parser output).
-    Fused stages drop the intermediates they eliminate (gathered rows, pred_grad, dense grad) and
-    count what they add (the K+3-wide accumulator rows: one read-modify-write in the scatter, one
-    read + one clearing write in the update)."""
+    """Compulsory bytes per stage (fp32; ids i64 at the parser output) -> (strict, as_implemented).
+
+    strict: SURVEY.md section 8(d) to the letter -- each tensor that crosses a stage boundary once per write and
+    once per read, each DISTINCT row once per stage that needs it, and a fused stage DROPS the intermediates it
+    eliminates (gathered rows, pred_grad, the dense gradient) without adding anything of its own.  This is the
+    numerator of roofline.frac.
+    as_implemented: strict plus the traffic the chosen algorithm adds by design (the K+3-wide accumulator rows of
+    the claim / fused paths: one read-modify-write in the scatter, one read + one clearing write in the update;
+    the per-occurrence id list the claim update walks; the sort's key/payload passes and the [B, K+1] example
+    records of the sorted path).  Reported as frac_as_implemented."""
     rb = 4 * (k + 1)
     ab = 4 * (k + 3)
+    parse = text_bytes + 12 * n + 8 * b                # count + fill together
     if fused == "claim":   # no unique; the update walks the N occurrences' ids
-        return {
-            "parse": text_bytes + 12 * n + 8 * b,
-            "score_scatter": 12 * n + 4 * (b + 1) + 8 * b + u * rb + 2 * u * ab,
-            "adagrad": 8 * n + 2 * u * ab + 4 * u * rb,
-        }
+        strict = {"parse": parse,
+                  "score_scatter": 12 * n + 4 * (b + 1) + 8 * b + 2 * u * rb,     # rows read, gradient rows written
+                  "adagrad": 8 * u + 5 * u * rb}
+        impl = {"parse": parse,
+                "score_scatter": 12 * n + 4 * (b + 1) + 8 * b + u * rb + 2 * u * ab,
+                "adagrad": 8 * n + 2 * u * ab + 4 * u * rb}
+        return strict, impl
+    if fused == "sorted":  # run-ahead sort by id; the gradient rows are never materialised
+        strict = {"parse": parse,
+                  "sort": 12 * n + 8 * u + 4 * (b + 1),                           # section 8(d)'s unique + cumsum
+                  "score": 12 * n + 4 * (b + 1) + 8 * b + u * rb,
+                  "update": 8 * u + 4 * u * rb}
+        passes = 3 if k <= 16 else 4
+        impl = {"parse": parse,
+                "sort": 12 * n + 4 * n + passes * 2 * 12 * n + 12 * n,            # keys + payload per pass, heads
+                "score": 12 * n + 4 * (b + 1) + 8 * b + u * rb + b * rb,          # + the [B, K+1] example records
+                "update": 12 * n + 4 * u + n * rb + 4 * u * rb}                   # sorted pairs, record gathers (L2)
+        return strict, impl
     if fused == "fused":
-        return {
-            "parse": text_bytes + 12 * n + 8 * b,
-            "unique": 12 * n + 8 * u + 4 * (b + 1),
-            "score_scatter": 16 * n + 4 * (b + 1) + 8 * b + u * rb + 2 * u * ab,
-            "adagrad": 8 * u + 2 * u * ab + 4 * u * rb,
-        }
-    return {
-        "parse": text_bytes + 12 * n + 8 * b,          # count + fill together
+        strict = {"parse": parse,
+                  "unique": 12 * n + 8 * u + 4 * (b + 1),
+                  "score_scatter": 16 * n + 4 * (b + 1) + 8 * b + 2 * u * rb,
+                  "adagrad": 8 * u + 5 * u * rb}
+        impl = dict(strict, score_scatter=16 * n + 4 * (b + 1) + 8 * b + u * rb + 2 * u * ab,
+                    adagrad=8 * u + 2 * u * ab + 4 * u * rb)
+        return strict, impl
+    strict = {
+        "parse": parse,
         "unique": 12 * n + 8 * u + 4 * (b + 1),
         "lookup": 8 * u + 2 * u * rb,
         "score": 8 * n + 4 * (b + 1) + u * rb + 4 * b,
@@ -78,6 +99,28 @@ def algorithmic_bytes(n, u, b, k, text_bytes, fused):
         "grad": 8 * n + 4 * (b + 1) + 4 * b + 2 * u * rb,
         "adagrad": 8 * u + 5 * u * rb,
     }
+    return strict, dict(strict)
+
+
+def kernel_traffic(workload, dist, path, layout):
+    """DRAM bytes per launch per kernel from the committed `ncu --set full` capture of this very workload
+    (profiles/traffic_r2.json, else round 1's); {} when there is none for this workload / path / layout"""
+    for name in ("traffic_r2.json", "traffic_r1.json"):
+        tpath = os.path.join(ROOT, "profiles", name)
+        if not os.path.exists(tpath):
+            continue
+        doc = json.load(open(tpath))
+        for entry in doc.get("captures", [doc]):
+            if (entry.get("workload", "cfg2") == workload and entry.get("dist", "uniform") == dist
+                    and entry.get("path", "claim") == path and entry.get("layout", "interleaved") == layout):
+                return entry["dram_bytes_per_launch"]
+    return {}
+
+
+STAGE_KERNELS = {   # the kernels behind each stage mark (ncu names)
+    "claim": {"adagrad": ["fused_adagrad_claim"], "score_scatter": ["fused_score_scatter"],
+              "parse": ["parse_count_kernel", "parse_fill_kernel"]},
+}
 
 
 class ClockSampler(threading.Thread):
@@ -148,7 +191,9 @@ def cpu_baseline(steps, warmup, sample_lines, dist, threads):
             stage += ts
     names = ["parse", "unique", "lookup", "score", "loss", "grad", "adagrad"]
     return {"value": steps * sample_lines / total, "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": "%d steps of %d-line cfg2 batches (%s ids), all stages, oracle faithful-threaded build"
+            "sample": "%d steps of %d-line cfg2 batches (%s ids), all stages, oracle faithful-threaded build; a LOWER "
+                      "BOUND on the reference: parser and tf.unique are serial in the reference too, but the lookup "
+                      "and Adagrad row loops here are serial where TF runs one task per vocabulary block"
                       % (steps, sample_lines, dist),
             "ms_per_step": 1e3 * total / steps,
             "stage_ms": {n: round(1e3 * s / steps, 3) for n, s in zip(names, stage)}}
@@ -160,7 +205,7 @@ def run_reference(args):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    sample = 16384
+    sample = CFG["batch"]        # the benchmark's own batch: same config as the GPU arm
     base = cpu_baseline(args.steps, max(args.warmup, 1), sample, args.dist, threads)
     line = {
         "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
@@ -298,29 +343,32 @@ def run_ours(args):
     value = args.steps * b / (total_ms * 1e-3)
 
     # ---- roofline of the dominant stage -------------------------------------------
-    alg = algorithmic_bytes(nnz, n_unique, b, k, text_bytes, fused)
+    alg, alg_impl = algorithmic_bytes(nnz, n_unique, b, k, text_bytes, fused)
     merged = dict(stage_ms)
     merged["parse"] = merged.pop("parse_count") + merged.pop("parse_fill")
     peak, peak_kind = measured_peak_gbs()
-    per_stage = {n: {"ms": round(ms, 4), "alg_mb": round(alg[n] / 1e6, 2),
-                     "gbs": round(alg[n] / (ms * 1e-3) / 1e9, 1) if ms > 0 else None,
-                     "frac": round(alg[n] / (ms * 1e-3) / 1e9 / peak, 4) if ms > 0 else None}
-                 for n, ms in merged.items()}
+    layout_used = getattr(m, "layout", args.layout)
+    dram = kernel_traffic(args.workload, args.dist, fused, layout_used) if args.ld is None else {}
+    per_stage = {}
+    for n_, ms in merged.items():
+        kernels = STAGE_KERNELS.get(fused, {}).get(n_, [])
+        traffic_n = sum(dram[kn] for kn in kernels) if kernels and all(kn in dram for kn in kernels) else None
+        gbs = alg[n_] / (ms * 1e-3) / 1e9 if ms > 0 else None
+        per_stage[n_] = {"ms": round(ms, 4), "alg_mb": round(alg[n_] / 1e6, 2),
+                         "alg_mb_as_implemented": round(alg_impl[n_] / 1e6, 2),
+                         "gbs": round(gbs, 1) if gbs else None, "frac": round(gbs / peak, 4) if gbs else None,
+                         "frac_as_implemented": round(alg_impl[n_] / (ms * 1e-3) / 1e9 / peak, 4) if ms > 0 else None,
+                         "dram_mb": None if traffic_n is None else round(traffic_n / 1e6, 1),
+                         "traffic_ratio": None if traffic_n is None else round(traffic_n / alg[n_], 3)}
     # the dominant GATHER/SCATTER kernel: the longest of the table-touching stages
-    dom = max(merged, key=lambda n: merged[n])
-    # DRAM bytes per launch of that kernel from the committed ncu --set full capture of this very
-    # workload (profiles/traffic_r1.json); null for any other workload / path / layout
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "traffic_r1.json")
-    if (os.path.exists(tpath) and args.workload == "cfg2" and args.dist == "uniform" and fused == "claim"
-            and args.layout == "interleaved" and args.ld is None):
-        per_kernel = json.load(open(tpath))["dram_bytes_per_launch"]
-        stage_kernels = {"adagrad": ["fused_adagrad_claim"], "score_scatter": ["fused_score_scatter"],
-                         "parse": ["parse_count_kernel", "parse_fill_kernel"]}
-        if all(kn in per_kernel for kn in stage_kernels.get(dom, ["?"])):
-            traffic = sum(per_kernel[kn] for kn in stage_kernels[dom])
+    dom = max((n_ for n_ in merged if n_ not in ("parse", "sort")), key=lambda n_: merged[n_])
     roofline = {"bound": "hbm", "kernel": dom, "achieved": per_stage[dom]["gbs"], "peak": peak,
-                "peak_kind": peak_kind, "unit": "GB/s", "frac": per_stage[dom]["frac"], "traffic": traffic,
+                "peak_kind": peak_kind, "unit": "GB/s", "frac": per_stage[dom]["frac"],
+                "frac_as_implemented": per_stage[dom]["frac_as_implemented"],
+                "traffic": None if per_stage[dom]["dram_mb"] is None else int(per_stage[dom]["dram_mb"] * 1e6),
+                "traffic_ratio": per_stage[dom]["traffic_ratio"],
+                "bytes_rule": "frac = SURVEY 8(d) bytes (fused stages drop intermediates, add nothing) / kernel ms / "
+                              "peak; frac_as_implemented adds the traffic the algorithm itself introduces",
                 "step_frac": round(sum(alg.values()) / (total_ms / args.steps * 1e-3) / 1e9 / peak, 4),
                 "stages": per_stage,
                 "stages_note": "per-kernel ms from an untimed pass with the parse inline (nothing runs beside the "

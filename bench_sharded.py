@@ -16,6 +16,56 @@ import torch.distributed as dist
 import bench_data
 
 
+def parity_check(cls, cfg, world, rank, dev):
+    """One small step through the sharded model on every rank and through the single-GPU Model on rank 0, same
+    global batch, same explicit initial table: loss, scores and the trained table must agree to 1e-5 (relative, over
+    the magnitude of the summed terms).  Raises if they do not; the returned dict goes into the JSON line, so the
+    scaling runs carry their own evidence that G GPUs compute what one GPU computes."""
+    from fast_tffm_b200.fm_model import Model
+    vocab, k, per = 1 << 20, cfg["factor_num"], 512
+    gen = torch.Generator().manual_seed(1234)
+    init = (torch.rand(vocab, k + 1, generator=gen) - 0.5) * 0.02
+    kw = dict(vocabulary_size=vocab, factor_num=k, batch_size=per * world, hash_feature_id=True,
+              loss_type=cfg["loss_type"], learning_rate=0.05, adagrad_init_accumulator=cfg["init_acc"],
+              factor_lambda=1e-3, bias_lambda=1e-3)
+    text, off, _ = bench_data.criteo_batch(per * world, 777, "zipf")      # hot ids: rows shared between ranks
+    lines = [bytes(text[off[i]:off[i + 1] - 1]) for i in range(per * world)]
+    sm = cls(Model(**kw), device=dev).build(init_table=init)
+    loss = sm.train_step(lines[rank * per:(rank + 1) * per])
+    pred = sm.predict(lines[rank * per:(rank + 1) * per])
+    preds = [torch.empty_like(pred) for _ in range(world)]
+    dist.all_gather(preds, pred)
+    full = sm.gather_full_table()
+    out = None
+    if rank == 0:
+        one = Model(**kw).build(dev, init_table=init)
+        loss1 = one.train_step(lines)
+        pred1 = one.predict(lines)
+        t1, tg = one.table[:, :k + 1].double(), full.double()
+        moved = (t1 != init.to(dev).double()).any(1)
+        # scale of a score: sum |x b| + 0.5 sum_k (sum |x v_k|)^2 per example (the second-order term cancels)
+        bufs = one._bufs
+        nnz = int(bufs["status"][1])
+        ids, x = bufs["ids"][:nnz], bufs["vals"][:nnz].double().abs()
+        poses = bufs["poses"][:per * world + 1].long()
+        ex = torch.repeat_interleave(torch.arange(per * world, device=dev), poses[1:] - poses[:-1])
+        rows = t1[ids].abs()
+        lin = torch.zeros(per * world, dtype=torch.float64, device=dev).index_add_(0, ex, x * rows[:, 0])
+        fac = torch.zeros(per * world, k, dtype=torch.float64, device=dev).index_add_(0, ex, x[:, None] * rows[:, 1:])
+        pscale = lin + 0.5 * (fac ** 2).sum(1)
+        perr = float(((torch.cat(preds).double() - pred1.double()).abs() / (pred1.double().abs() + pscale)).max())
+        terr = float(((tg - t1).abs() / (t1.abs() + 0.05)).max())
+        lerr = abs(loss - loss1) / abs(loss1)
+        out = {"ok": bool(perr <= 1e-5 and terr <= 1e-5 and lerr <= 1e-5), "global_batch": per * world,
+               "rel_err_loss": lerr, "max_err_over_scale_pred": perr, "max_err_over_scale_table": terr,
+               "rows_moved": int(moved.sum()), "tolerance": 1e-5,
+               "what": "sharded step + predict on %d ranks vs single-GPU Model on rank 0, same batch and table" % world}
+        assert out["ok"], "multi-GPU parity check failed: %r" % (out,)
+    del sm
+    dist.barrier()
+    return out
+
+
 def run_sharded(args, cfg, workload_config):
     from bench import METRIC, UNIT, ClockSampler, algorithmic_bytes, measured_peak_gbs
     from fast_tffm_b200.fm_model import Model
@@ -36,6 +86,7 @@ def run_sharded(args, cfg, workload_config):
                   bias_lambda=cfg["bias_lambda"])
     peer = args.shard_mode == "peer"
     cls = PeerShardedModel if peer else ShardedModel
+    parity = parity_check(cls, cfg, world, rank, dev)
     m = cls(model, device=dev, max_nnz_per_line=cfg["nnz_per_line"]).build(seed=0)
     host, devb = [], []
     for i in range(args.batches):
@@ -150,7 +201,7 @@ def run_sharded(args, cfg, workload_config):
     if rank == 0:
         nnz, nuniq, sent = (float(x) / world for x in stats.tolist())
         text_bytes = int(host[0].offsets[-1])
-        alg = algorithmic_bytes(nnz, nuniq, b, k, text_bytes, "fused")
+        alg, _ = algorithmic_bytes(nnz, nuniq, b, k, text_bytes, "fused")
         peak, peak_kind = measured_peak_gbs()
         step_s = total_ms / args.steps * 1e-3
         gld = (k + 3 + 3) // 4 * 4
@@ -163,12 +214,17 @@ def run_sharded(args, cfg, workload_config):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, world, b),
-            "roofline": {"bound": "hbm", "kernel": "whole step (per rank)", "achieved": round(sum(alg.values()) / step_s / 1e9, 1),
-                         "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
-                         "frac": round(sum(alg.values()) / step_s / 1e9 / peak, 4), "traffic": None,
-                         "exchange": {"bytes_per_rank_per_direction": int(xbytes),
-                                      "gbs_if_exchange_were_the_whole_step": round(xbytes / step_s / 1e9, 1),
-                                      "nvlink_peer_copy_gbs_measured_reference": 770}},
+            # the step is bound by what crosses NVLink: bytes per rank per direction over the whole step
+            # time, against the peer-copy bandwidth B200_PROFILING.md states as measured on this pool (770 GB/s per
+            # direction per GPU; 900 nominal).  The HBM view of the same step stays beside it.
+            "roofline": {"bound": "nvlink", "kernel": "whole step (per rank, per direction)",
+                         "achieved": round(xbytes / step_s / 1e9, 1), "peak": 770.0,
+                         "peak_kind": "measured peer copy per direction (B200_PROFILING.md); nominal 900",
+                         "unit": "GB/s", "frac": round(xbytes / step_s / 1e9 / 770.0, 4), "traffic": None,
+                         "bytes_per_rank_per_direction": int(xbytes),
+                         "hbm": {"achieved": round(sum(alg.values()) / step_s / 1e9, 1), "peak": peak,
+                                 "peak_kind": peak_kind, "frac": round(sum(alg.values()) / step_s / 1e9 / peak, 4)}},
+            "parity_check": parity,
             "cpu_baseline": None,
             "e2e": {"value": args.steps * b * world / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": int(host[0].text.numel() + host[0].offsets.numel() * 8) * world,

@@ -307,9 +307,8 @@ fused_adagrad_kernel(float* __restrict__ table, float* __restrict__ accum, int64
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const int col = 4 * chunk + e;
-          float g = 0.f;
-          if (col == 0) g = fmaf(bias_scale, wv[e], av[e]);
-          else if (col <= K) g = fmaf(wv[e], fac_scale, av[e]);
+          if (col > K) continue;   // pad columns stay as they are (an accumulator pad of 0 would give 0 / sqrt(0))
+          const float g = col == 0 ? fmaf(bias_scale, wv[e], av[e]) : fmaf(wv[e], fac_scale, av[e]);
           hv[e] = fmaf(g, g, hv[e]);
           wv[e] -= __fdiv_rn(lr * g, __fsqrt_rn(hv[e]));
         }
@@ -393,9 +392,8 @@ fused_adagrad_claim_kernel(float* __restrict__ table, float* __restrict__ accum,
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const int col = 4 * chunk + e;
-          float gr = 0.f;
-          if (col == 0) gr = fmaf(bias_scale, wv[e], av[e]);
-          else if (col <= K) gr = fmaf(wv[e], fac_scale, av[e]);
+          if (col > K) continue;   // pad columns stay as they are (an accumulator pad of 0 would give 0 * inf)
+          const float gr = col == 0 ? fmaf(bias_scale, wv[e], av[e]) : fmaf(wv[e], fac_scale, av[e]);
           hv[e] = fmaf(gr, gr, hv[e]);
           wv[e] = fmaf(-lr * gr, rsqrtf(hv[e]), wv[e]);   // w -= lr g / sqrt(acc)  (TF: g * lr * rsqrt(acc))
         }
@@ -564,9 +562,8 @@ fused_adagrad_wide_kernel(float* __restrict__ table, float* __restrict__ accum, 
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const int col = 4 * chunk + e;
-          float gr = 0.f;
-          if (col == 0) gr = fmaf(bias_scale, wv[e], av[e]);
-          else if (col <= K) gr = fmaf(wv[e], fac_scale, av[e]);
+          if (col > K) continue;
+          const float gr = col == 0 ? fmaf(bias_scale, wv[e], av[e]) : fmaf(wv[e], fac_scale, av[e]);
           hv[e] = fmaf(gr, gr, hv[e]);
           wv[e] = fmaf(-lr * gr, rsqrtf(hv[e]), wv[e]);
         }
@@ -587,6 +584,21 @@ static inline int wide_warps(int64_t factor_num, size_t* smem) {
   if (w < 1) w = 1;
   *smem = w * per_warp;
   return (int)w;
+}
+
+// the wide kernels' dynamic shared memory opt-in, once per device instead of once per call
+static cudaError_t wide_smem_opt_in(bool peer) {
+  static bool done[2][64];
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev >= 0 && dev < 64 && done[peer][dev]) return cudaSuccess;
+  e = peer ? cudaFuncSetAttribute(fused_score_scatter_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)kWideSmemMax)
+           : cudaFuncSetAttribute(fused_score_scatter_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)kWideSmemMax);
+  if (e == cudaSuccess && dev >= 0 && dev < 64) done[peer][dev] = true;   // benign race: the attribute is idempotent
+  return e;
 }
 
 // bitmap of touched rows -> list of row numbers (and the bitmap is cleared on the way)
@@ -678,8 +690,7 @@ FM_EXPORT int fm_fused_score_scatter(const int64_t* feature_ids, const int32_t* 
     size_t smem = 0;
     const int warps = wide_warps(factor_num, &smem);
     if (warps == 0) return fm_fail(FM_E_LIMIT, "fm_fused_score_scatter: factor_num %lld too large", (long long)factor_num);
-    FM_CUDA(cudaFuncSetAttribute(fused_score_scatter_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)kWideSmemMax));
+    FM_CUDA(wide_smem_opt_in(false));
     fused_score_scatter_wide_kernel<false><<<blocks, warps * 32, smem, stream>>>(
         feature_ids, local_ids, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, table, table_ld,
         factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, gacc, gacc_ld, partials,
@@ -821,8 +832,7 @@ FM_EXPORT int fm_peer_score_scatter(const int64_t* feature_ids, const float* fea
     size_t smem = 0;
     const int warps = wide_warps(factor_num, &smem);
     if (warps == 0) return fm_fail(FM_E_LIMIT, "fm_peer_score_scatter: factor_num %lld too large", (long long)factor_num);
-    FM_CUDA(cudaFuncSetAttribute(fused_score_scatter_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)kWideSmemMax));
+    FM_CUDA(wide_smem_opt_in(true));
     fused_score_scatter_wide_kernel<true><<<blocks, warps * 32, smem, stream>>>(
         feature_ids, nullptr, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, peers.table[0],
         table_ld, factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, scatter_flag, gtab_ld, partials,

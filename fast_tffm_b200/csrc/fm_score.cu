@@ -389,6 +389,30 @@ static inline bool vec_shape(int64_t K, int64_t ld, const void* a, const void* b
   return *t <= 3;
 }
 
+// the scorer launch shared by fm_score and fm_score_noalloc: float4 chunks when the rows allow it
+// (vec_shape), else the scalar kernels; `partials` = one float per block
+static int launch_score(const int32_t* feature_ids, const float* params, int64_t params_ld,
+                        const float* feature_vals, const int32_t* feature_poses, int64_t batch,
+                        int64_t factor_num, float factor_lambda, float bias_lambda, float* pred_score,
+                        float* partials, unsigned blocks, cudaStream_t stream) {
+  int gs, t;
+  if (vec_shape(factor_num, params_ld, params, nullptr, &gs, &t)) {  // rows as 16-byte chunks
+#define CALL(T)                                                                                                  \
+  score_vec_kernel<T><<<blocks, kWarps * 32, 0, stream>>>(feature_ids, params, params_ld, feature_vals,          \
+                                                          feature_poses, batch, (int)factor_num, factor_lambda,  \
+                                                          bias_lambda, pred_score, partials, gs)
+    if (t == 1) { CALL(1); } else if (t == 2) { CALL(2); } else { CALL(3); }
+#undef CALL
+  } else {
+    const int rc = dispatch<ScoreLaunch>(factor_num, feature_ids, params, params_ld, feature_vals, feature_poses,
+                                         batch, (int)factor_num, factor_lambda, bias_lambda, pred_score,
+                                         partials, blocks, stream);
+    if (rc != FM_OK) return rc;
+  }
+  FM_LAUNCH_CHECK();
+  return FM_OK;
+}
+
 }  // namespace
 }  // namespace fm
 
@@ -412,21 +436,9 @@ FM_EXPORT int fm_score(const int32_t* feature_ids, const float* params, int64_t 
   const unsigned blocks = (unsigned)((batch + kWarps - 1) / kWarps);
   float* partials = reinterpret_cast<float*>(workspace);
   if (batch > 0) {
-    int gs, t;
-    if (vec_shape(factor_num, params_ld, params, nullptr, &gs, &t)) {  // rows as 16-byte chunks
-#define CALL(T)                                                                                                  \
-  score_vec_kernel<T><<<blocks, kWarps * 32, 0, stream>>>(feature_ids, params, params_ld, feature_vals,          \
-                                                          feature_poses, batch, (int)factor_num, factor_lambda,  \
-                                                          bias_lambda, pred_score, partials, gs)
-      if (t == 1) { CALL(1); } else if (t == 2) { CALL(2); } else { CALL(3); }
-#undef CALL
-    } else {
-      const int rc = dispatch<ScoreLaunch>(factor_num, feature_ids, params, params_ld, feature_vals, feature_poses,
-                                           batch, (int)factor_num, factor_lambda, bias_lambda, pred_score,
-                                           partials, blocks, stream);
-      if (rc != FM_OK) return rc;
-    }
-    FM_LAUNCH_CHECK();
+    const int rc = launch_score(feature_ids, params, params_ld, feature_vals, feature_poses, batch, factor_num,
+                                factor_lambda, bias_lambda, pred_score, partials, blocks, stream);
+    if (rc != FM_OK) return rc;
   }
   reduce_partials_kernel<<<1, 256, 0, stream>>>(partials, (int)blocks, 1.0f, reg_score);
   FM_LAUNCH_CHECK();
@@ -551,12 +563,10 @@ FM_EXPORT int fm_score_noalloc(const int32_t* feature_ids, const float* params, 
   const int rc0 = noalloc_scratch_for_current_device(&partials);
   if (rc0 != FM_OK) return rc0;
   const unsigned blocks = (unsigned)((batch + kWarps - 1) / kWarps);
-  if (batch > 0) {
-    const int rc = dispatch<ScoreLaunch>(factor_num, feature_ids, params, params_ld, feature_vals, feature_poses,
-                                         batch, (int)factor_num, factor_lambda, bias_lambda, pred_score,
-                                         partials, blocks, stream);
+  if (batch > 0) {   // the same kernels fm_score launches for these shapes
+    const int rc = launch_score(feature_ids, params, params_ld, feature_vals, feature_poses, batch, factor_num,
+                                factor_lambda, bias_lambda, pred_score, partials, blocks, stream);
     if (rc != FM_OK) return rc;
-    FM_LAUNCH_CHECK();
   }
   reduce_partials_kernel<<<1, 256, 0, stream>>>(partials, (int)blocks, 1.0f, reg_score);
   FM_LAUNCH_CHECK();

@@ -110,13 +110,19 @@ class DeviceDataset:
             ends.append(off[1:])
         self.begins = torch.cat(begins) if begins else torch.zeros(0, dtype=torch.int64, device=self.device)
         self.ends = torch.cat(ends) if ends else torch.zeros(0, dtype=torch.int64, device=self.device)
-        self.lines = fm_ops.PackedLines(self.text, begins=self.begins, ends=self.ends)
+        longest = int((self.ends - self.begins).max()) if self.begins.numel() else 0
+        self.lines = fm_ops.PackedLines(self.text, begins=self.begins, ends=self.ends, max_line_bytes=longest)
         self.weights = None
         if weight_files:
             parts = []
             for path, n in zip(weight_files, counts):
                 with open(path, "rb") as f:
-                    wl = fm_ops.pack_lines(f.read().split(b"\n")[:n])
+                    wlines = f.read().split(b"\n")
+                if wlines and wlines[-1] == b"":
+                    wlines.pop()
+                if len(wlines) != n:        # as the host batcher: a misaligned weight file is an error, not a truncation
+                    raise ValueError("%s has %d lines, its data file %d" % (path, len(wlines), n))
+                wl = fm_ops.pack_lines(wlines)
                 labels, sizes, _, _ = fm_ops.fm_parser(wl.to(self.device, non_blocking=False), 1)
                 if int(sizes.sum()) != 0 or labels.numel() != n:
                     raise ValueError("%s: expected %d lines holding one number each" % (path, n))
@@ -239,7 +245,7 @@ class SegmentedDataset:
         pend_w = torch.zeros(0, dtype=torch.float32, device=dev) if self.weight_files else None
         wcache, wpos = {}, {}
         seg_no = 0
-        copied = None
+        longest = 0       # longest line seen so far (lines carried over from the previous segment included)
         for _ in range(num_epochs):
             order = list(range(len(self.train_files)))
             if shuffle:
@@ -257,6 +263,7 @@ class SegmentedDataset:
                 n_lines = int((half[:n_bytes] == 10).sum())      # also: the copy is done, the pinned buffer is free
                 off = fm_ops.fm_split_lines(half, n_bytes, n_lines)
                 begins, ends = off[:-1] + base, off[1:] + base
+                longest = max(longest, int((off[1:] - off[:-1]).max())) if n_lines else longest
                 w = None
                 if self.weight_files:
                     # lines of each file in this segment: newlines inside that file's byte range
@@ -284,14 +291,35 @@ class SegmentedDataset:
                 k = 0
                 while all_b.numel() - k >= batch_size:
                     sl = slice(k, k + batch_size)
-                    yield (fm_ops.PackedLines(arena, begins=all_b[sl].contiguous(), ends=all_e[sl].contiguous()),
+                    yield (fm_ops.PackedLines(arena, begins=all_b[sl].contiguous(), ends=all_e[sl].contiguous(),
+                                              max_line_bytes=longest),
                            None if all_w is None else all_w[sl].contiguous())
                     k += batch_size
                 pend_b, pend_e = all_b[k:], all_e[k:]
                 pend_w = None if all_w is None else all_w[k:]
         if pend_b.numel():
-            yield (fm_ops.PackedLines(arena, begins=pend_b.contiguous(), ends=pend_e.contiguous()),
+            yield (fm_ops.PackedLines(arena, begins=pend_b.contiguous(), ends=pend_e.contiguous(),
+                                      max_line_bytes=longest),
                    None if pend_w is None else pend_w.contiguous())
+
+
+def _bind_by_nvml(bus):
+    """NVML's CPU affinity of the GPU with PCI address `bus` (nvidia-smi topo's "CPU Affinity" column)"""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + bit for w, m in enumerate(mask) for bit in range(64) if (int(m) >> bit) & 1}
+    except Exception as e:      # no NVML, or it does not know either
+        return "gpu %s: numa node not reported (sysfs -1; NVML: %s)" % (bus, e)
+    allowed = os.sched_getaffinity(0) & cpus
+    if not allowed or allowed == os.sched_getaffinity(0):
+        return "gpu %s: NVML affinity covers %d cpus, nothing to narrow" % (bus, len(cpus))
+    os.sched_setaffinity(0, allowed)
+    return "gpu %s: bound to %d cpus (NVML cpu affinity)" % (bus, len(allowed))
 
 
 def bind_host_to_gpu(index=None):
@@ -308,8 +336,8 @@ def bind_host_to_gpu(index=None):
         bus = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
         with open("/sys/bus/pci/devices/%s/numa_node" % bus) as f:
             node = int(f.read())
-        if node < 0:
-            return "gpu %s: numa node not reported" % bus
+        if node < 0:      # sysfs does not say (common in containers): ask the driver for the GPU's ideal CPUs
+            return _bind_by_nvml(bus)
         with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
             cpus = set()
             for part in f.read().strip().split(","):

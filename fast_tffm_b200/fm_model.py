@@ -242,6 +242,8 @@ class Model(object):
         self.num_epochs = int(read(T, 'epoch_num'))
         self.learning_rate = float(read(T, 'learning_rate'))
         self.adagrad_init_accumulator = float(read(T, 'adagrad.initial_accumulator'))
+        if not self.adagrad_init_accumulator > 0:
+            raise ValueError("initial_accumulator_value must be positive: %s" % self.adagrad_init_accumulator)
         self.loss_type = read(T, 'loss_type').strip().lower()
         if self.loss_type not in ('logistic', 'mse'):
             raise ValueError("loss_type must be logistic or mse")
@@ -284,6 +286,8 @@ class Model(object):
         init: uniform(-init_value_range, init_value_range) (:278-281) or `init_table`
         ([vocabulary_size, K+1], for parity runs)."""
         lib = load()
+        if not self.adagrad_init_accumulator > 0:      # tf.train.AdagradOptimizer raises the same way
+            raise ValueError("initial_accumulator_value must be positive: %s" % self.adagrad_init_accumulator)
         if device is None:
             device = torch.device("cuda", torch.cuda.current_device())
         self.device = torch.device(device)
@@ -330,7 +334,7 @@ class Model(object):
             self._parse_stream = torch.cuda.Stream(device=self.device)
         self._ahead_slot = 3 - self._ahead_slot
         slot = self._ahead_slot
-        b = self._buffers(packed.n_lines, packed.text.numel(), slot=slot)
+        b = self._buffers(packed.n_lines, packed.nnz_bound(), slot=slot)
         main = torch.cuda.current_stream(self.device)
         side = self._parse_stream
         side.wait_stream(main) if b.get("free") is None else side.wait_event(b["free"])
@@ -364,17 +368,18 @@ class Model(object):
             self.gtab = torch.zeros(self.vocabulary_size, self.gld, dtype=torch.float32, device=self.device)
         return self.gtab
 
-    def _buffers(self, n_lines, text_bytes, slot=0):
+    def _buffers(self, n_lines, nnz_bound, slot=0):
         """per-batch device buffers, allocated once and grown on demand (two sets: the second one
-        lets parse_ahead() fill the next batch while the current one trains)"""
-        b = self._buffers_one(self._slots.get(slot), n_lines, text_bytes)
+        lets parse_ahead() fill the next batch while the current one trains).
+        nnz_bound: PackedLines.nnz_bound() of the batch -- sized from the batch's own lines, not from the
+        buffer they live in (a batch selected from a resident file shares the file's whole text)"""
+        b = self._buffers_one(self._slots.get(slot), n_lines, nnz_bound)
         self._slots[slot] = b
         self._bufs = b          # the set used last (tests and callers read results from it)
         return b
 
-    def _buffers_one(self, b, n_lines, text_bytes):
-        # every feature costs at least two bytes (" x"), so nnz <= text_bytes / 2
-        cap = int(text_bytes // 2 + 1)
+    def _buffers_one(self, b, n_lines, nnz_bound):
+        cap = int(nnz_bound)
         if self._max_nnz_per_line:
             cap = min(cap, int(n_lines * self._max_nnz_per_line))
         if b is not None and b["lines"] >= n_lines and b["cap"] >= cap:
@@ -470,7 +475,7 @@ class Model(object):
             raise ValueError("path must be one of %s" % (self.PATHS,))
         if parsed is not None and path != "claim":
             raise ValueError("parse_ahead() feeds the claim path only")
-        b = parsed["b"] if parsed is not None else self._buffers(packed.n_lines, packed.text.numel())
+        b = parsed["b"] if parsed is not None else self._buffers(packed.n_lines, packed.nnz_bound())
         lib, st = load(), stream()
         n_lines, k = packed.n_lines, self.factor_num
         tstride = self.table.stride(0)
@@ -561,7 +566,7 @@ class Model(object):
         """scores of a device-resident batch in b["pred"].  Default: parse, then the scorer reads
         the rows straight from the table by feature id (no unique, no gathered copy);
         path="composed" runs the reference's chain parse -> unique -> lookup -> fm_scorer."""
-        b = self._buffers(packed.n_lines, packed.text.numel())
+        b = self._buffers(packed.n_lines, packed.nnz_bound())
         if path == "composed":
             self._forward(packed, b)
             return b

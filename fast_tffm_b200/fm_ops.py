@@ -50,12 +50,23 @@ class PackedLines:
     begins / ends index tensors -- e.g. a shuffled selection of the lines of a file, see select().
     """
 
-    def __init__(self, text: Tensor, offsets: Tensor = None, begins: Tensor = None, ends: Tensor = None):
+    def __init__(self, text: Tensor, offsets: Tensor = None, begins: Tensor = None, ends: Tensor = None,
+                 max_line_bytes: int = None):
         self.text, self.offsets = text, offsets
         if offsets is not None:
             begins, ends = offsets[:-1], offsets[1:]
         self.begins, self.ends = begins, ends
         self.text_bytes = text.numel() // 16 * 16     # readable extent handed to the kernels
+        # upper bound on ends[i] - begins[i] when known: a selection over a resident file shares the file's whole
+        # text, so per-batch buffers are sized from the lines, not from the backing buffer (see nnz_bound)
+        self.max_line_bytes = max_line_bytes
+
+    def nnz_bound(self):
+        """upper bound on the number of features in this batch: every feature costs at least two bytes (" x")"""
+        bound = int(self.text.numel() // 2 + 1)
+        if self.max_line_bytes is not None:
+            bound = min(bound, self.n_lines * (int(self.max_line_bytes) // 2) + 1)
+        return bound
 
     @property
     def n_lines(self):
@@ -68,14 +79,18 @@ class PackedLines:
 
     def select(self, index: Tensor):
         """the lines `index` (any order, e.g. a slice of a random permutation); the text is not copied"""
-        return PackedLines(self.text, begins=self.begins[index].contiguous(), ends=self.ends[index].contiguous())
+        if self.max_line_bytes is None and self.n_lines:     # once per parent (one device reduction + read-back)
+            self.max_line_bytes = int((self.ends - self.begins).max())
+        return PackedLines(self.text, begins=self.begins[index].contiguous(), ends=self.ends[index].contiguous(),
+                           max_line_bytes=self.max_line_bytes)
 
     def to(self, device, non_blocking=True):
         text = self.text.to(device, non_blocking=non_blocking)
         if self.offsets is not None:
-            return PackedLines(text, self.offsets.to(device, non_blocking=non_blocking))
+            return PackedLines(text, self.offsets.to(device, non_blocking=non_blocking),
+                               max_line_bytes=self.max_line_bytes)
         return PackedLines(text, begins=self.begins.to(device, non_blocking=non_blocking),
-                           ends=self.ends.to(device, non_blocking=non_blocking))
+                           ends=self.ends.to(device, non_blocking=non_blocking), max_line_bytes=self.max_line_bytes)
 
 
 def pack_lines(lines, pin_memory=False) -> PackedLines:

@@ -55,8 +55,8 @@ class CudaShardKernels:
         self.max_nnz_per_line = max_nnz_per_line
         self._b = None
 
-    def _buffers(self, n_lines, text_bytes, n_ranks, dev):
-        cap = int(text_bytes // 2 + 1)
+    def _buffers(self, n_lines, nnz_bound, n_ranks, dev):
+        cap = int(nnz_bound)
         if self.max_nnz_per_line:
             cap = min(cap, int(n_lines * self.max_nnz_per_line))
         b = self._b
@@ -84,7 +84,7 @@ class CudaShardKernels:
         """parse -> unique -> group distinct ids by owner -> per-occurrence slots; enqueues only.
         Returns capacity-sized tensors and `info` = [nnz, n_unique, parse status, counts[G]] (device)."""
         lib, dev, n_lines, st = self.lib, packed.text.device, packed.n_lines, stream()
-        b = self._buffers(n_lines, packed.text.numel(), n_ranks, dev)
+        b = self._buffers(n_lines, packed.nnz_bound(), n_ranks, dev)
         status, nnz_dev, nuniq_dev = ptr(b["status"]), _at(b["status"], 1), _at(b["status"], 4)
         check(lib.fm_parse_count(ptr(packed.text), packed.text_bytes, ptr(packed.begins), ptr(packed.ends), -1, n_lines,
                                  vocab, int(hashed), ptr(b["sizes"]), ptr(b["poses"]), status, ptr(b["ws_parse"]),
@@ -428,8 +428,8 @@ class PeerShardedModel:
         torch.cuda.synchronize(self.device)
         dist.barrier(group=self.group)
 
-    def _buffers(self, n_lines, text_bytes, slot=0):
-        cap = int(text_bytes // 2 + 1)
+    def _buffers(self, n_lines, nnz_bound, slot=0):
+        cap = int(nnz_bound)
         if self.max_nnz_per_line:
             cap = min(cap, int(n_lines * self.max_nnz_per_line))
         b = self._slots.get(slot)
@@ -470,7 +470,7 @@ class PeerShardedModel:
         packed = lines if isinstance(lines, PackedLines) else pack_lines(list(lines))
         if packed.text.device != self.device:
             packed = packed.to(self.device, non_blocking=True)
-        b = self._buffers(packed.n_lines, packed.text.numel(), slot)
+        b = self._buffers(packed.n_lines, packed.nnz_bound(), slot)
         n_lines, hashed = packed.n_lines, int(cfg.hash_feature_id)
         check(lib.fm_parse_count(ptr(packed.text), packed.text_bytes, ptr(packed.begins), ptr(packed.ends), -1, n_lines,
                                  cfg.vocabulary_size, hashed, ptr(b["sizes"]), ptr(b["poses"]), ptr(b["status"]),

@@ -14,10 +14,11 @@ import bench_data
 from fast_tffm_b200 import fm_ops
 from fast_tffm_b200.fm_model import Model
 from oracle import dense_ref, oracle as O
+from parity_util import RTOL, assert_model_state as _assert_model_state, close as _close, pred_scale as _pred_scale
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
-RTOL = 1e-5
+PATHS = list(Model.PATHS)
 
 
 def dev(a, dtype=None):
@@ -324,14 +325,6 @@ def _random_case(rng, b, rows, k, ld_pad, max_nnz):
     return fids, params, vals, poses
 
 
-def _close(got, exp, scale):
-    """|got - exp| <= RTOL * (|exp| + scale): scale = magnitude of the terms summed"""
-    got, exp = np.asarray(got, np.float64), np.asarray(exp, np.float64)
-    err = np.abs(got - exp)
-    tol = RTOL * (np.abs(exp) + scale)
-    assert (err <= tol).all(), "max err %g, tol there %g" % (err.max(), tol[np.argmax(err - tol)])
-
-
 def test_scorer_reference_case(golden_scorer):
     """port of test/fm_scorer_op_test.py: pred, reg and d cost / d params (autograd through fm_scorer)"""
     g = golden_scorer
@@ -468,7 +461,7 @@ def test_lookup_and_adagrad_vs_oracle():
 
 
 # ------------------------------------------------------------ whole step ----
-@pytest.mark.parametrize("path", ["claim", "fused", "composed"])
+@pytest.mark.parametrize("path", PATHS)
 @pytest.mark.parametrize("loss_type,hashed", [("mse", False), ("logistic", False), ("logistic", True)])
 def test_train_steps_match_reference_model(criteo_lines, loss_type, hashed, path):
     """cfg1 shape in small: sample.cfg's pipeline on the Criteo excerpt, explicit initial table,
@@ -487,12 +480,12 @@ def test_train_steps_match_reference_model(criteo_lines, loss_type, hashed, path
         e = ref.train_step(lines[sl], w)
         got = m.train_step(lines[sl], w, path=path)
         np.testing.assert_allclose(got, e["loss"], rtol=RTOL)
-        np.testing.assert_allclose(m._bufs["pred"][:bs].cpu().numpy(), e["pred"], rtol=1e-4, atol=1e-6)
+        _close(m._bufs["pred"][:bs].cpu().numpy(), e["pred"], _pred_scale(e))
         np.testing.assert_allclose(float(m._bufs["scalars"][2]), e["reg"], rtol=RTOL)
-    np.testing.assert_allclose(m.table[:, :k + 1].cpu().numpy(), ref.flat_table(), rtol=1e-4, atol=1e-7)
-    np.testing.assert_allclose(m.accum[:, :k + 1].cpu().numpy(), ref.flat_acc(), rtol=1e-4, atol=1e-9)
+    _assert_model_state(m, ref, k, 0.05, 4)
     pred = m.predict(lines[1000:1300], path="composed" if path == "composed" else "claim")
-    np.testing.assert_allclose(pred.cpu().numpy(), ref.predict(lines[1000:1300]), rtol=1e-4, atol=1e-6)
+    f = ref.forward(lines[1000:1300])
+    _close(pred.cpu().numpy(), f["pred"], _pred_scale(f))
     if path == "claim":   # table-shaped accumulators are left all zero by the update
         assert not m.gtab.any()
 
@@ -522,12 +515,55 @@ def test_train_steps_any_factor_num(k):
             e = ref.train_step(lines[sl], w if step else None)
             got = m.train_step(lines[sl], w if step else None, path=path)
             np.testing.assert_allclose(got, e["loss"], rtol=RTOL, err_msg="%s %s" % (path, layout))
-            np.testing.assert_allclose(m._bufs["pred"][:bs].cpu().numpy(), e["pred"], rtol=1e-4, atol=1e-6)
-        np.testing.assert_allclose(m.table[:, :k + 1].cpu().numpy(), ref.flat_table(), rtol=1e-4, atol=1e-7,
-                                   err_msg="%s %s" % (path, layout))
-        np.testing.assert_allclose(m.accum[:, :k + 1].cpu().numpy(), ref.flat_acc(), rtol=1e-4, atol=1e-9)
+            _close(m._bufs["pred"][:bs].cpu().numpy(), e["pred"], _pred_scale(e))
+        _assert_model_state(m, ref, k, 0.05, 2)
         pred = m.predict(lines[:bs], path="composed" if path == "composed" else "claim")
-        np.testing.assert_allclose(pred.cpu().numpy(), ref.predict(lines[:bs]), rtol=1e-4, atol=1e-6)
+        f = ref.forward(lines[:bs])
+        _close(pred.cpu().numpy(), f["pred"], _pred_scale(f))
+
+
+# BASELINE.json shapes cut down only in batch (and, where the host cannot hold the oracle's copy of the table, in
+# vocabulary): hashed 2^24 x K=16 with 39 features per line (cfg2), K=64 (cfg3: lane groups of 17), mse + weight file
+# with 1..512 features per line at K=32 (cfg4: the per-example loop runs up to 16 rounds of 32 rows)
+_SHAPES = {
+    "cfg2": dict(vocab=1 << 24, k=16, bs=4096, hashed=True, loss_type="logistic", lam=1e-5),
+    "cfg3": dict(vocab=1 << 22, k=64, bs=2048, hashed=True, loss_type="logistic", lam=1e-5),
+    "cfg4": dict(vocab=1 << 22, k=32, bs=192, hashed=False, loss_type="mse", lam=1e-4),
+}
+
+
+@pytest.mark.parametrize("path", [p for p in PATHS if p != "composed"])
+@pytest.mark.parametrize("shape", sorted(_SHAPES))
+def test_whole_step_at_baseline_shapes(shape, path):
+    c = _SHAPES[shape]
+    vocab, k, bs = c["vocab"], c["k"], c["bs"]
+    rng = np.random.default_rng(7)
+    flat = (rng.random((vocab, k + 1), dtype=np.float32) - 0.5) * 0.02
+    kw = dict(factor_lambda=c["lam"], bias_lambda=c["lam"], loss_type=c["loss_type"])
+    ref = O.RefModel(vocab, 1, k, flat, batch_size=bs, hash_feature_id=c["hashed"], lr=0.01, init_acc=0.1, **kw)
+    m = Model(vocabulary_size=vocab, vocabulary_block_num=1, factor_num=k, batch_size=bs, hash_feature_id=c["hashed"],
+              learning_rate=0.01, adagrad_init_accumulator=0.1, **kw).build(DEV, init_table=flat)
+    touched = []
+    steps = 2
+    for step in range(steps):
+        if shape == "cfg4":
+            lines, w = bench_data.ragged_batch(bs, 30 + step, max_nnz=512, vocab=vocab)
+        else:
+            text, off, _ = bench_data.criteo_batch(bs, 30 + step)
+            lines, w = [bytes(text[off[i]:off[i + 1] - 1]) for i in range(bs)], None
+        e = ref.train_step(lines, w)
+        got = m.train_step(lines, w, path=path)
+        np.testing.assert_allclose(got, e["loss"], rtol=RTOL)
+        _close(m._bufs["pred"][:bs].cpu().numpy(), e["pred"], _pred_scale(e))
+        np.testing.assert_allclose(float(m._bufs["scalars"][2]), e["reg"], rtol=RTOL)
+        touched.append(e["ori"])
+    # the rows the steps touched, and a sample of the ones they must have left alone
+    rows = np.unique(np.concatenate(touched + [rng.integers(0, vocab, 20000)]))
+    idx = torch.from_numpy(rows).to(DEV)
+    _close(m.table[idx, :k + 1].cpu().numpy(), ref.blocks[0, rows], 0.01 * steps)
+    _close(m.accum[idx, :k + 1].cpu().numpy(), ref.acc[0, rows], 0.0)
+    f = ref.forward(lines)
+    _close(m.predict(lines).cpu().numpy(), f["pred"], _pred_scale(f))
 
 
 def test_parse_ahead_pipeline_matches_inline_steps(criteo_lines):

@@ -16,6 +16,7 @@ import pytest
 import torch
 
 from fast_tffm_b200 import _lib
+from oracle import oracle as O
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -23,16 +24,20 @@ RTOL = 1e-5          # the tolerance of tests/test_gpu_parity.py
 MAX_BATCH = 1048576  # FM_SCORE_NOALLOC_MAX_BATCH in include/fm_b200.h
 
 
-def _case(seed, batch, k, rows, max_nnz):
+def _case(seed, batch, k, rows, max_nnz, ld=None):
+    """ld: row stride in floats (default K+1: rows are not 16-byte aligned, the scalar kernels run;
+    a multiple of 4 >= K+1 with zero pad columns takes the float4 kernels, like the model's tables)"""
     rng = np.random.default_rng(seed)
     sizes = rng.integers(0, max_nnz + 1, batch)
     poses = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
     n = int(poses[-1])
     t = lambda a, dt: torch.as_tensor(a, dtype=dt).to(DEV)
+    params = np.zeros((rows, ld or k + 1), np.float32)
+    params[:, :k + 1] = rng.uniform(-0.3, 0.3, (rows, k + 1))
     return dict(
         batch=batch, k=k,
         fids=t(rng.integers(0, rows, n), torch.int32), vals=t(rng.normal(size=n), torch.float32),
-        poses=t(poses, torch.int32), params=t(rng.uniform(-0.3, 0.3, (rows, k + 1)), torch.float32),
+        poses=t(poses, torch.int32), params=t(params, torch.float32),
         pred_ws=torch.empty(batch, device=DEV), reg_ws=torch.empty((), device=DEV),
         pred_na=torch.empty(batch, device=DEV), reg_na=torch.empty((), device=DEV))
 
@@ -58,6 +63,24 @@ def _assert_same(c):
     assert np.isfinite(c["reg_na"].item())
 
 
+def _assert_matches_oracle(c, lf, lb):
+    """the arithmetic itself, not only the scratch plumbing: the CPU oracle's scorer on the same inputs, with the
+    absolute floor of tests/test_gpu_parity.py (the second-order term cancels, so the error scales with the terms)"""
+    fids, params = c["fids"].cpu().numpy(), c["params"].cpu().numpy()
+    vals, poses, k = c["vals"].cpu().numpy(), c["poses"].cpu().numpy(), c["k"]
+    e_pred, e_reg = O.score(fids, params, vals, poses, lf, lb, k=k)
+    r = np.abs(params[fids])
+    terms = np.abs(vals) * r[:, 0]
+    fac = np.abs(vals)[:, None] * r[:, 1:k + 1]
+    scale = np.zeros(c["batch"])
+    for i in range(c["batch"]):
+        sl = slice(poses[i], poses[i + 1])
+        scale[i] = terms[sl].sum() + 0.5 * (fac[sl].sum(0) ** 2).sum()
+    got = c["pred_na"].cpu().numpy().astype(np.float64)
+    assert (np.abs(got - e_pred) <= RTOL * (np.abs(e_pred) + scale)).all()
+    np.testing.assert_allclose(c["reg_na"].item(), e_reg, rtol=RTOL)
+
+
 def test_noalloc_scorer_matches_fm_score_on_two_calls_in_a_row():
     lib = _lib.load()
     torch.cuda.set_device(0)
@@ -78,6 +101,23 @@ def test_noalloc_scorer_matches_fm_score_on_two_calls_in_a_row():
     big["pred_na"].zero_()
     _score_noalloc(lib, big, 0.02, 0.3)
     _assert_same(big)
+    _assert_matches_oracle(big, 0.02, 0.3)
+    _score_noalloc(lib, small, 0.02, 0.3)
+    _assert_matches_oracle(small, 0.02, 0.3)
+
+
+def test_noalloc_scorer_on_16_byte_aligned_rows():
+    """tables as the model lays them out (row stride a multiple of 4 floats, zero pad columns): both entry points
+    take the float4 kernels there; again two calls in a row, against fm_score and against the oracle"""
+    lib = _lib.load()
+    torch.cuda.set_device(0)
+    a = _case(5, 9000, 16, 4000, 45, ld=32)
+    b = _case(6, 501, 64, 700, 20, ld=68)
+    for c in (a, b):
+        _score_with_workspace(lib, c, 0.02, 0.3)
+        _score_noalloc(lib, c, 0.02, 0.3)
+        _assert_same(c)
+        _assert_matches_oracle(c, 0.02, 0.3)
 
 
 def test_noalloc_scorer_refuses_batches_beyond_its_scratch():
