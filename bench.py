@@ -31,6 +31,7 @@ CFG = dict(vocab=1 << 24, factor_num=16, batch=65536, nnz_per_line=39, hash_feat
 CFG3 = dict(CFG, vocab=1 << 27, factor_num=64, batch=32768)   # BASELINE config 3 (meant for 8 GPUs)
 METRIC, UNIT = "fm_train_examples_per_sec", "examples/s"
 STAGES = {  # stage marks per step, in order
+    "sorted": ["parse_count", "parse_fill", "sort", "score", "update"],
     "claim": ["parse_count", "parse_fill", "score_scatter", "adagrad"],
     "fused": ["parse_count", "parse_fill", "unique", "score_scatter", "adagrad"],
     "composed": ["parse_count", "parse_fill", "unique", "lookup", "score", "loss", "grad", "adagrad"],
@@ -38,7 +39,8 @@ STAGES = {  # stage marks per step, in order
 # my kernels per step.  parse: count, count-slow, poses scan, fill, fill-slow (5); unique: insert, rank
 # scan, finish (3); claim: + score_scatter, reduce2, adagrad_claim; fused: + unique + score_scatter,
 # reduce2, adagrad; composed: + unique + lookup | score, reduce | loss, reduce | zero rows, grad | adagrad
-KERNELS_PER_STEP = {"claim": 8, "fused": 11, "composed": 16}
+# sorted: + expand, histogram, one radix pass per 8 key bits, chunk scan | score, reduce2 | update, finish
+KERNELS_PER_STEP = {"sorted": 15, "claim": 8, "fused": 11, "composed": 16}
 
 
 def measured_peak_gbs():
@@ -118,6 +120,8 @@ def kernel_traffic(workload, dist, path, layout):
 
 
 STAGE_KERNELS = {   # the kernels behind each stage mark (ncu names)
+    "sorted": {"update": ["sorted_update_kernel", "sorted_finish_kernel"], "score": ["fused_score_scatter"],
+               "parse": ["parse_count_kernel", "parse_fill_kernel"]},
     "claim": {"adagrad": ["fused_adagrad_claim"], "score_scatter": ["fused_score_scatter"],
               "parse": ["parse_count_kernel", "parse_fill_kernel"]},
 }
@@ -234,6 +238,8 @@ def workload_config(args, n_gpus, batch):
 
 def run_ours(args):
     import torch
+    if args.layout is None:
+        args.layout = "pair" if args.path == "sorted" else "interleaved"
     from fast_tffm_b200.fm_model import Model
     from fast_tffm_b200.fm_ops import PackedLines
 
@@ -255,7 +261,7 @@ def run_ours(args):
               loss_type=cfg["loss_type"], learning_rate=cfg["learning_rate"],
               adagrad_init_accumulator=cfg["init_acc"], factor_lambda=cfg["factor_lambda"],
               bias_lambda=cfg["bias_lambda"]).build(dev, seed=0, max_nnz_per_line=cfg["nnz_per_line"], ld=args.ld,
-                                                     layout=args.layout)
+                                                     layout=args.layout, path=args.path)
     if args.l2_fetch:
         # experiment knob: cudaLimitMaxL2FetchGranularity (0x05)
         import ctypes
@@ -281,7 +287,7 @@ def run_ours(args):
     # ---- device-resident throughput (value) + per-stage CUDA events ----------------
     fused = args.path
     stages = STAGES[fused]
-    ahead_on = fused == "claim" and not args.no_parse_ahead
+    ahead_on = fused in ("claim", "sorted") and not args.no_parse_ahead
 
     def run_steps(n_steps, base, ev=None):
         """the timed loop; the warm-up runs the very same code so that every buffer set, stream and
@@ -339,6 +345,8 @@ def run_ours(args):
     assert int(st[0]) == -1, "parse error in the benchmark data"
     nnz = int(st[1])
     n_unique = int(st[4]) if fused != "claim" else int(torch.unique(bufs["ids"][:nnz]).numel())
+    if fused == "sorted":
+        assert n_unique == int(torch.unique(bufs["ids"][:nnz]).numel()) and int(st[5]) == nnz, "sort counts are off"
     loss = float(st[6:8].view(torch.float32)[0])
     value = args.steps * b / (total_ms * 1e-3)
 
@@ -456,10 +464,12 @@ def main():
     ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3"],
                     help="cfg2 (default): 2^24 vocab, K=16, 65536 examples per GPU; cfg3: 2^27 vocab, K=64, "
                          "32768 examples per GPU (BASELINE config 3, 8 GPUs)")
-    ap.add_argument("--path", default="claim", choices=["claim", "fused", "composed"],
-                    help="claim: no unique, table-shaped accumulators (default); fused: unique + compact "
-                         "accumulators; composed: the reference's op-by-op chain")
-    ap.add_argument("--layout", default="interleaved", choices=["split", "interleaved"])
+    ap.add_argument("--path", default="sorted", choices=["sorted", "claim", "fused", "composed"],
+                    help="sorted: run-ahead radix sort by row + segment-reduce update (default); claim: no unique, "
+                         "table-shaped accumulators; fused: unique + compact accumulators; composed: the reference's "
+                         "op-by-op chain")
+    ap.add_argument("--layout", default=None, choices=["pair", "split", "interleaved"],
+                    help="default: pair ([w | h] per id) for the sorted path, interleaved ([w | h | g]) for the others")
     ap.add_argument("--no-parse-ahead", action="store_true",
                     help="parse each batch inline instead of on a side stream under the previous batch's kernels")
     ap.add_argument("--shard-mode", default="peer", choices=["peer", "exchange"],

@@ -84,7 +84,7 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
                            int K, const float* __restrict__ table, int64_t ld, float lam_f, float lam_b,
                            int loss_kind, float inv_batch, float* __restrict__ pred, float* __restrict__ gacc, int64_t gacc_ld,
                            float* __restrict__ partials, const unsigned long long* __restrict__ guard,
-                           const PeerPtrs peers, int gs) {
+                           const PeerPtrs peers, int gs, float* __restrict__ emit, int64_t emit_ld) {
   __shared__ float s_loss[kWarps], s_reg[kWarps];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int RPW = 32 / gs;                       // rows per warp step
@@ -181,6 +181,23 @@ fused_score_scatter_kernel(const int64_t* __restrict__ ids, const int32_t* __res
       loss_acc += w * l;
     }
 
+    if (emit != nullptr) {
+      // sorted update (fm_sorted.cu): no scatter here.  The example leaves one record [pg, s_1 .. s_K] behind --
+      // everything the gradient of its rows needs besides the rows themselves and the occurrence's value
+      if (lane_on && r == 0) {
+        float* rec = emit + i * emit_ld;
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+          const int chunk = c + t * gs;
+          if (chunk < vc_table) {
+            float4 o = S[t];
+            if (chunk == 0) o.x = pg;            // column 0 (the bias column, whose total is unused) carries pg
+            *reinterpret_cast<float4*>(rec + 4 * chunk) = o;
+          }
+        }
+      }
+      continue;
+    }
     // ---- pass B: scatter {C, B_k, D, cnt} to the accumulator rows ---------------------
     for (int base = start; base < end; base += 32) {
       const int j = base + lane;
@@ -704,7 +721,51 @@ FM_EXPORT int fm_fused_score_scatter(const int64_t* feature_ids, const int32_t* 
   fused_score_scatter_kernel<T, false><<<blocks, kWarps * 32, 0, stream>>>(                                       \
       feature_ids, local_ids, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, table, table_ld, \
       factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, gacc, gacc_ld, partials,                      \
-      reinterpret_cast<const unsigned long long*>(guard), PeerPtrs(), gs)
+      reinterpret_cast<const unsigned long long*>(guard), PeerPtrs(), gs, nullptr, 0)
+  if (t == 1) { CALL(1); } else if (t == 2) { CALL(2); } else { CALL(3); }
+#undef CALL
+  FM_LAUNCH_CHECK();
+  reduce2_kernel<<<1, 256, 0, stream>>>(partials, blocks, inv_batch, loss, reg_score);
+  FM_LAUNCH_CHECK();
+  return FM_OK;
+}
+
+FM_EXPORT int64_t fm_sorted_record_ld(int64_t factor_num) { return (factor_num + 4) / 4 * 4; }
+
+// the scorer of the sorted path: fm_fused_score_scatter without the scatter; per example it leaves the record
+// [pg, s_1 .. s_K] (pg = d loss / d pred over the batch, s_k = sum_j x_j v_jk) for fm_sorted_update
+FM_EXPORT int fm_sorted_score(const int64_t* feature_ids, const float* feature_vals, const int32_t* feature_poses,
+                              const float* labels, const float* weights, int64_t batch, int64_t factor_num,
+                              const float* table, int64_t table_ld, float factor_lambda, float bias_lambda,
+                              int loss_kind, int64_t loss_batch, float* pred_score, float* loss, float* reg_score,
+                              float* records, int64_t record_ld, const uint64_t* guard, void* workspace,
+                              size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  FM_REQUIRE(batch >= 0 && factor_num >= 0, "fm_sorted_score: bad shape");
+  FM_REQUIRE(table_ld >= factor_num + 1 && table_ld % 4 == 0, "fm_sorted_score: table_ld must be a multiple of 4 and >= K+1");
+  FM_REQUIRE(record_ld >= fm_sorted_record_ld(factor_num) && record_ld % 4 == 0,
+             "fm_sorted_score: record_ld must be a multiple of 4 and >= fm_sorted_record_ld(K)");
+  FM_REQUIRE(loss_kind == FM_LOSS_LOGISTIC || loss_kind == FM_LOSS_MSE, "fm_sorted_score: unknown loss kind");
+  FM_REQUIRE(loss && reg_score && workspace, "fm_sorted_score: null pointer");
+  FM_REQUIRE(batch == 0 || (feature_ids && feature_vals && feature_poses && table && pred_score && labels && records),
+             "fm_sorted_score: null pointer");
+  FM_REQUIRE((((uintptr_t)table | (uintptr_t)records) & 15) == 0, "fm_sorted_score: table and records must be 16-byte aligned");
+  if (workspace_bytes < fm_fused_workspace(batch))
+    return fm_fail(FM_E_WORKSPACE, "fm_sorted_score: workspace %zu < %zu", workspace_bytes, fm_fused_workspace(batch));
+  const int64_t chunks = (factor_num + 4) / 4;      // a K+1 wide row: no K+3 wide accumulator row on this path
+  const int gs = chunks <= 32 ? (int)chunks : 32;
+  const int t = (int)((chunks + gs - 1) / gs);
+  if (t > 3) return fm_fail(FM_E_LIMIT, "fm_sorted_score: factor_num %lld beyond the sorted path (use the claim path)",
+                            (long long)factor_num);
+  const int blocks = fused_blocks(batch);
+  float* partials = reinterpret_cast<float*>(workspace);
+  const int64_t denom = loss_batch > 0 ? loss_batch : batch;
+  const float inv_batch = denom > 0 ? 1.0f / (float)denom : 0.f;
+#define CALL(T)                                                                                                   \
+  fused_score_scatter_kernel<T, false><<<blocks, kWarps * 32, 0, stream>>>(                                       \
+      feature_ids, nullptr, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, table, table_ld, \
+      factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, nullptr, 0, partials,                         \
+      reinterpret_cast<const unsigned long long*>(guard), PeerPtrs(), gs, records, record_ld)
   if (t == 1) { CALL(1); } else if (t == 2) { CALL(2); } else { CALL(3); }
 #undef CALL
   FM_LAUNCH_CHECK();
@@ -846,7 +907,7 @@ FM_EXPORT int fm_peer_score_scatter(const int64_t* feature_ids, const float* fea
   fused_score_scatter_kernel<T, true><<<blocks, kWarps * 32, 0, stream>>>(                                          \
       feature_ids, nullptr, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, peers.table[0],   \
       table_ld, factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, scatter_flag, gtab_ld, partials,      \
-      reinterpret_cast<const unsigned long long*>(guard), peers, gs)
+      reinterpret_cast<const unsigned long long*>(guard), peers, gs, nullptr, 0)
   if (t == 1) { CALL(1); } else if (t == 2) { CALL(2); } else { CALL(3); }
 #undef CALL
   FM_LAUNCH_CHECK();

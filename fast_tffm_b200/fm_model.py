@@ -183,6 +183,7 @@ class Model(object):
     queue_size = 10000
     shuffle_threads = 1
     tolerance = None
+    optimizer = 'adagrad'     # extension: 'sgd' (sorted path only); the reference always builds AdagradOptimizer
 
     def __init__(self, config_file=None, **overrides):
         self.train_files, self.weight_files, self.predict_files = [], [], []
@@ -247,6 +248,10 @@ class Model(object):
         self.loss_type = read(T, 'loss_type').strip().lower()
         if self.loss_type not in ('logistic', 'mse'):
             raise ValueError("loss_type must be logistic or mse")
+        if cfg.has_option(T, 'optimizer'):      # not a key of the reference (tffm/fm_model.py:341-344 is Adagrad only)
+            self.optimizer = read(T, 'optimizer').strip().lower()
+            if self.optimizer not in ('adagrad', 'sgd'):
+                raise ValueError("optimizer must be adagrad or sgd")
         v = read(T, 'save_steps', False)
         if v is not None:
             self.save_steps = int(v)
@@ -275,14 +280,17 @@ class Model(object):
 
     # ---- the vocabulary table ------------------------------------------------------
     def build(self, device=None, init_table=None, seed=None, max_nnz_per_line=None, ld=None,
-              layout="interleaved"):
+              layout="pair", path=None):
         """Allocates table + Adagrad accumulator (+ table-shaped gradient accumulator) in HBM.
         The table is [vocabulary_size, ld] (row = feature id, see _stride_for); the reference's
         vocabulary_block_num blocks (fm_model.py:269-284) are a relabelling applied when
         checkpoints are written (blocks_state / load_blocks_state).
-        layout "split": three arrays; "interleaved": one array whose row holds the weight,
-        Adagrad and gradient-accumulator rows of one id side by side (the update kernel then
-        touches one contiguous piece of memory per id).
+        layout "pair" (default): one array whose row holds [w | h], the weight and Adagrad rows of one
+        id side by side in whole 128-byte lines -- what the sorted path touches per id; "interleaved":
+        [w | h | g] with the claim path's gradient-accumulator row beside them; "split": separate arrays.
+        Every path runs on every layout (a path that needs an accumulator table the layout lacks
+        allocates it on first use).
+        path: the default of train_step / parse_ahead: "sorted" unless the row is too wide for it.
         init: uniform(-init_value_range, init_value_range) (:278-281) or `init_table`
         ([vocabulary_size, K+1], for parity runs)."""
         lib = load()
@@ -296,7 +304,25 @@ class Model(object):
         assert self.ld >= k + 1 and self.ld % 4 == 0
         self.gld = _stride_for(int(lib.fm_fused_gacc_ld(k)))
         self.layout = layout
-        if layout == "interleaved":
+        if layout not in ("pair", "interleaved", "split"):
+            raise ValueError("layout must be pair, interleaved or split")
+        if self.optimizer not in ("adagrad", "sgd"):
+            raise ValueError("optimizer must be adagrad or sgd")
+        sortable = (k + 4) // 4 <= 96 and v <= 1 << 32
+        if path is None:
+            path = "sorted" if sortable else "claim"
+        if path not in self.PATHS or (path == "sorted" and not sortable) or (self.optimizer == "sgd" and path != "sorted"):
+            raise ValueError("path %r not available for factor_num %d / optimizer %s" % (path, k, self.optimizer))
+        self.default_path = path
+        if layout == "pair":
+            # [w | h] of one id packed at 16-byte granularity in whole 128-byte lines (K=16: 2 x 20 floats in
+            # 256 B; the weight row, which the scorer reads alone, never straddles a line)
+            part = (k + 1 + 3) // 4 * 4 if ld is None else int(ld)
+            block = (2 * part + 31) // 32 * 32 if ld is None else 2 * part
+            self._store = torch.zeros(v, block, dtype=torch.float32, device=self.device)
+            self.table = self._store[:, :part]
+            self.gtab = None
+        elif layout == "interleaved":
             # [w | h | g] of one id packed at 16-byte granularity in a block that is a whole number of
             # 128-byte lines (K=16: 3 x 20 floats in 256 B = 2 lines; the weight row never straddles)
             part = max((k + 1 + 3) // 4 * 4, int(lib.fm_fused_gacc_ld(k)))
@@ -316,7 +342,7 @@ class Model(object):
             if seed is not None:
                 gen.manual_seed(seed)
             self.table[:, :k + 1].uniform_(-self.init_value_range, self.init_value_range, generator=gen)
-        if layout == "interleaved":
+        if layout in ("pair", "interleaved"):
             self.accum = self._store[:, part:2 * part]
             self.accum.fill_(self.adagrad_init_accumulator)
         else:
@@ -326,7 +352,7 @@ class Model(object):
         self._max_nnz_per_line = max_nnz_per_line
         return self
 
-    def parse_ahead(self, packed: PackedLines, after=None):
+    def parse_ahead(self, packed: PackedLines, after=None, sort=None):
         """Enqueues the parse of a device-resident batch on a side stream, into the buffer set the
         current step is not using, and returns a handle for train_step_async(parsed=...).  The
         parser is instruction-bound while the table kernels are memory-bound, so the two overlap."""
@@ -342,11 +368,14 @@ class Model(object):
             side.wait_event(after)
         if self._bg_blocks is None:
             self._bg_blocks = self.BACKGROUND_PARSE_BLOCKS
+        sort = self.default_path == "sorted" if sort is None else sort
         with torch.cuda.stream(side):
             self._parse_unique(packed, b, unique=False, max_blocks=self._bg_blocks)
+            if sort:        # the sort needs only the ids: it runs ahead with the parse
+                self._sort(b, packed.n_lines, max_blocks=self._bg_blocks)
             done = torch.cuda.Event(enable_timing=True)
             done.record(side)
-        return dict(b=b, done=done, packed=packed)
+        return dict(b=b, done=done, packed=packed, sorted=sort)
 
     def _adapt_parse_grid(self, need, done):
         """The run-ahead parse is a thin background kernel (BACKGROUND_PARSE_BLOCKS blocks) so that it takes
@@ -407,6 +436,7 @@ class Model(object):
             ws_parse=_lib.workspace(lib.fm_parse_workspace(lines), dev),
             ws_score=_lib.workspace(lib.fm_score_workspace(lines), dev),
             ws_loss=_lib.workspace(lib.fm_loss_workspace(lines), dev),
+            skeys=None,      # the sorted path's buffers, allocated on first use (_sort)
         )
         b["scalars"] = b["status"][6:8].view(torch.float32)  # [loss, -, reg, -]
         return b
@@ -455,14 +485,36 @@ class Model(object):
                            ptr(b["ws_score"]), b["ws_score"].numel(), st), "fm_score")
         mark("score")
 
-    PATHS = ("claim", "fused", "composed")
+    def _sort(self, b, n_lines, mark=_no_mark, max_blocks=0):
+        """occurrences of the parsed batch in `b` sorted by table row (fm_sort_by_row); counts land in
+        status[3:6] = n_chunks, n_unique, nnz"""
+        lib, st, dev = load(), stream(), self.device
+        if b.get("skeys") is None:
+            cap = b["cap"]
+            b["skeys"] = torch.empty(cap, dtype=torch.int32, device=dev)
+            b["spairs"] = torch.empty(cap, 2, dtype=torch.int32, device=dev)
+            b["chunks"] = torch.empty(cap + 2, dtype=torch.int32, device=dev)
+            b["ws_sort"] = _lib.workspace(lib.fm_sort_workspace(cap), dev)
+            b["rec_ld"] = int(lib.fm_sorted_record_ld(self.factor_num))
+            b["rec"] = torch.empty(b["lines"], b["rec_ld"], dtype=torch.float32, device=dev)
+            b["ws_sorted"] = _lib.workspace(lib.fm_sorted_workspace(cap, self.factor_num), dev)
+        check(lib.fm_sort_by_row(ptr(b["ids"]), ptr(b["vals"]), ptr(b["poses"]), n_lines, b["cap"], _off(b["status"], 1),
+                                 self.vocabulary_size, 1, ptr(b["skeys"]), ptr(b["spairs"]), ptr(b["chunks"]),
+                                 _off(b["status"], 3), ptr(b["status"]), ptr(b["ws_sort"]), b["ws_sort"].numel(),
+                                 max_blocks, st), "fm_sort_by_row")
+        mark("sort")
 
-    def train_step_async(self, packed: PackedLines, weights=None, mark=_no_mark, path="claim", parsed=None,
+    PATHS = ("sorted", "claim", "fused", "composed")
+
+    def train_step_async(self, packed: PackedLines, weights=None, mark=_no_mark, path=None, parsed=None,
                          prefetch=None):
         """One training step on a device-resident batch; enqueues only.  Returns the
         buffers dict: status[0] parse status word, status[1] nnz, status[4] n_unique,
         scalars[0] loss, scalars[2] reg.
-        path "claim"    (default) parse -> fm_fused_score_scatter into table-shaped accumulator
+        path "sorted"   (default) parse -> fm_sort_by_row -> fm_sorted_score -> fm_sorted_update: FmGrad's
+                        scatter-add and the optimizer step as one segment reduce over the occurrences
+                        sorted by row; no atomics, no accumulator rows, reproducible sums;
+             "claim"    parse -> fm_fused_score_scatter into table-shaped accumulator
                         rows -> fm_fused_adagrad_claim: no tf.unique, each table row read once;
              "fused"    parse -> unique -> fm_fused_score_scatter (compact accumulators) ->
                         fm_fused_adagrad;
@@ -471,14 +523,51 @@ class Model(object):
         prefetch: the NEXT batch (device-resident): its parse is started on the side stream right
                   after this batch's scorer kernel, i.e. under the DRAM-bound update kernel, and the
                   handle comes back as result["ahead"]."""
+        path = self.default_path if path is None else path
         if path not in self.PATHS:
             raise ValueError("path must be one of %s" % (self.PATHS,))
-        if parsed is not None and path != "claim":
-            raise ValueError("parse_ahead() feeds the claim path only")
+        if parsed is not None and path not in ("claim", "sorted"):
+            raise ValueError("parse_ahead() feeds the sorted and claim paths only")
+        if self.optimizer != "adagrad" and path != "sorted":
+            raise ValueError("optimizer %r runs on the sorted path only" % self.optimizer)
         b = parsed["b"] if parsed is not None else self._buffers(packed.n_lines, packed.nnz_bound())
         lib, st = load(), stream()
         n_lines, k = packed.n_lines, self.factor_num
         tstride = self.table.stride(0)
+        if path == "sorted":
+            if parsed is not None:
+                main = torch.cuda.current_stream(self.device)
+                need = torch.cuda.Event(enable_timing=True)
+                need.record(main)
+                main.wait_event(parsed["done"])
+                self._adapt_parse_grid(need, parsed["done"])
+                mark("parse_count")
+                mark("parse_fill")
+                if parsed.get("sorted"):
+                    mark("sort")
+                else:
+                    self._sort(b, n_lines, mark)
+            else:
+                self._parse_unique(packed, b, mark, unique=False)
+                self._sort(b, n_lines, mark)
+            check(lib.fm_sorted_score(
+                ptr(b["ids"]), ptr(b["vals"]), ptr(b["poses"]), ptr(b["labels"]), ptr(weights), n_lines, k,
+                ptr(self.table), tstride, self.factor_lambda, self.bias_lambda, _lib.LOSS_KIND[self.loss_type], 0,
+                ptr(b["pred"]), _off(b["status"], 6), _off(b["status"], 7), ptr(b["rec"]), b["rec_ld"],
+                ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st), "fm_sorted_score")
+            mark("score")
+            check(lib.fm_sorted_update(
+                ptr(self.table), ptr(self.accum), tstride, ptr(b["skeys"]), ptr(b["spairs"]), ptr(b["chunks"]),
+                _off(b["status"], 3), b["cap"], ptr(b["rec"]), b["rec_ld"], k, _lib.OPTIMIZER[self.optimizer],
+                self.learning_rate, self.factor_lambda, self.bias_lambda, 1.0 / self.batch_size, 0,
+                ptr(b["status"]), ptr(b["ws_sorted"]), b["ws_sorted"].numel(), st), "fm_sorted_update")
+            mark("update")
+            if parsed is not None:   # the buffer set may be refilled once this step is through with it
+                b["status_snapshot"] = b["status"].clone()
+                b["free"] = torch.cuda.Event()
+                b["free"].record(torch.cuda.current_stream(self.device))
+            self.global_step += 1
+            return b
         if path == "claim":
             gtab = self._gtab()
             if parsed is not None:
@@ -553,7 +642,7 @@ class Model(object):
         self.global_step += 1
         return b
 
-    def train_step(self, lines, weights=None, path="claim"):
+    def train_step(self, lines, weights=None, path=None):
         """lines: list of str / PackedLines (host or device); weights: per-example floats or None.
         Returns the batch loss (python float); raises FmParseError like the op would."""
         packed, weights = self._to_device(lines, weights)

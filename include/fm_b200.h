@@ -247,6 +247,54 @@ int fm_fused_adagrad_claim(float* table, float* accum, int64_t table_ld, const i
                            float bias_lambda, float reg_grad, const uint64_t* guard,
                            int discard_on_guard, void* stream);
 
+/* ---- sorted training path: G + A1 as a sort / segment reduce fused with the optimizer step ----
+ * Not ops of the reference: together with fm_sorted_score they compute what FmGrad's scatter
+ * (cc/fm_grad_op.h:80-106; CAS-loop float adds, :3-16) followed by the embedding_lookup gradient and
+ * SparseApplyAdagrad (tffm/fm_model.py:341-348) compute, without atomics and without a dense gradient.
+ *
+ * fm_sort_by_row: stable LSD radix sort of the batch's occurrences by table row.  Needs only the parser's
+ *   outputs, so it can run ahead on a side stream next to the parse.  n = *nnz_dev (<= capacity).
+ *   sorted_keys[n]   the row keys ascending (key = feature id; with n_ranks > 1: (id % n_ranks) <<
+ *                    row_bits | id / n_ranks, row_bits = bit length of ceil(vocab_size / n_ranks) - 1, i.e.
+ *                    grouped by owning rank of an `id % n_ranks` partition, rows ascending inside)
+ *   sorted_pairs[2n] (example index, bits of feature_vals) of each occurrence, in that order; occurrences
+ *                    of one row keep their batch order (the sort is stable => sums are reproducible)
+ *   chunk_starts[]   start of every run of equal keys, runs cut at multiples of FM_SORT_CHUNK so that no work
+ *                    item is longer; chunk_starts[n_chunks] = n; capacity + 2 entries
+ *   counts[3]        device int64: n_chunks, number of distinct keys (= tf.unique's U), n
+ *   guard tripped (*guard != UINT64_MAX): counts = 0, nothing sorted.
+ *   vocab_size <= 2^32, capacity < 2^30.  max_blocks: grid cap (0 = default), as in fm_parse_fill.
+ * fm_sorted_score: fm_fused_score_scatter's scorer + loss; instead of scattering it leaves one record per
+ *   example, records[i] = [pg_i, s_i1 .. s_iK] (pg = d loss / d pred_i / loss_batch; s_ik = sum_j x_j v_jk,
+ *   cc/fm_grad_op.h:42-47), record_ld >= fm_sorted_record_ld(K) floats.
+ * fm_sorted_update: one lane group per run: G_0 = C + cnt rg lb b, G_k = v_k (cnt rg lf - D) + B_k from the
+ *   run's occurrences (C = sum pg x, D = sum pg x^2, B_k = sum pg x s_k), then the optimizer step on
+ *   table / accum rows (key & (2^row_bits - 1); row_bits = 0: the key is the row).  FM_OPT_ADAGRAD = TF1
+ *   SparseApplyAdagrad; FM_OPT_SGD (w -= lr G; accum unused, may be NULL) is an extension -- the reference only
+ *   ever builds AdagradOptimizer (tffm/fm_model.py:341-344).  guard as in fm_sparse_adagrad. */
+#define FM_SORT_CHUNK 128
+enum { FM_OPT_ADAGRAD = 0, FM_OPT_SGD = 1 };
+size_t fm_sort_workspace(int64_t capacity);
+int fm_sort_by_row(const int64_t* feature_ids, const float* feature_vals, const int32_t* feature_poses,
+                   int64_t batch, int64_t capacity, const int64_t* nnz_dev, int64_t vocab_size,
+                   int64_t n_ranks, uint32_t* sorted_keys, uint32_t* sorted_pairs, uint32_t* chunk_starts,
+                   int64_t* counts, const uint64_t* guard, void* workspace, size_t workspace_bytes,
+                   int max_blocks, void* stream);
+int64_t fm_sorted_record_ld(int64_t factor_num);
+int fm_sorted_score(const int64_t* feature_ids, const float* feature_vals, const int32_t* feature_poses,
+                    const float* labels, const float* weights, int64_t batch, int64_t factor_num,
+                    const float* table, int64_t table_ld, float factor_lambda, float bias_lambda,
+                    int loss_kind, int64_t loss_batch, float* pred_score, float* loss, float* reg_score,
+                    float* records, int64_t record_ld, const uint64_t* guard, void* workspace,
+                    size_t workspace_bytes, void* stream);
+size_t fm_sorted_workspace(int64_t capacity, int64_t factor_num);
+int fm_sorted_update(float* table, float* accum, int64_t table_ld, const uint32_t* sorted_keys,
+                     const uint32_t* sorted_pairs, const uint32_t* chunk_starts, const int64_t* counts,
+                     int64_t capacity, const float* records, int64_t record_ld, int64_t factor_num,
+                     int optimizer, float learning_rate, float factor_lambda, float bias_lambda,
+                     float reg_grad, int64_t row_bits, const uint64_t* guard, void* workspace,
+                     size_t workspace_bytes, void* stream);
+
 /* ---- D1: the parameter-server sharding of tffm/fm_model.py:269-291 + run_tffm.py:181-206,
  * as explicit routing around an all-to-all: rank id % n_ranks owns table row id / n_ranks ----
  * fm_shard_bucket: stable counting sort of `ids` (the batch's distinct ids) by owner:

@@ -1,5 +1,5 @@
 """Short driver for ncu: a few cfg2 train steps (device-resident batches), nothing else.
-usage: python profiles/run_step.py [steps] [dist] [path]"""
+usage: python profiles/run_step.py [steps] [dist] [path] [factor_num] [vocab_log2] [batch]"""
 import os
 import sys
 
@@ -14,14 +14,18 @@ from fast_tffm_b200.fm_ops import PackedLines  # noqa: E402
 
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 dist = sys.argv[2] if len(sys.argv) > 2 else "uniform"
-path = sys.argv[3] if len(sys.argv) > 3 else "claim"
+path = sys.argv[3] if len(sys.argv) > 3 else "sorted"
+k = int(sys.argv[4]) if len(sys.argv) > 4 else CFG["factor_num"]
+vocab = 1 << int(sys.argv[5]) if len(sys.argv) > 5 else CFG["vocab"]
+batch = int(sys.argv[6]) if len(sys.argv) > 6 else CFG["batch"]
 dev = torch.device("cuda", 0)
-m = Model(vocabulary_size=CFG["vocab"], factor_num=CFG["factor_num"], batch_size=CFG["batch"], hash_feature_id=True,
+m = Model(vocabulary_size=vocab, factor_num=k, batch_size=batch, hash_feature_id=True,
           loss_type=CFG["loss_type"], learning_rate=CFG["learning_rate"], adagrad_init_accumulator=CFG["init_acc"],
-          factor_lambda=CFG["factor_lambda"], bias_lambda=CFG["bias_lambda"]).build(dev, seed=0, max_nnz_per_line=39)
+          factor_lambda=CFG["factor_lambda"], bias_lambda=CFG["bias_lambda"]).build(
+              dev, seed=0, max_nnz_per_line=39, layout="pair" if path == "sorted" else "interleaved", path=path)
 batches = []
 for i in range(2):
-    text, off, _ = bench_data.criteo_batch(CFG["batch"], 1 + i, dist)
+    text, off, _ = bench_data.criteo_batch(batch, 1 + i, dist)
     batches.append(PackedLines(torch.from_numpy(bench_data.pad16(text)).to(dev), torch.from_numpy(off).to(dev)))
 for s in range(steps):
     b = m.train_step_async(batches[s % 2], path=path)

@@ -310,6 +310,93 @@ def test_unique_all_equal_and_large_ids():
     assert ori.cpu().tolist() == [(1 << 62) + 12345] and not local.any()
 
 
+# ------------------------------------------------------ sort by row ----
+def _sort_by_row(ids, vals, poses, vocab, n_ranks=1, capacity=None):
+    from fast_tffm_b200 import _lib
+    lib = _lib.load()
+    n, b = len(ids), len(poses) - 1
+    cap = n if capacity is None else capacity
+    d_ids = dev(np.concatenate([ids, np.zeros(cap - n, np.int64)]), torch.int64)
+    d_vals = dev(np.concatenate([vals, np.zeros(cap - n, np.float32)]), torch.float32)
+    d_poses, d_n = dev(poses, torch.int32), dev([n], torch.int64)
+    keys = torch.empty(max(cap, 1), dtype=torch.int32, device=DEV)
+    pairs = torch.empty(max(cap, 1), 2, dtype=torch.int32, device=DEV)
+    chunks = torch.empty(cap + 2, dtype=torch.int32, device=DEV)
+    counts = torch.zeros(3, dtype=torch.int64, device=DEV)
+    ws = _lib.workspace(lib.fm_sort_workspace(cap), torch.device(DEV))
+    _lib.check(lib.fm_sort_by_row(_lib.ptr(d_ids), _lib.ptr(d_vals), _lib.ptr(d_poses), b, cap, _lib.ptr(d_n), vocab,
+                                  n_ranks, _lib.ptr(keys), _lib.ptr(pairs), _lib.ptr(chunks), _lib.ptr(counts), None,
+                                  _lib.ptr(ws), ws.numel(), 0, _lib.stream()), "fm_sort_by_row")
+    c = counts.cpu().numpy()
+    return (keys[:n].cpu().numpy().view(np.uint32), pairs[:n].cpu().numpy().view(np.uint32),
+            chunks[:int(c[0]) + 1].cpu().numpy().view(np.uint32), c)
+
+
+@pytest.mark.parametrize("n,vocab,n_ranks,slack", [(0, 10, 1, 5), (1, 10, 1, 0), (5000, 37, 1, 0), (40000, 1 << 16, 1, 999),
+                                                  (300000, 1 << 24, 1, 0), (300000, (1 << 27) + 5, 1, 17),
+                                                  (200000, 1 << 24, 8, 0), (70000, 1000003, 3, 0),
+                                                  (2555904, 1 << 24, 1, 0)])
+def test_sort_by_row_is_a_stable_sort(n, vocab, n_ranks, slack):
+    """keys ascending, occurrences of one row in batch order (bit-exact index work); chunk starts = run heads
+    and multiples of FM_SORT_CHUNK; counts = [n_chunks, n_unique, n]"""
+    rng = np.random.default_rng(n + n_ranks)
+    ids = rng.integers(0, vocab, n)
+    if n > 1000:
+        ids[rng.integers(0, n, n // 3)] = ids[0]              # one very hot row: its run is cut into many chunks
+    vals = rng.normal(size=n).astype(np.float32)
+    b = max(1, n // 39)
+    cuts = np.sort(rng.integers(0, n + 1, b - 1))
+    poses = np.concatenate([[0], cuts, [n]]).astype(np.int32)  # ragged examples, some empty
+    keys, pairs, chunks, counts = _sort_by_row(ids, vals, poses, vocab, n_ranks, n + slack)
+    if n_ranks > 1:
+        rows = -(-vocab // n_ranks)
+        row_bits = max(1, int(rows - 1).bit_length())
+        exp_key = ((ids % n_ranks) << row_bits) | (ids // n_ranks)
+    else:
+        exp_key = ids
+    order = np.argsort(exp_key, kind="stable")
+    example = np.repeat(np.arange(b), np.diff(poses))
+    np.testing.assert_array_equal(keys, exp_key[order].astype(np.uint32))
+    np.testing.assert_array_equal(pairs[:, 0], example[order].astype(np.uint32))
+    np.testing.assert_array_equal(pairs[:, 1], vals[order].view(np.uint32))
+    sk = exp_key[order]
+    head = np.ones(n, bool)
+    head[1:] = sk[1:] != sk[:-1]
+    start = head | (np.arange(n) % 128 == 0)
+    np.testing.assert_array_equal(chunks, np.concatenate([np.flatnonzero(start), [n]]).astype(np.uint32))
+    assert counts.tolist() == [int(start.sum()), int(head.sum()), n]
+
+
+def test_sgd_step_extension(criteo_lines):
+    """optimizer = sgd (not in the reference, which only builds Adagrad): w -= lr * G with the reference's own
+    gradient (the oracle's FmGrad), two steps, hot and cold rows"""
+    lines, weights = criteo_lines
+    rng = np.random.default_rng(77)
+    vocab, k, bs, lr = 200003, 16, 300, 0.05
+    flat = rng.uniform(-0.01, 0.01, (vocab, k + 1)).astype(np.float32)
+    kw = dict(factor_lambda=2e-3, bias_lambda=1e-3, loss_type="logistic")
+    ref = O.RefModel(vocab, 1, k, flat, batch_size=bs, lr=lr, **kw)
+    m = Model(vocabulary_size=vocab, factor_num=k, batch_size=bs, learning_rate=lr, optimizer="sgd", **kw).build(
+        DEV, init_table=flat)
+    for step in range(2):
+        sl = slice(step * bs, (step + 1) * bs)
+        w = np.float32(weights[sl])
+        f = ref.forward(lines[sl])
+        lv, pg = O.loss(f["pred"], f["labels"], w, "logistic")
+        g = O.grad(f["local"], f["lp"], f["vals"], f["poses"], ref.lf, ref.lb, pg, 1.0 / bs)
+        ref.blocks[0, f["ori"]] -= np.float32(lr) * g
+        got = m.train_step(lines[sl], w)
+        np.testing.assert_allclose(got, lv, rtol=RTOL)
+    got_t = m.table[:, :k + 1].cpu().numpy()
+    _close(got_t, ref.blocks[0], 0.0)
+    # and the movement itself (tiny next to the weights): within 1e-3 of the largest move
+    move, exp_move = got_t.astype(np.float64) - flat, ref.blocks[0].astype(np.float64) - flat
+    assert np.abs(exp_move).max() > 0 and np.abs(move - exp_move).max() <= 1e-3 * np.abs(exp_move).max()
+    assert bool((m.accum[:, :k + 1] == m.adagrad_init_accumulator).all())      # SGD leaves the accumulator alone
+    with pytest.raises(ValueError, match="sorted path only"):
+        m.train_step(lines[:bs], path="claim")
+
+
 # ------------------------------------------------------ scorer and grad ----
 def _random_case(rng, b, rows, k, ld_pad, max_nnz):
     sizes = rng.integers(0, max_nnz + 1, b).astype(np.int32)
@@ -506,7 +593,10 @@ def test_train_steps_any_factor_num(k):
     flat = rng.uniform(-0.05, 0.05, (vocab, k + 1)).astype(np.float32)
     kw = dict(factor_lambda=3e-3, bias_lambda=2e-3, loss_type="logistic")
     w = rng.uniform(0.5, 2.0, bs).astype(np.float32)
-    for path, layout in (("claim", "interleaved"), ("claim", "split"), ("fused", "split"), ("composed", "split")):
+    combos = [("claim", "interleaved"), ("claim", "split"), ("fused", "split"), ("composed", "split"), ("claim", "pair")]
+    if (k + 4) // 4 <= 96:      # the sorted path's lane groups cover rows of up to 96 chunks
+        combos += [("sorted", "pair"), ("sorted", "interleaved"), ("sorted", "split")]
+    for path, layout in combos:
         ref = O.RefModel(vocab, 7, k, flat, batch_size=bs, lr=0.05, init_acc=0.1, **kw)
         m = Model(vocabulary_size=vocab, vocabulary_block_num=7, factor_num=k, batch_size=bs, learning_rate=0.05,
                   adagrad_init_accumulator=0.1, **kw).build(DEV, init_table=flat, layout=layout)
