@@ -61,12 +61,12 @@ _SIGNATURES = {
     "fm_shard_local_rows": (C.c_int, [_vp, _i64, _i64, _vp, _vp]),
     "fm_shard_combine": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _vp, _i64, _vp]),
     "fm_sort_workspace": (_sz, [_i64]),
-    "fm_sort_by_row": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i32, _vp]),
+    "fm_sort_by_row": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _i32, _vp]),
     "fm_sorted_record_ld": (_i64, [_i64]),
     "fm_sorted_score": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _i64, _f32, _f32, _i32, _i64, _vp, _vp, _vp,
                                   _vp, _i64, _vp, _vp, _sz, _vp]),
     "fm_sorted_workspace": (_sz, [_i64, _i64]),
-    "fm_sorted_update": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _vp, _i64, _i64, _i32, _f32, _f32, _f32,
+    "fm_sorted_update": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _i64, _i32, _f32, _f32, _f32,
                                    _f32, _i64, _vp, _vp, _sz, _vp]),
     "fm_fused_adagrad": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _f32, _f32, _f32, _f32, _vp, _vp]),
 }

@@ -3,21 +3,22 @@
 // The reference scatters FmGrad's per-occurrence gradients with a CAS-loop float add
 // (cc/fm_grad_op.h:3-16, :80-106) and lets TF's unique + SparseApplyAdagrad find the rows
 // (tffm/fm_model.py:72, :341-348).  Here the occurrences are SORTED by feature id instead --
-// a stable LSD radix sort that needs nothing but the parser's ids, so it runs on the side
-// stream next to the parse, under the table kernels of the previous batch -- and the update
-// (fm_sorted.cu) walks each row's run of occurrences once: no atomics, no accumulator rows,
-// the same summation order every time.
+// a stable LSD radix sort that needs nothing but the parser's ids, so it can run on a side
+// stream next to the parse -- and the update (fm_sorted.cu) walks each row's run of occurrences
+// once: no atomics, no accumulator rows, the same summation order every time.
 //
-//   expand   example index of every occurrence (the inverse of feature_poses)
-//   hist     digit histograms of all passes in one read of the ids
-//   pass x P 8-bit stable counting pass: per-warp match ranking, tile offsets by decoupled
-//            look-back (tiles are taken from a ticket, so a tile only waits on started tiles),
-//            tile reordered in shared memory so that the scatter writes runs, not single words
-//            (last pass: writes the sorted ids and, gathered through the carried occurrence
-//            index, the (example, value) pair of each occurrence)
-//   chunks   one scan over the sorted ids: the start of every run of equal ids, runs cut at
-//            multiples of kSortChunk so that no work item of the update is longer than that
-//            (hot rows under skewed ids), the number of chunks and of distinct ids
+//   expand        example index of every occurrence (the inverse of feature_poses)
+//   per 8-bit digit, least significant first (3 passes for a 2^24 vocabulary):
+//     count       digit histogram of every tile of 3072 keys -> counts[digit][tile]
+//     scan        one exclusive scan over that matrix, digit-major: the global position of
+//                 (digit, tile)'s first key (fm_scan.cuh, single pass)
+//     scatter     per tile: stable ranks by warp-wide match, the tile reordered in shared
+//                 memory so that the writes are runs, not single words; the last pass writes
+//                 the sorted keys and, gathered through the carried occurrence index, the
+//                 (example, value) pair of each occurrence
+// No block waits on another block.  Runs of equal keys are not listed: the update gives every
+// sorted position a lane group and the positions that open a run (or sit on a multiple of
+// FM_SORT_CHUNK inside one) do the work.
 //
 // Everything is sized by the parser's device-resident nnz; 2.5 M occurrences are 30 MB of keys,
 // payload and pairs: the whole sort lives in the 126 MB L2.
@@ -34,17 +35,16 @@ constexpr int kTile = kThreads * kItems;            // 3072 keys per tile
 constexpr int kWarpSpan = 32 * kItems;              // keys of one warp, in order: round r, lane l
 constexpr int kBins = 256;
 constexpr int kMaxPasses = 4;
+constexpr int kScanItems = 8;
 constexpr unsigned long long kNoError = 0xffffffffffffffffull;
 
 struct SortWs {
-  unsigned* hist;        // [kMaxPasses][kBins]
-  unsigned* tickets;     // [kMaxPasses + 1] tile tickets of the passes
-  unsigned* status;      // [kMaxPasses][tiles][kBins] look-back words: flag << 30 | count
-  unsigned* example;     // [cap] example index of every occurrence
-  unsigned* keys[2];     // ping-pong
+  char* scan[kMaxPasses];  // scan scratch of each pass (zeroed per call)
+  unsigned* counts;        // [kBins][tiles]: digit counts per tile, then (scanned) global offsets
+  unsigned* example;       // [cap] example index of every occurrence
+  unsigned* keys[2];       // ping-pong
   unsigned* pay[2];
-  void* scan;            // scratch of the chunk scan
-  size_t zero_bytes;     // hist + tickets + status, zeroed per call
+  size_t zero_bytes;
 };
 
 static inline int64_t sort_tiles(int64_t cap) { return cap <= 0 ? 1 : (cap + kTile - 1) / kTile; }
@@ -57,26 +57,24 @@ static inline size_t carve(size_t* off, size_t bytes) {
 
 static size_t layout(int64_t cap, char* base, SortWs* ws) {
   size_t off = 0;
-  const size_t h = carve(&off, sizeof(unsigned) * kMaxPasses * kBins);
-  const size_t t = carve(&off, sizeof(unsigned) * 64);
-  const size_t s = carve(&off, sizeof(unsigned) * kMaxPasses * (size_t)sort_tiles(cap) * kBins);
+  const int64_t cells = sort_tiles(cap) * kBins;
+  size_t sc[kMaxPasses];
+  for (int p = 0; p < kMaxPasses; ++p) sc[p] = carve(&off, scan_scratch_bytes(cells, kScanItems));
   const size_t zero_end = off;
+  const size_t c = carve(&off, sizeof(unsigned) * (size_t)cells);
   const size_t e = carve(&off, sizeof(unsigned) * (size_t)cap);
   const size_t k0 = carve(&off, sizeof(unsigned) * (size_t)cap);
   const size_t k1 = carve(&off, sizeof(unsigned) * (size_t)cap);
   const size_t p0 = carve(&off, sizeof(unsigned) * (size_t)cap);
   const size_t p1 = carve(&off, sizeof(unsigned) * (size_t)cap);
-  const size_t sc = carve(&off, scan_scratch_bytes(cap, 8));
   if (ws) {
-    ws->hist = reinterpret_cast<unsigned*>(base + h);
-    ws->tickets = reinterpret_cast<unsigned*>(base + t);
-    ws->status = reinterpret_cast<unsigned*>(base + s);
+    for (int p = 0; p < kMaxPasses; ++p) ws->scan[p] = base + sc[p];
+    ws->counts = reinterpret_cast<unsigned*>(base + c);
     ws->example = reinterpret_cast<unsigned*>(base + e);
     ws->keys[0] = reinterpret_cast<unsigned*>(base + k0);
     ws->keys[1] = reinterpret_cast<unsigned*>(base + k1);
     ws->pay[0] = reinterpret_cast<unsigned*>(base + p0);
     ws->pay[1] = reinterpret_cast<unsigned*>(base + p1);
-    ws->scan = base + sc;
     ws->zero_bytes = zero_end;
   }
   return off;
@@ -97,85 +95,94 @@ __device__ __forceinline__ unsigned key_of(int64_t id, int n_ranks, int row_bits
   return ((u % (unsigned)n_ranks) << row_bits) | (u / (unsigned)n_ranks);
 }
 
-// example[j] = i for poses[i] <= j < poses[i + 1]
+// example[j] = i for poses[i] <= j < poses[i + 1]: a binary search per occurrence over the B + 1 bounds (the
+// upper levels of the search stay in L1; neighbouring occurrences take the same path)
 __global__ void __launch_bounds__(kThreads)
-expand_kernel(const int32_t* __restrict__ poses, int64_t batch, unsigned* __restrict__ example,
-              int64_t cap, const unsigned long long* __restrict__ guard) {
-  if (guard && *guard != kNoError) return;
-  const int lane = threadIdx.x & 31;
-  const int64_t warps = (int64_t)gridDim.x * kWarpsPerBlock;
-  for (int64_t i = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5); i < batch; i += warps) {
-    const int64_t a = poses[i], b = min((int64_t)poses[i + 1], cap);
-    for (int64_t j = a + lane; j < b; j += 32) example[j] = (unsigned)i;
-  }
-}
-
-// digit histograms of every pass, one read of the ids
-__global__ void __launch_bounds__(kThreads)
-hist_kernel(const int64_t* __restrict__ ids, int64_t cap, const int64_t* __restrict__ n_dev,
-            const unsigned long long* __restrict__ guard, int n_ranks, int row_bits, int passes,
-            unsigned* __restrict__ hist) {
-  __shared__ unsigned s_hist[kMaxPasses * kBins];
+expand_kernel(const int32_t* __restrict__ poses, int64_t batch, unsigned* __restrict__ example, int64_t cap,
+              const int64_t* __restrict__ n_dev, const unsigned long long* __restrict__ guard) {
   const int64_t n = live_count(cap, n_dev, guard);
-  for (int i = threadIdx.x; i < kMaxPasses * kBins; i += kThreads) s_hist[i] = 0;
-  __syncthreads();
   for (int64_t j = (int64_t)blockIdx.x * kThreads + threadIdx.x; j < n; j += (int64_t)gridDim.x * kThreads) {
-    const unsigned key = key_of(ids[j], n_ranks, row_bits);
-    for (int p = 0; p < passes; ++p) atomicAdd(&s_hist[p * kBins + ((key >> (8 * p)) & 255u)], 1u);
+    int64_t lo = 0, hi = batch;                  // invariant: poses[lo] <= j < poses[hi]
+    while (hi - lo > 1) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (__ldg(poses + mid) <= j) lo = mid; else hi = mid;
+    }
+    example[j] = (unsigned)lo;
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < passes * kBins; i += kThreads)
-    if (s_hist[i]) atomicAdd(&hist[i], s_hist[i]);
 }
 
-// One stable 8-bit counting pass.  FIRST: keys come from the ids, the payload is the occurrence index itself.
+// digit counts of every tile: counts[digit * n_tiles_cap + tile].  Tiles past the live keys write zeros, so the
+// matrix needs no clearing.
+template <bool FIRST>
+__global__ void __launch_bounds__(kThreads)
+count_kernel(const int64_t* __restrict__ ids, const unsigned* __restrict__ keys_in, int64_t cap,
+             const int64_t* __restrict__ n_dev, const unsigned long long* __restrict__ guard, int n_ranks, int row_bits,
+             int shift, unsigned* __restrict__ counts, int64_t n_tiles_cap) {
+  __shared__ unsigned s_hist[kWarpsPerBlock][kBins];     // one histogram per warp: fewer same-address collisions
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int64_t n = live_count(cap, n_dev, guard);
+  for (int64_t tile = blockIdx.x; tile < n_tiles_cap; tile += gridDim.x) {
+    for (int i = tid; i < kWarpsPerBlock * kBins; i += kThreads) (&s_hist[0][0])[i] = 0;
+    __syncthreads();
+    const int64_t tile_base = tile * kTile;
+    unsigned key[kItems];
+#pragma unroll
+    for (int r = 0; r < kItems; ++r) {
+      const int64_t j = tile_base + r * kThreads + tid;
+      key[r] = j < n ? (FIRST ? key_of(ids[j], n_ranks, row_bits) : keys_in[j]) : 0u;
+    }
+#pragma unroll
+    for (int r = 0; r < kItems; ++r)
+      if (tile_base + r * kThreads + tid < n) atomicAdd(&s_hist[warp][(key[r] >> shift) & 255u], 1u);
+    __syncthreads();
+    unsigned c = 0;
+#pragma unroll
+    for (int w = 0; w < kWarpsPerBlock; ++w) c += s_hist[w][tid];
+    counts[(int64_t)tid * n_tiles_cap + tile] = c;
+    __syncthreads();
+  }
+}
+
+// the exclusive scan over counts[] in place (digit-major: a cell ends up holding the global position of its first key)
+struct CellIn {
+  const unsigned* cells; int64_t n;
+  __device__ int64_t count() const { return n; }
+  __device__ long long operator()(int64_t i) const { return cells[i]; }
+};
+struct CellOut {
+  unsigned* cells;
+  __device__ void operator()(int64_t i, long long excl, long long) const { cells[i] = (unsigned)excl; }
+  __device__ void total(long long) const {}
+};
+
+// One stable 8-bit scatter pass.  FIRST: keys come from the ids, the payload is the occurrence index itself.
 // LAST: writes the sorted keys and the (example, value bits) pair of each occurrence instead of the payload.
 template <bool FIRST, bool LAST>
 __global__ void __launch_bounds__(kThreads)
-pass_kernel(const int64_t* __restrict__ ids, const unsigned* __restrict__ keys_in, const unsigned* __restrict__ pay_in,
-            unsigned* __restrict__ keys_out, unsigned* __restrict__ pay_out, uint2* __restrict__ pairs_out,
-            const unsigned* __restrict__ example, const float* __restrict__ vals, int64_t cap,
-            const int64_t* __restrict__ n_dev, const unsigned long long* __restrict__ guard, int n_ranks, int row_bits,
-            int shift, const unsigned* __restrict__ hist, unsigned* __restrict__ status, unsigned* __restrict__ ticket) {
+scatter_kernel(const int64_t* __restrict__ ids, const unsigned* __restrict__ keys_in, const unsigned* __restrict__ pay_in,
+               unsigned* __restrict__ keys_out, unsigned* __restrict__ pay_out, uint2* __restrict__ pairs_out,
+               const unsigned* __restrict__ example, const float* __restrict__ vals, int64_t cap,
+               const int64_t* __restrict__ n_dev, const unsigned long long* __restrict__ guard, int n_ranks, int row_bits,
+               int shift, const unsigned* __restrict__ offsets, int64_t n_tiles_cap, int64_t* __restrict__ out_counts) {
   __shared__ unsigned s_cnt[kWarpsPerBlock][kBins];   // per-warp digit counts, then the warp's offset inside its digit
   __shared__ unsigned s_keys[kTile], s_pay[kTile];
   __shared__ unsigned s_tile_off[kBins];              // first slot of each digit in the reordered tile
   __shared__ unsigned s_glob[kBins];                  // global position of slot i of digit d = s_glob[d] + i
-  __shared__ unsigned s_base[kBins];                  // exclusive scan of the pass histogram
   __shared__ unsigned s_scan[kWarpsPerBlock];
-  __shared__ unsigned s_tile;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t n = live_count(cap, n_dev, guard);
-  if (n == 0) return;
   const int64_t n_tiles = (n + kTile - 1) / kTile;
+  if (LAST && blockIdx.x == 0 && tid == 0) out_counts[0] = n;
 
-  {  // s_base: exclusive scan over the 256 digit totals (thread d owns digit d)
-    const unsigned c = hist[tid];
-    unsigned incl = c;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const unsigned v = __shfl_up_sync(kFull, incl, o);
-      if (lane >= o) incl += v;
-    }
-    if (lane == 31) s_scan[warp] = incl;
-    __syncthreads();
-    unsigned off = 0;
-    for (int w = 0; w < warp; ++w) off += s_scan[w];
-    s_base[tid] = off + incl - c;
-    __syncthreads();
-  }
-
-  while (true) {
-    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     for (int i = tid; i < kWarpsPerBlock * kBins; i += kThreads) (&s_cnt[0][0])[i] = 0;
+    const unsigned first_pos = offsets[(int64_t)tid * n_tiles_cap + tile];   // global position of digit tid's first key
     __syncthreads();
-    const int64_t tile = s_tile;
-    if (tile >= n_tiles) return;
     const int64_t tile_base = tile * kTile;
     const int tile_n = (int)min((int64_t)kTile, n - tile_base);
 
-    // ---- load + rank: warp w owns keys [w * kWarpSpan, (w + 1) * kWarpSpan) of the tile, round r lane l ----
-    unsigned key[kItems], pay[kItems], rank[kItems];
+    // ---- load: warp w owns keys [w * kWarpSpan, (w + 1) * kWarpSpan) of the tile, round r lane l ----
+    unsigned key[kItems], pay[kItems], rank[kItems], peers[kItems];
 #pragma unroll
     for (int r = 0; r < kItems; ++r) {
       const int local = warp * kWarpSpan + r * 32 + lane;
@@ -189,25 +196,26 @@ pass_kernel(const int64_t* __restrict__ ids, const unsigned* __restrict__ keys_i
         pay[r] = valid ? pay_in[j] : 0u;
       }
     }
+    // ---- stable ranks: all the matches first (independent), then the warp's counters round by round ----
 #pragma unroll
     for (int r = 0; r < kItems; ++r) {
-      const int local = warp * kWarpSpan + r * 32 + lane;
-      const bool valid = local < tile_n;
+      const bool valid = warp * kWarpSpan + r * 32 + lane < tile_n;
+      peers[r] = __match_any_sync(kFull, valid ? (key[r] >> shift) & 255u : 0xffffffffu);   // lanes with my digit
+    }
+    volatile unsigned* my_cnt = s_cnt[warp];
+#pragma unroll
+    for (int r = 0; r < kItems; ++r) {
+      const bool valid = warp * kWarpSpan + r * 32 + lane < tile_n;
       const unsigned d = (key[r] >> shift) & 255u;
-      const unsigned peers = __match_any_sync(kFull, valid ? d : 0xffffffffu);   // lanes with my digit (in lane order)
-      const int leader = __ffs(peers) - 1;
-      unsigned before = 0;
-      if (valid && lane == leader) {
-        before = s_cnt[warp][d];
-        s_cnt[warp][d] = before + __popc(peers);
-      }
-      before = __shfl_sync(kFull, before, leader);
-      rank[r] = before + __popc(peers & ((1u << lane) - 1u));
+      const unsigned before = valid ? my_cnt[d] : 0u;        // every lane of the group reads the same word ...
       __syncwarp();
+      if (valid && lane == __ffs(peers[r]) - 1) my_cnt[d] = before + __popc(peers[r]);   // ... its first lane bumps it
+      __syncwarp();
+      rank[r] = before + __popc(peers[r] & ((1u << lane) - 1u));
     }
     __syncthreads();
 
-    // ---- digit d (thread d): offsets of the warps inside the digit, the tile's count ----
+    // ---- digit d (thread d): offsets of the warps inside the digit, the tile's count, its first slot ----
     unsigned count = 0;
 #pragma unroll
     for (int w = 0; w < kWarpsPerBlock; ++w) {
@@ -215,19 +223,7 @@ pass_kernel(const int64_t* __restrict__ ids, const unsigned* __restrict__ keys_i
       s_cnt[w][tid] = count;
       count += c;
     }
-    // publish the tile's count for digit d, then sum the predecessors' (decoupled look-back per digit)
-    unsigned* st = status + (size_t)tile * kBins + tid;
-    atomicExch(st, ((tile == 0 ? 2u : 1u) << 30) | count);
-    unsigned excl = 0;
-    for (int64_t t = tile - 1; t >= 0; --t) {
-      const volatile unsigned* sp = status + (size_t)t * kBins + tid;
-      unsigned s;
-      do { s = *sp; } while ((s >> 30) == 0u);
-      excl += s & 0x3fffffffu;
-      if ((s >> 30) == 2u) break;
-    }
-    if (tile != 0) atomicExch(st, (2u << 30) | (excl + count));
-    {  // exclusive scan of the tile's digit counts
+    {
       unsigned incl = count;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -240,7 +236,7 @@ pass_kernel(const int64_t* __restrict__ ids, const unsigned* __restrict__ keys_i
       for (int w = 0; w < warp; ++w) off += s_scan[w];
       const unsigned tile_off = off + incl - count;
       s_tile_off[tid] = tile_off;
-      s_glob[tid] = s_base[tid] + excl - tile_off;     // unsigned wrap is fine: + slot index brings it back
+      s_glob[tid] = first_pos - tile_off;            // unsigned wrap is fine: + slot index brings it back
     }
     __syncthreads();
 
@@ -260,37 +256,12 @@ pass_kernel(const int64_t* __restrict__ ids, const unsigned* __restrict__ keys_i
       const unsigned k = s_keys[i], p = s_pay[i];
       const unsigned pos = s_glob[(k >> shift) & 255u] + (unsigned)i;
       keys_out[pos] = k;
-      if (LAST) pairs_out[pos] = make_uint2(example[p], __float_as_uint(vals[p]));
+      if (LAST) pairs_out[pos] = make_uint2(__ldg(example + p), __float_as_uint(__ldg(vals + p)));
       else pay_out[pos] = p;
     }
     __syncthreads();
   }
 }
-
-// chunk starts: p is a start if it opens a run of equal keys or is a multiple of kSortChunk
-struct ChunkIn {
-  const unsigned* keys; int64_t cap; const int64_t* n_dev; const unsigned long long* guard;
-  __device__ int64_t count() const { return live_count(cap, n_dev, guard); }
-  __device__ long long operator()(int64_t p) const {
-    const bool head = p == 0 || keys[p] != keys[p - 1];
-    const bool start = head || (p % FM_SORT_CHUNK) == 0;
-    return (long long)start | ((long long)head << 32);      // both counts ride one scan
-  }
-};
-struct ChunkOut {
-  unsigned* starts; int64_t* counts; int64_t cap; const int64_t* n_dev; const unsigned long long* guard;
-  __device__ void operator()(int64_t p, long long excl, long long item) const {
-    if (item & 1) starts[excl & 0xffffffffll] = (unsigned)p;
-  }
-  __device__ void total(long long t) const {
-    const int64_t n = live_count(cap, n_dev, guard);
-    const long long chunks = t & 0xffffffffll;
-    starts[chunks] = (unsigned)n;
-    counts[0] = chunks;
-    counts[1] = t >> 32;
-    counts[2] = n;
-  }
-};
 
 static inline int bit_length(uint64_t v) {
   int b = 0;
@@ -310,7 +281,7 @@ FM_EXPORT size_t fm_sort_workspace(int64_t capacity) {
 
 FM_EXPORT int fm_sort_by_row(const int64_t* feature_ids, const float* feature_vals, const int32_t* feature_poses,
                              int64_t batch, int64_t capacity, const int64_t* nnz_dev, int64_t vocab_size,
-                             int64_t n_ranks, uint32_t* sorted_keys, uint32_t* sorted_pairs, uint32_t* chunk_starts,
+                             int64_t n_ranks, uint32_t* sorted_keys, uint32_t* sorted_pairs,
                              int64_t* counts, const uint64_t* guard, void* workspace, size_t workspace_bytes,
                              int max_blocks, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
@@ -318,7 +289,7 @@ FM_EXPORT int fm_sort_by_row(const int64_t* feature_ids, const float* feature_va
   if (vocab_size > (int64_t)1 << 32 || capacity >= (int64_t)1 << 30)
     return fm_fail(FM_E_LIMIT, "fm_sort_by_row: vocabulary_size <= 2^32 and capacity < 2^30 (got %lld, %lld)",
                    (long long)vocab_size, (long long)capacity);
-  FM_REQUIRE(counts && chunk_starts && workspace, "fm_sort_by_row: null pointer");
+  FM_REQUIRE(counts && workspace, "fm_sort_by_row: null pointer");
   FM_REQUIRE(capacity == 0 || (feature_ids && feature_vals && feature_poses && sorted_keys && sorted_pairs),
              "fm_sort_by_row: null pointer");
   FM_REQUIRE(((uintptr_t)sorted_pairs & 7) == 0, "fm_sort_by_row: sorted_pairs must be 8-byte aligned");
@@ -336,43 +307,44 @@ FM_EXPORT int fm_sort_by_row(const int64_t* feature_ids, const float* feature_va
   const int passes = (key_bits + 7) / 8;
 
   FM_CUDA(cudaMemsetAsync(workspace, 0, ws.zero_bytes, stream));
-  FM_CUDA(cudaMemsetAsync(ws.scan, 0, scan_scratch_bytes(capacity, 8), stream));
+  FM_CUDA(cudaMemsetAsync(counts, 0, 2 * sizeof(int64_t), stream));     // stays 0 when there is nothing to sort
+  if (capacity == 0 || batch == 0) return FM_OK;
   const int64_t tiles = sort_tiles(capacity);
-  const int cap_blocks = max_blocks > 0 ? max_blocks : 148 * 4;
+  const int64_t cells = tiles * kBins;
+  const int cap_blocks = max_blocks > 0 ? max_blocks : 148 * 8;
   const unsigned grid = (unsigned)(tiles < cap_blocks ? tiles : cap_blocks);
-  if (capacity > 0 && batch > 0) {
-    int64_t eb = (batch + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    if (eb > cap_blocks) eb = cap_blocks;
-    expand_kernel<<<(unsigned)eb, kThreads, 0, stream>>>(feature_poses, batch, ws.example, capacity, g);
-    FM_LAUNCH_CHECK();
-    hist_kernel<<<grid, kThreads, 0, stream>>>(feature_ids, capacity, nnz_dev, g, (int)n_ranks, row_bits, passes, ws.hist);
-    FM_LAUNCH_CHECK();
-    for (int p = 0; p < passes; ++p) {
-      const bool first = p == 0, last = p == passes - 1;
-      const unsigned* kin = ws.keys[(p + 1) & 1];
-      const unsigned* pin = ws.pay[(p + 1) & 1];
-      unsigned* kout = last ? sorted_keys : ws.keys[p & 1];
-      unsigned* pout = ws.pay[p & 1];
-      unsigned* status = ws.status + (size_t)p * tiles * kBins;
-#define FM_PASS(F, L)                                                                                                  \
-  pass_kernel<F, L><<<grid, kThreads, 0, stream>>>(feature_ids, kin, pin, kout, pout,                                  \
-                                                   reinterpret_cast<uint2*>(sorted_pairs), ws.example, feature_vals,   \
-                                                   capacity, nnz_dev, g, (int)n_ranks, row_bits, 8 * p,                \
-                                                   ws.hist + p * kBins, status, ws.tickets + p)
-      if (first && last) { FM_PASS(true, true); }
-      else if (first) { FM_PASS(true, false); }
-      else if (last) { FM_PASS(false, true); }
-      else { FM_PASS(false, false); }
-#undef FM_PASS
-      FM_LAUNCH_CHECK();
-    }
-  }
-  ChunkIn in{sorted_keys, capacity, nnz_dev, g};
-  ChunkOut out{chunk_starts, counts, capacity, nnz_dev, g};
-  const int64_t scan_n_tiles = scan_tiles(capacity, 8);
-  // the scan walks live_count() items; its last tile (by capacity) reports the total, so size it by capacity
-  scan_kernel<8><<<(unsigned)scan_n_tiles, kScanThreads, 0, stream>>>(in, out, scan_scratch_at(ws.scan, capacity, 8),
-                                                                      scan_n_tiles);
+  int64_t eb = (capacity + kThreads - 1) / kThreads;
+  if (eb > cap_blocks) eb = cap_blocks;
+  expand_kernel<<<(unsigned)eb, kThreads, 0, stream>>>(feature_poses, batch, ws.example, capacity, nnz_dev, g);
   FM_LAUNCH_CHECK();
+  const int64_t scan_n_tiles = scan_tiles(cells, kScanItems);
+  for (int p = 0; p < passes; ++p) {
+    const bool first = p == 0, last = p == passes - 1;
+    const unsigned* kin = ws.keys[(p + 1) & 1];
+    const unsigned* pin = ws.pay[(p + 1) & 1];
+    unsigned* kout = last ? sorted_keys : ws.keys[p & 1];
+    unsigned* pout = ws.pay[p & 1];
+    if (first)
+      count_kernel<true><<<grid, kThreads, 0, stream>>>(feature_ids, kin, capacity, nnz_dev, g, (int)n_ranks, row_bits,
+                                                        8 * p, ws.counts, tiles);
+    else
+      count_kernel<false><<<grid, kThreads, 0, stream>>>(feature_ids, kin, capacity, nnz_dev, g, (int)n_ranks, row_bits,
+                                                         8 * p, ws.counts, tiles);
+    FM_LAUNCH_CHECK();
+    scan_kernel<kScanItems><<<(unsigned)scan_n_tiles, kScanThreads, 0, stream>>>(
+        CellIn{ws.counts, cells}, CellOut{ws.counts}, scan_scratch_at(ws.scan[p], cells, kScanItems), scan_n_tiles);
+    FM_LAUNCH_CHECK();
+#define FM_PASS(F, L)                                                                                                    \
+  scatter_kernel<F, L><<<grid, kThreads, 0, stream>>>(feature_ids, kin, pin, kout, pout,                                \
+                                                      reinterpret_cast<uint2*>(sorted_pairs), ws.example, feature_vals, \
+                                                      capacity, nnz_dev, g, (int)n_ranks, row_bits, 8 * p, ws.counts,   \
+                                                      tiles, counts)
+    if (first && last) { FM_PASS(true, true); }
+    else if (first) { FM_PASS(true, false); }
+    else if (last) { FM_PASS(false, true); }
+    else { FM_PASS(false, false); }
+#undef FM_PASS
+    FM_LAUNCH_CHECK();
+  }
   return FM_OK;
 }

@@ -2,7 +2,7 @@
 //
 // Replaces cc/fm_grad_op.h:80-106 (one atomic float add per occurrence per column into a dense
 // [U, K+1] gradient) + TF's SparseApplyAdagrad (tffm/fm_model.py:341-348).  Input: the batch's
-// occurrences sorted by table row (fm_sort.cu: keys, (example, x) pairs, chunk starts) and one record
+// occurrences sorted by table row (fm_sort.cu: keys and (example, x) pairs) and one record
 // per example [pg, s_1 .. s_K] (fm_sorted_score).  FmGrad's per-occurrence gradient
 //     g_0 = pg x + rg lb b            g_k = rg lf v_k - pg x^2 v_k + pg x s_k
 // summed over a row's occurrences is
@@ -27,8 +27,7 @@ constexpr int kOptAdagrad = 0, kOptSgd = 1;
 struct SortedIn {
   const unsigned* keys;      // sorted row keys
   const uint2* pairs;        // (example, x bits) of each sorted occurrence
-  const unsigned* starts;    // chunk starts, starts[n_chunks] = n
-  const int64_t* counts;     // [n_chunks, n_unique, n]
+  int64_t* counts;           // [n, n_unique]: n from the sort, n_unique counted here
   const float* rec;          // [batch, rec_ld] example records [pg, s_1 .. s_K]
   int64_t rec_ld;
 };
@@ -40,34 +39,25 @@ struct Step {
 
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 
-// sums of occurrences [p0, p1) for lane chunk(s) c + t * gs of the row: G[t] = (C | B_k) columns, D, cnt
+// one occurrence's terms for lane chunk(s) c + t * gs of the row: G[t] = (. | B_k) columns, C, D, cnt
 template <int T>
-__device__ __forceinline__ void reduce_run(const SortedIn& in, unsigned p0, unsigned p1, int c, int gs, int vc,
-                                           float4 (&G)[T], float& D, float& cnt) {
-  float C = 0.f;
+__device__ __forceinline__ void add_occurrence(const SortedIn& in, uint2 pr, int c, int gs, int vc, float4 (&G)[T],
+                                               float& C, float& D, float& cnt) {
+  const float x = __uint_as_float(pr.y);
+  const float* r = in.rec + (int64_t)pr.x * in.rec_ld;
+  const float pgx = __ldg(r) * x;
+  C += pgx;
+  D = fmaf(pgx, x, D);
+  cnt += 1.0f;
 #pragma unroll
-  for (int t = 0; t < T; ++t) G[t] = make_float4(0.f, 0.f, 0.f, 0.f);
-  D = 0.f; cnt = 0.f;
-#pragma unroll 2
-  for (unsigned p = p0; p < p1; ++p) {
-    const uint2 pr = __ldg(in.pairs + p);
-    const float x = __uint_as_float(pr.y);
-    const float* r = in.rec + (int64_t)pr.x * in.rec_ld;
-    const float pgx = __ldg(r) * x;
-    C += pgx;
-    D = fmaf(pgx, x, D);
-    cnt += 1.0f;
-#pragma unroll
-    for (int t = 0; t < T; ++t) {
-      const int chunk = c + t * gs;
-      if (chunk < vc) {
-        const float4 s = __ldg(reinterpret_cast<const float4*>(r + 4 * chunk));
-        G[t].x = fmaf(pgx, s.x, G[t].x); G[t].y = fmaf(pgx, s.y, G[t].y);
-        G[t].z = fmaf(pgx, s.z, G[t].z); G[t].w = fmaf(pgx, s.w, G[t].w);
-      }
+  for (int t = 0; t < T; ++t) {
+    const int chunk = c + t * gs;
+    if (chunk < vc) {
+      const float4 s = __ldg(reinterpret_cast<const float4*>(r + 4 * chunk));
+      G[t].x = fmaf(pgx, s.x, G[t].x); G[t].y = fmaf(pgx, s.y, G[t].y);
+      G[t].z = fmaf(pgx, s.z, G[t].z); G[t].w = fmaf(pgx, s.w, G[t].w);
     }
   }
-  if (c == 0) G[0].x = C;      // column 0 of a record holds pg, not a factor sum: its column is C itself
 }
 
 template <int T>
@@ -100,8 +90,11 @@ __device__ __forceinline__ void apply_row(float* __restrict__ table, float* __re
   }
 }
 
-// one lane group per chunk.  gs lanes = the float4 chunks of a K+1 wide row (at most 32; wider rows take T chunks
-// per lane); a warp works on 32 / gs chunks at once.
+// One lane group per SORTED POSITION; the positions that open a run of equal keys, or sit on a multiple of
+// FM_SORT_CHUNK inside one, do the work (their piece ends at the next such position), the others leave at once.
+// gs lanes = the float4 chunks of a K+1 wide row (at most 32; wider rows take T chunks per lane); a warp covers
+// 32 / gs positions per step, so keys are read coalesced and a piece's row address is known one L2 round trip
+// after the group starts.
 template <int T>
 __global__ void __launch_bounds__(256)
 sorted_update_kernel(float* __restrict__ table, float* __restrict__ accum, int64_t ld, const SortedIn in, int K,
@@ -109,8 +102,7 @@ sorted_update_kernel(float* __restrict__ table, float* __restrict__ accum, int64
                      unsigned* __restrict__ hot_count, const unsigned long long* __restrict__ guard, int gs,
                      unsigned key_mask) {
   if (guard && *guard != kNoError) return;
-  const int64_t n_chunks = in.counts[0];
-  const unsigned n = (unsigned)in.counts[2];
+  const unsigned n = (unsigned)in.counts[0];
   const int lane = threadIdx.x & 31;
   const int per_warp = 32 / gs;
   const int g = lane / gs, c = lane - g * gs;
@@ -118,16 +110,20 @@ sorted_update_kernel(float* __restrict__ table, float* __restrict__ accum, int64
   const int vc = (K + 4) >> 2;
   const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
   const int64_t warp_id = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  for (int64_t base = warp_id * per_warp; base < n_chunks; base += warps_total * per_warp) {
-    const int64_t q = base + g;
-    if (!(lane_on && q < n_chunks)) continue;          // no warp-wide operation below
-    const unsigned p0 = in.starts[q], p1 = in.starts[q + 1];
-    const unsigned key = in.keys[p0];
-    const bool first = p0 == 0 || in.keys[p0 - 1] != key;
-    const bool last = p1 == n || in.keys[p1] != key;
+  unsigned heads = 0;                                  // runs opened by this lane (lane c == 0 of a group counts)
+  for (int64_t base = warp_id * per_warp; base < n; base += warps_total * per_warp) {
+    const int64_t p64 = base + g;
+    if (!(lane_on && p64 < n)) continue;               // no warp-wide operation below
+    const unsigned p0 = (unsigned)p64;
+    const unsigned key = __ldg(in.keys + p0);
+    const bool first = p0 == 0 || __ldg(in.keys + p0 - 1) != key;
+    if (!first && (p0 % FM_SORT_CHUNK) != 0) continue; // inside someone else's piece
+    unsigned knext = p0 + 1 < n ? __ldg(in.keys + p0 + 1) : ~key;
+    uint2 pr = __ldg(in.pairs + p0);
     const int64_t row = (int64_t)(key & key_mask) * ld;
     float4 w[T], h[T], G[T];
-    if (first && last) {                               // the usual case: the whole run; start the row loads now
+    if (first) {                                       // nearly always the whole run: start the row loads now
+      heads += c == 0;
 #pragma unroll
       for (int t = 0; t < T; ++t) {
         const int chunk = c + t * gs;
@@ -137,8 +133,19 @@ sorted_update_kernel(float* __restrict__ table, float* __restrict__ accum, int64
         }
       }
     }
-    float D, cnt;
-    reduce_run<T>(in, p0, p1, c, gs, vc, G, D, cnt);
+#pragma unroll
+    for (int t = 0; t < T; ++t) G[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+    float C = 0.f, D = 0.f, cnt = 0.f;
+    unsigned p1 = p0;
+    while (true) {
+      add_occurrence<T>(in, pr, c, gs, vc, G, C, D, cnt);
+      ++p1;
+      if (p1 >= n || (p1 % FM_SORT_CHUNK) == 0 || knext != key) break;
+      pr = __ldg(in.pairs + p1);
+      knext = p1 + 1 < n ? __ldg(in.keys + p1 + 1) : ~key;
+    }
+    if (c == 0) G[0].x = C;        // column 0 of a record holds pg, not a factor sum: its column is C itself
+    const bool last = p1 >= n || knext != key;         // knext = keys[p1] here
     if (first && last) {
       apply_row<T>(table, accum, row, c, gs, vc, K, w, h, G, D, cnt, st);
       continue;
@@ -156,6 +163,9 @@ sorted_update_kernel(float* __restrict__ table, float* __restrict__ accum, int64
       if (first) hot[atomicAdd(hot_count, 1u)] = p1 / FM_SORT_CHUNK;   // the run's first piece: someone finishes it
     }
   }
+  // number of distinct rows (tf.unique's U): one atomic per warp
+  heads = (unsigned)warp_sum((int)heads);
+  if (lane == 0 && heads) atomicAdd(reinterpret_cast<unsigned long long*>(in.counts + 1), (unsigned long long)heads);
 }
 
 // the cut runs: add the pieces' partial sums in order, then the step.  One lane group per run.
@@ -167,7 +177,7 @@ sorted_finish_kernel(float* __restrict__ table, float* __restrict__ accum, int64
                      unsigned key_mask) {
   if (guard && *guard != kNoError) return;
   const unsigned n_hot = *hot_count;
-  const unsigned n = (unsigned)in.counts[2];
+  const unsigned n = (unsigned)in.counts[0];
   const int lane = threadIdx.x & 31;
   const int per_warp = 32 / gs;
   const int g = lane / gs, c = lane - g * gs;
@@ -226,8 +236,7 @@ FM_EXPORT size_t fm_sorted_workspace(int64_t capacity, int64_t factor_num) {
 }
 
 FM_EXPORT int fm_sorted_update(float* table, float* accum, int64_t table_ld, const uint32_t* sorted_keys,
-                               const uint32_t* sorted_pairs, const uint32_t* chunk_starts, const int64_t* counts,
-                               int64_t capacity, const float* records, int64_t record_ld, int64_t factor_num,
+                               const uint32_t* sorted_pairs, int64_t* counts, int64_t capacity, const float* records, int64_t record_ld, int64_t factor_num,
                                int optimizer, float learning_rate, float factor_lambda, float bias_lambda,
                                float reg_grad, int64_t row_bits, const uint64_t* guard, void* workspace,
                                size_t workspace_bytes, void* stream_) {
@@ -238,7 +247,7 @@ FM_EXPORT int fm_sorted_update(float* table, float* accum, int64_t table_ld, con
   FM_REQUIRE(optimizer == FM_OPT_ADAGRAD || optimizer == FM_OPT_SGD, "fm_sorted_update: unknown optimizer");
   FM_REQUIRE(row_bits >= 0 && row_bits <= 32, "fm_sorted_update: bad row_bits");
   if (capacity == 0) return FM_OK;
-  FM_REQUIRE(table && (accum || optimizer == FM_OPT_SGD) && sorted_keys && sorted_pairs && chunk_starts && counts &&
+  FM_REQUIRE(table && (accum || optimizer == FM_OPT_SGD) && sorted_keys && sorted_pairs && counts &&
              records && workspace, "fm_sorted_update: null pointer");
   FM_REQUIRE((((uintptr_t)table | (uintptr_t)accum | (uintptr_t)records) & 15) == 0 && ((uintptr_t)sorted_pairs & 7) == 0,
              "fm_sorted_update: table, accum, records 16-byte aligned; sorted_pairs 8-byte aligned");
@@ -256,7 +265,8 @@ FM_EXPORT int fm_sorted_update(float* table, float* accum, int64_t table_ld, con
   float* part = reinterpret_cast<float*>(ws + fm_align_up(256 + sizeof(unsigned) * (size_t)cuts_of(capacity), 256));
   const int64_t part_ld = part_ld_of(factor_num);
   FM_CUDA(cudaMemsetAsync(hot_count, 0, sizeof(unsigned), stream));
-  SortedIn in{sorted_keys, reinterpret_cast<const uint2*>(sorted_pairs), chunk_starts, counts, records, record_ld};
+  FM_CUDA(cudaMemsetAsync(counts + 1, 0, sizeof(int64_t), stream));
+  SortedIn in{sorted_keys, reinterpret_cast<const uint2*>(sorted_pairs), counts, records, record_ld};
   Step st{learning_rate, reg_grad * factor_lambda, reg_grad * bias_lambda, optimizer == FM_OPT_SGD ? kOptSgd : kOptAdagrad};
   // sharded tables sort by owner << row_bits | row: the owner's shard is indexed by the row alone
   const unsigned key_mask = row_bits == 0 || row_bits >= 32 ? 0xffffffffu : ((1u << row_bits) - 1u);

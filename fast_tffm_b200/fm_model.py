@@ -487,19 +487,18 @@ class Model(object):
 
     def _sort(self, b, n_lines, mark=_no_mark, max_blocks=0):
         """occurrences of the parsed batch in `b` sorted by table row (fm_sort_by_row); counts land in
-        status[3:6] = n_chunks, n_unique, nnz"""
+        status[3] = nnz sorted, status[4] = n_unique (once the update has run)"""
         lib, st, dev = load(), stream(), self.device
         if b.get("skeys") is None:
             cap = b["cap"]
             b["skeys"] = torch.empty(cap, dtype=torch.int32, device=dev)
             b["spairs"] = torch.empty(cap, 2, dtype=torch.int32, device=dev)
-            b["chunks"] = torch.empty(cap + 2, dtype=torch.int32, device=dev)
             b["ws_sort"] = _lib.workspace(lib.fm_sort_workspace(cap), dev)
             b["rec_ld"] = int(lib.fm_sorted_record_ld(self.factor_num))
             b["rec"] = torch.empty(b["lines"], b["rec_ld"], dtype=torch.float32, device=dev)
             b["ws_sorted"] = _lib.workspace(lib.fm_sorted_workspace(cap, self.factor_num), dev)
         check(lib.fm_sort_by_row(ptr(b["ids"]), ptr(b["vals"]), ptr(b["poses"]), n_lines, b["cap"], _off(b["status"], 1),
-                                 self.vocabulary_size, 1, ptr(b["skeys"]), ptr(b["spairs"]), ptr(b["chunks"]),
+                                 self.vocabulary_size, 1, ptr(b["skeys"]), ptr(b["spairs"]),
                                  _off(b["status"], 3), ptr(b["status"]), ptr(b["ws_sort"]), b["ws_sort"].numel(),
                                  max_blocks, st), "fm_sort_by_row")
         mark("sort")
@@ -557,7 +556,7 @@ class Model(object):
                 ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st), "fm_sorted_score")
             mark("score")
             check(lib.fm_sorted_update(
-                ptr(self.table), ptr(self.accum), tstride, ptr(b["skeys"]), ptr(b["spairs"]), ptr(b["chunks"]),
+                ptr(self.table), ptr(self.accum), tstride, ptr(b["skeys"]), ptr(b["spairs"]),
                 _off(b["status"], 3), b["cap"], ptr(b["rec"]), b["rec_ld"], k, _lib.OPTIMIZER[self.optimizer],
                 self.learning_rate, self.factor_lambda, self.bias_lambda, 1.0 / self.batch_size, 0,
                 ptr(b["status"]), ptr(b["ws_sorted"]), b["ws_sorted"].numel(), st), "fm_sorted_update")

@@ -259,15 +259,16 @@ int fm_fused_adagrad_claim(float* table, float* accum, int64_t table_ld, const i
  *                    grouped by owning rank of an `id % n_ranks` partition, rows ascending inside)
  *   sorted_pairs[2n] (example index, bits of feature_vals) of each occurrence, in that order; occurrences
  *                    of one row keep their batch order (the sort is stable => sums are reproducible)
- *   chunk_starts[]   start of every run of equal keys, runs cut at multiples of FM_SORT_CHUNK so that no work
- *                    item is longer; chunk_starts[n_chunks] = n; capacity + 2 entries
- *   counts[3]        device int64: n_chunks, number of distinct keys (= tf.unique's U), n
+ *   counts[2]        device int64: counts[0] = n (written here), counts[1] = number of distinct keys (= tf.unique's
+ *                    U; written by fm_sorted_update, which counts the runs it walks)
  *   guard tripped (*guard != UINT64_MAX): counts = 0, nothing sorted.
  *   vocab_size <= 2^32, capacity < 2^30.  max_blocks: grid cap (0 = default), as in fm_parse_fill.
  * fm_sorted_score: fm_fused_score_scatter's scorer + loss; instead of scattering it leaves one record per
  *   example, records[i] = [pg_i, s_i1 .. s_iK] (pg = d loss / d pred_i / loss_batch; s_ik = sum_j x_j v_jk,
  *   cc/fm_grad_op.h:42-47), record_ld >= fm_sorted_record_ld(K) floats.
- * fm_sorted_update: one lane group per run: G_0 = C + cnt rg lb b, G_k = v_k (cnt rg lf - D) + B_k from the
+ * fm_sorted_update: one lane group per run of equal keys (runs longer than FM_SORT_CHUNK occurrences are cut into
+ *   pieces whose partial sums are added up, in order, by a second short kernel -- hot rows under skewed ids):
+ *   G_0 = C + cnt rg lb b, G_k = v_k (cnt rg lf - D) + B_k from the
  *   run's occurrences (C = sum pg x, D = sum pg x^2, B_k = sum pg x s_k), then the optimizer step on
  *   table / accum rows (key & (2^row_bits - 1); row_bits = 0: the key is the row).  FM_OPT_ADAGRAD = TF1
  *   SparseApplyAdagrad; FM_OPT_SGD (w -= lr G; accum unused, may be NULL) is an extension -- the reference only
@@ -277,7 +278,7 @@ enum { FM_OPT_ADAGRAD = 0, FM_OPT_SGD = 1 };
 size_t fm_sort_workspace(int64_t capacity);
 int fm_sort_by_row(const int64_t* feature_ids, const float* feature_vals, const int32_t* feature_poses,
                    int64_t batch, int64_t capacity, const int64_t* nnz_dev, int64_t vocab_size,
-                   int64_t n_ranks, uint32_t* sorted_keys, uint32_t* sorted_pairs, uint32_t* chunk_starts,
+                   int64_t n_ranks, uint32_t* sorted_keys, uint32_t* sorted_pairs,
                    int64_t* counts, const uint64_t* guard, void* workspace, size_t workspace_bytes,
                    int max_blocks, void* stream);
 int64_t fm_sorted_record_ld(int64_t factor_num);
@@ -289,8 +290,7 @@ int fm_sorted_score(const int64_t* feature_ids, const float* feature_vals, const
                     size_t workspace_bytes, void* stream);
 size_t fm_sorted_workspace(int64_t capacity, int64_t factor_num);
 int fm_sorted_update(float* table, float* accum, int64_t table_ld, const uint32_t* sorted_keys,
-                     const uint32_t* sorted_pairs, const uint32_t* chunk_starts, const int64_t* counts,
-                     int64_t capacity, const float* records, int64_t record_ld, int64_t factor_num,
+                     const uint32_t* sorted_pairs, int64_t* counts, int64_t capacity, const float* records, int64_t record_ld, int64_t factor_num,
                      int optimizer, float learning_rate, float factor_lambda, float bias_lambda,
                      float reg_grad, int64_t row_bits, const uint64_t* guard, void* workspace,
                      size_t workspace_bytes, void* stream);

@@ -10,7 +10,8 @@ def close(got, exp, scale):
     got, exp = np.asarray(got, np.float64), np.asarray(exp, np.float64)
     err = np.abs(got - exp)
     tol = RTOL * (np.abs(exp) + scale)
-    assert (err <= tol).all(), "max err %g, tol there %g" % (err.max(), tol[np.argmax(err - tol)])
+    tol = np.broadcast_to(tol, err.shape)
+    assert (err <= tol).all(), "max err %g, tol there %g" % (err.max(), tol.flat[np.argmax(err - tol)])
 
 
 def pred_scale(f):
