@@ -464,10 +464,10 @@ def main():
     ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3"],
                     help="cfg2 (default): 2^24 vocab, K=16, 65536 examples per GPU; cfg3: 2^27 vocab, K=64, "
                          "32768 examples per GPU (BASELINE config 3, 8 GPUs)")
-    ap.add_argument("--path", default="sorted", choices=["sorted", "claim", "fused", "composed"],
-                    help="sorted: run-ahead radix sort by row + segment-reduce update (default); claim: no unique, "
-                         "table-shaped accumulators; fused: unique + compact accumulators; composed: the reference's "
-                         "op-by-op chain")
+    ap.add_argument("--path", default="claim", choices=["sorted", "claim", "fused", "composed"],
+                    help="claim: no unique, table-shaped accumulators (default: the fastest measured); sorted: radix "
+                         "sort by row + segment-reduce update; fused: unique + compact accumulators; composed: the "
+                         "reference's op-by-op chain")
     ap.add_argument("--layout", default=None, choices=["pair", "split", "interleaved"],
                     help="default: pair ([w | h] per id) for the sorted path, interleaved ([w | h | g]) for the others")
     ap.add_argument("--no-parse-ahead", action="store_true",

@@ -1,6 +1,7 @@
 // fm_api.cu -- library-wide pieces of the C ABI: version and per-thread error text.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 #include "fm_common.cuh"
 
@@ -12,6 +13,11 @@ int fm_fail(int code, const char* fmt, ...) {
   vsnprintf(g_error, sizeof g_error, fmt, ap);
   va_end(ap);
   return code;
+}
+
+int fm_env_int(const char* name, int fallback) {
+  const char* v = getenv(name);
+  return v && *v ? atoi(v) : fallback;
 }
 
 FM_EXPORT int fm_abi_version(void) { return FM_B200_ABI_VERSION; }

@@ -27,6 +27,9 @@ int fm_fail(int code, const char* fmt, ...);
 
 static inline size_t fm_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// tuning knob read once from the environment (experiments only; the defaults are the measured optima)
+int fm_env_int(const char* name, int fallback);
+
 namespace fm {
 
 constexpr int kWarp = 32;

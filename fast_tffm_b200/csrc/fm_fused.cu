@@ -660,8 +660,10 @@ static inline bool pick_shape(int64_t chunks, Shape* s) {
   }
 
 static inline int fused_blocks(int64_t batch) {
+  static const int bpsm = fm_env_int("FM_SCORE_BLOCKS_PER_SM", 8);
   int64_t b = (batch + kWarps - 1) / kWarps;
-  if (b > 148 * 8) b = 148 * 8;
+  if (b > 148 * 8) b = 148 * 8;      // the workspace is sized for this many partials
+  if (b > 148 * bpsm && bpsm > 0 && bpsm < 8) b = 148 * bpsm;
   return (int)(b < 1 ? 1 : b);
 }
 

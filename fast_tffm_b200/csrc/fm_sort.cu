@@ -95,19 +95,16 @@ __device__ __forceinline__ unsigned key_of(int64_t id, int n_ranks, int row_bits
   return ((u % (unsigned)n_ranks) << row_bits) | (u / (unsigned)n_ranks);
 }
 
-// example[j] = i for poses[i] <= j < poses[i + 1]: a binary search per occurrence over the B + 1 bounds (the
-// upper levels of the search stay in L1; neighbouring occurrences take the same path)
+// example[j] = i for poses[i] <= j < poses[i + 1]: eight lanes per example write its range
 __global__ void __launch_bounds__(kThreads)
 expand_kernel(const int32_t* __restrict__ poses, int64_t batch, unsigned* __restrict__ example, int64_t cap,
               const int64_t* __restrict__ n_dev, const unsigned long long* __restrict__ guard) {
   const int64_t n = live_count(cap, n_dev, guard);
-  for (int64_t j = (int64_t)blockIdx.x * kThreads + threadIdx.x; j < n; j += (int64_t)gridDim.x * kThreads) {
-    int64_t lo = 0, hi = batch;                  // invariant: poses[lo] <= j < poses[hi]
-    while (hi - lo > 1) {
-      const int64_t mid = (lo + hi) >> 1;
-      if (__ldg(poses + mid) <= j) lo = mid; else hi = mid;
-    }
-    example[j] = (unsigned)lo;
+  const int sub = threadIdx.x & 7;
+  const int64_t groups = (int64_t)gridDim.x * (kThreads / 8);
+  for (int64_t i = (int64_t)blockIdx.x * (kThreads / 8) + (threadIdx.x >> 3); i < batch; i += groups) {
+    const int64_t a = __ldg(poses + i), b = min((int64_t)__ldg(poses + i + 1), n);
+    for (int64_t j = a + sub; j < b; j += 8) example[j] = (unsigned)i;
   }
 }
 
@@ -313,7 +310,7 @@ FM_EXPORT int fm_sort_by_row(const int64_t* feature_ids, const float* feature_va
   const int64_t cells = tiles * kBins;
   const int cap_blocks = max_blocks > 0 ? max_blocks : 148 * 8;
   const unsigned grid = (unsigned)(tiles < cap_blocks ? tiles : cap_blocks);
-  int64_t eb = (capacity + kThreads - 1) / kThreads;
+  int64_t eb = (batch + kThreads / 8 - 1) / (kThreads / 8);
   if (eb > cap_blocks) eb = cap_blocks;
   expand_kernel<<<(unsigned)eb, kThreads, 0, stream>>>(feature_poses, batch, ws.example, capacity, nnz_dev, g);
   FM_LAUNCH_CHECK();

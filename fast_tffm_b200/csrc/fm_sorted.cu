@@ -39,27 +39,6 @@ struct Step {
 
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 
-// one occurrence's terms for lane chunk(s) c + t * gs of the row: G[t] = (. | B_k) columns, C, D, cnt
-template <int T>
-__device__ __forceinline__ void add_occurrence(const SortedIn& in, uint2 pr, int c, int gs, int vc, float4 (&G)[T],
-                                               float& C, float& D, float& cnt) {
-  const float x = __uint_as_float(pr.y);
-  const float* r = in.rec + (int64_t)pr.x * in.rec_ld;
-  const float pgx = __ldg(r) * x;
-  C += pgx;
-  D = fmaf(pgx, x, D);
-  cnt += 1.0f;
-#pragma unroll
-  for (int t = 0; t < T; ++t) {
-    const int chunk = c + t * gs;
-    if (chunk < vc) {
-      const float4 s = __ldg(reinterpret_cast<const float4*>(r + 4 * chunk));
-      G[t].x = fmaf(pgx, s.x, G[t].x); G[t].y = fmaf(pgx, s.y, G[t].y);
-      G[t].z = fmaf(pgx, s.z, G[t].z); G[t].w = fmaf(pgx, s.w, G[t].w);
-    }
-  }
-}
-
 template <int T>
 __device__ __forceinline__ void apply_row(float* __restrict__ table, float* __restrict__ accum, int64_t row, int c,
                                           int gs, int vc, int K, const float4 (&w)[T], const float4 (&h)[T],
@@ -110,16 +89,30 @@ sorted_update_kernel(float* __restrict__ table, float* __restrict__ accum, int64
   const int vc = (K + 4) >> 2;
   const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
   const int64_t warp_id = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  unsigned heads = 0;                                  // runs opened by this lane (lane c == 0 of a group counts)
-  for (int64_t base = warp_id * per_warp; base < n; base += warps_total * per_warp) {
-    const int64_t p64 = base + g;
-    if (!(lane_on && p64 < n)) continue;               // no warp-wide operation below
-    const unsigned p0 = (unsigned)p64;
+  unsigned heads = 0;                                  // runs opened, counted by lane c == 0 of the group that walks them
+  // a warp step covers 32 sorted positions: every lane tests one for "opens a piece", then the lane groups take the
+  // pieces found, per_warp at a time (under skewed ids most positions sit inside somebody's piece)
+  for (int64_t base = warp_id * 32; base < n; base += warps_total * 32) {
+    const int64_t mine = base + lane;
+    bool opens = false;
+    if (mine < n) {
+      const unsigned k0 = __ldg(in.keys + mine);
+      opens = mine == 0 || __ldg(in.keys + mine - 1) != k0 || (mine % FM_SORT_CHUNK) == 0;
+    }
+    const unsigned opening = __ballot_sync(kFull, opens);
+    const int n_open = __popc(opening);
+    for (int taken = 0; taken < n_open; taken += per_warp) {       // warp-uniform
+    if (!(lane_on && taken + g < n_open)) continue;                // no warp-wide operation below
+    const unsigned p0 = (unsigned)(base + __fns(opening, 0, taken + g + 1));
     const unsigned key = __ldg(in.keys + p0);
     const bool first = p0 == 0 || __ldg(in.keys + p0 - 1) != key;
-    if (!first && (p0 % FM_SORT_CHUNK) != 0) continue; // inside someone else's piece
-    unsigned knext = p0 + 1 < n ? __ldg(in.keys + p0 + 1) : ~key;
-    uint2 pr = __ldg(in.pairs + p0);
+    // the piece ends at the next key change, multiple of FM_SORT_CHUNK or n (one more key read in the usual case)
+    unsigned p1 = p0 + 1;
+    unsigned knext = p1 < n ? __ldg(in.keys + p1) : ~key;
+    while (p1 < n && (p1 % FM_SORT_CHUNK) != 0 && knext == key) {
+      ++p1;
+      knext = p1 < n ? __ldg(in.keys + p1) : ~key;
+    }
     const int64_t row = (int64_t)(key & key_mask) * ld;
     float4 w[T], h[T], G[T];
     if (first) {                                       // nearly always the whole run: start the row loads now
@@ -136,13 +129,38 @@ sorted_update_kernel(float* __restrict__ table, float* __restrict__ accum, int64
 #pragma unroll
     for (int t = 0; t < T; ++t) G[t] = make_float4(0.f, 0.f, 0.f, 0.f);
     float C = 0.f, D = 0.f, cnt = 0.f;
-    unsigned p1 = p0;
-    while (true) {
-      add_occurrence<T>(in, pr, c, gs, vc, G, C, D, cnt);
-      ++p1;
-      if (p1 >= n || (p1 % FM_SORT_CHUNK) == 0 || knext != key) break;
-      pr = __ldg(in.pairs + p1);
-      knext = p1 + 1 < n ? __ldg(in.keys + p1 + 1) : ~key;
+    constexpr int U = 2;                               // occurrences whose gathers are in flight together
+    for (unsigned p = p0; p < p1; p += U) {
+      uint2 pr[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) pr[u] = p + u < p1 ? __ldg(in.pairs + p + u) : make_uint2(0u, 0u);
+      float pg[U];
+      float4 sv[U][T];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (p + u >= p1) continue;
+        const float* r = in.rec + (int64_t)pr[u].x * in.rec_ld;
+        pg[u] = __ldg(r);
+#pragma unroll
+        for (int t = 0; t < T; ++t)
+          if (c + t * gs < vc) sv[u][t] = __ldg(reinterpret_cast<const float4*>(r + 4 * (c + t * gs)));
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {                    // added in sorted (= batch) order
+        if (p + u >= p1) continue;
+        const float x = __uint_as_float(pr[u].y);
+        const float pgx = pg[u] * x;
+        C += pgx;
+        D = fmaf(pgx, x, D);
+        cnt += 1.0f;
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+          if (c + t * gs < vc) {
+            G[t].x = fmaf(pgx, sv[u][t].x, G[t].x); G[t].y = fmaf(pgx, sv[u][t].y, G[t].y);
+            G[t].z = fmaf(pgx, sv[u][t].z, G[t].z); G[t].w = fmaf(pgx, sv[u][t].w, G[t].w);
+          }
+        }
+      }
     }
     if (c == 0) G[0].x = C;        // column 0 of a record holds pg, not a factor sum: its column is C itself
     const bool last = p1 >= n || knext != key;         // knext = keys[p1] here
@@ -162,13 +180,16 @@ sorted_update_kernel(float* __restrict__ table, float* __restrict__ accum, int64
       *reinterpret_cast<float4*>(dst + 4 * vc) = make_float4(D, cnt, 0.f, 0.f);
       if (first) hot[atomicAdd(hot_count, 1u)] = p1 / FM_SORT_CHUNK;   // the run's first piece: someone finishes it
     }
+    }
   }
   // number of distinct rows (tf.unique's U): one atomic per warp
   heads = (unsigned)warp_sum((int)heads);
   if (lane == 0 && heads) atomicAdd(reinterpret_cast<unsigned long long*>(in.counts + 1), (unsigned long long)heads);
 }
 
-// the cut runs: add the pieces' partial sums in order, then the step.  One lane group per run.
+// the cut runs: add the pieces' partial sums, then the step.  One WARP per run: its lane groups take the pieces
+// round-robin (a very hot row has hundreds of them), the groups' sums are combined by shuffles in a fixed order,
+// group 0 applies the step.  Same result every time.
 template <int T>
 __global__ void __launch_bounds__(256)
 sorted_finish_kernel(float* __restrict__ table, float* __restrict__ accum, int64_t ld, const SortedIn in, int K,
@@ -181,12 +202,11 @@ sorted_finish_kernel(float* __restrict__ table, float* __restrict__ accum, int64
   const int lane = threadIdx.x & 31;
   const int per_warp = 32 / gs;
   const int g = lane / gs, c = lane - g * gs;
+  const bool lane_on = g < per_warp;
   const int vc = (K + 4) >> 2;
   const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
   const int64_t warp_id = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  for (int64_t base = warp_id * per_warp; base < n_hot; base += warps_total * per_warp) {
-    const int64_t e = base + g;
-    if (!(g < per_warp && e < n_hot)) continue;
+  for (int64_t e = warp_id; e < n_hot; e += warps_total) {          // warp-uniform
     const unsigned cut0 = hot[e];
     const unsigned key = in.keys[cut0 * FM_SORT_CHUNK - 1];
     const int64_t row = (int64_t)(key & key_mask) * ld;
@@ -195,7 +215,8 @@ sorted_finish_kernel(float* __restrict__ table, float* __restrict__ accum, int64
     for (int t = 0; t < T; ++t) {
       const int chunk = c + t * gs;
       G[t] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (chunk < vc) {
+      w[t] = G[t]; h[t] = G[t];
+      if (lane_on && g == 0 && chunk < vc) {
         w[t] = ld4(table + row + 4 * chunk);
         h[t] = st.opt == kOptAdagrad ? ld4(accum + row + 4 * chunk) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
@@ -214,10 +235,30 @@ sorted_finish_kernel(float* __restrict__ table, float* __restrict__ accum, int64
       const float4 tail = ld4(src + 4 * vc);
       D += tail.x; cnt += tail.y;
     };
-    add(2 * (int64_t)cut0);
-    for (unsigned cut = cut0; (uint64_t)cut * FM_SORT_CHUNK < n && in.keys[cut * FM_SORT_CHUNK] == key; ++cut)
-      add(2 * (int64_t)cut + 1);
-    apply_row<T>(table, accum, row, c, gs, vc, K, w, h, G, D, cnt, st);
+    if (lane_on) {
+      if (g == 0) add(2 * (int64_t)cut0);                           // the run's first piece
+      // the pieces after cut0, cut0 + 1, ...: group g takes every per_warp-th; the keys are sorted, so the first
+      // cut that no longer continues the run ends the group's walk
+      for (unsigned cut = cut0 + g; (uint64_t)cut * FM_SORT_CHUNK < n && in.keys[cut * FM_SORT_CHUNK] == key;
+           cut += per_warp)
+        add(2 * (int64_t)cut + 1);
+    }
+    // group totals, added in group order on every lane
+    float Dt = 0.f, ct = 0.f;
+    float4 Gt[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) Gt[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int g2 = 0; g2 < per_warp; ++g2) {
+      const int src = c + g2 * gs;
+      Dt += __shfl_sync(kFull, D, src);
+      ct += __shfl_sync(kFull, cnt, src);
+#pragma unroll
+      for (int t = 0; t < T; ++t) {
+        Gt[t].x += __shfl_sync(kFull, G[t].x, src); Gt[t].y += __shfl_sync(kFull, G[t].y, src);
+        Gt[t].z += __shfl_sync(kFull, G[t].z, src); Gt[t].w += __shfl_sync(kFull, G[t].w, src);
+      }
+    }
+    if (lane_on && g == 0) apply_row<T>(table, accum, row, c, gs, vc, K, w, h, Gt, Dt, ct, st);
   }
 }
 
@@ -273,8 +314,12 @@ FM_EXPORT int fm_sorted_update(float* table, float* accum, int64_t table_ld, con
   const unsigned long long* g = reinterpret_cast<const unsigned long long*>(guard);
   const int64_t per_block = 8 * (32 / gs);
   int64_t blocks = (capacity + per_block - 1) / per_block;
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  int64_t fin_blocks = (cuts_of(capacity) + per_block - 1) / per_block;
+  // Few resident warps on purpose: read + write-back of rows in ascending order runs fastest at about 24 warps per SM
+  // (profiles/r2_bulk_rmw_probe.jsonl: 0.235 ms at 24, 0.29 at 32, 0.55 at 64 for one cfg2 batch), and the
+  // warps and registers left over are what the parse of the next batch runs in.
+  static const int bpsm = fm_env_int("FM_UPDATE_BLOCKS_PER_SM", 4);
+  if (blocks > 148 * bpsm) blocks = 148 * bpsm;
+  int64_t fin_blocks = (cuts_of(capacity) + 7) / 8;                  // a warp per cut run
   if (fin_blocks > 148 * 4) fin_blocks = 148 * 4;
 #define CALL(T)                                                                                                      \
   sorted_update_kernel<T><<<(unsigned)blocks, 256, 0, stream>>>(table, accum, table_ld, in, (int)factor_num, st,    \

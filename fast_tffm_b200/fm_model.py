@@ -280,17 +280,19 @@ class Model(object):
 
     # ---- the vocabulary table ------------------------------------------------------
     def build(self, device=None, init_table=None, seed=None, max_nnz_per_line=None, ld=None,
-              layout="pair", path=None):
+              layout=None, path=None):
         """Allocates table + Adagrad accumulator (+ table-shaped gradient accumulator) in HBM.
         The table is [vocabulary_size, ld] (row = feature id, see _stride_for); the reference's
         vocabulary_block_num blocks (fm_model.py:269-284) are a relabelling applied when
         checkpoints are written (blocks_state / load_blocks_state).
-        layout "pair" (default): one array whose row holds [w | h], the weight and Adagrad rows of one
-        id side by side in whole 128-byte lines -- what the sorted path touches per id; "interleaved":
-        [w | h | g] with the claim path's gradient-accumulator row beside them; "split": separate arrays.
-        Every path runs on every layout (a path that needs an accumulator table the layout lacks
-        allocates it on first use).
-        path: the default of train_step / parse_ahead: "sorted" unless the row is too wide for it.
+        layout "interleaved": one array whose row holds [w | h | g], the weight, Adagrad and the claim path's
+        gradient-accumulator rows of one id side by side in whole 128-byte lines; "pair": [w | h] only -- what
+        the sorted path touches per id, two thirds of the memory; "split": separate arrays.  Every path runs on
+        every layout (a path that needs an accumulator table the layout lacks allocates it on first use).
+        Default: the layout of the default path.
+        path: the default of train_step / parse_ahead.  "claim" unless the optimizer is sgd: measured on one
+        B200 at cfg2 it is the faster of the two (uniform ids 0.56 vs 0.63 ms per step, zipf 0.34 vs 0.57;
+        profiles/README.md r2); "sorted" is the reproducible one and the one that needs no third table.
         init: uniform(-init_value_range, init_value_range) (:278-281) or `init_table`
         ([vocabulary_size, K+1], for parity runs)."""
         lib = load()
@@ -303,16 +305,18 @@ class Model(object):
         self.ld = _ld_for(k) if ld is None else int(ld)
         assert self.ld >= k + 1 and self.ld % 4 == 0
         self.gld = _stride_for(int(lib.fm_fused_gacc_ld(k)))
-        self.layout = layout
-        if layout not in ("pair", "interleaved", "split"):
-            raise ValueError("layout must be pair, interleaved or split")
         if self.optimizer not in ("adagrad", "sgd"):
             raise ValueError("optimizer must be adagrad or sgd")
         sortable = (k + 4) // 4 <= 96 and v <= 1 << 32
         if path is None:
-            path = "sorted" if sortable else "claim"
+            path = "sorted" if self.optimizer == "sgd" else "claim"
+        if layout is None:
+            layout = "pair" if path == "sorted" else "interleaved"
+        if layout not in ("pair", "interleaved", "split"):
+            raise ValueError("layout must be pair, interleaved or split")
         if path not in self.PATHS or (path == "sorted" and not sortable) or (self.optimizer == "sgd" and path != "sorted"):
             raise ValueError("path %r not available for factor_num %d / optimizer %s" % (path, k, self.optimizer))
+        self.layout = layout
         self.default_path = path
         if layout == "pair":
             # [w | h] of one id packed at 16-byte granularity in whole 128-byte lines (K=16: 2 x 20 floats in

@@ -273,7 +273,7 @@ int fm_fused_adagrad_claim(float* table, float* accum, int64_t table_ld, const i
  *   table / accum rows (key & (2^row_bits - 1); row_bits = 0: the key is the row).  FM_OPT_ADAGRAD = TF1
  *   SparseApplyAdagrad; FM_OPT_SGD (w -= lr G; accum unused, may be NULL) is an extension -- the reference only
  *   ever builds AdagradOptimizer (tffm/fm_model.py:341-344).  guard as in fm_sparse_adagrad. */
-#define FM_SORT_CHUNK 128
+#define FM_SORT_CHUNK 32
 enum { FM_OPT_ADAGRAD = 0, FM_OPT_SGD = 1 };
 size_t fm_sort_workspace(int64_t capacity);
 int fm_sort_by_row(const int64_t* feature_ids, const float* feature_vals, const int32_t* feature_poses,
