@@ -215,3 +215,87 @@ FM_EXPORT int fm_shard_combine(const float* src_rows, int64_t src_ld, const int6
   FM_LAUNCH_CHECK();
   return FM_OK;
 }
+
+// ---- barrier + tiny all-reduce over peer-mapped memory (the sharded step's two synchronisation points) ----
+// Every rank owns FM_PEER_SYNC_BYTES of flag slots inside the allocation that is mapped into all processes:
+// slots[parity][sender] = {epoch, word, a, b}.  A call publishes this rank's {word, a, b} into every rank's
+// slots[epoch & 1][rank] (payload first, then the epoch with release semantics at system scope), waits until all
+// n senders' slots of that parity carry this epoch, and reduces: max of the words, sums of a and b in rank order.
+// Ranks move in lock step (nobody can be more than one call ahead of the slowest rank), so two parities suffice.
+namespace fm {
+namespace {
+
+struct SyncSlot { unsigned long long epoch; long long word; float a, b; unsigned long long pad; };
+static_assert(sizeof(SyncSlot) == 32, "slot layout");
+constexpr int kSyncMaxRanks = 16;
+
+struct SyncBases { SyncSlot* base[kSyncMaxRanks]; };
+
+__global__ void peer_sync_kernel(const SyncBases bases, int rank, int n, unsigned long long epoch,
+                                 const long long* __restrict__ word_in, const float* __restrict__ a_in,
+                                 const float* __restrict__ b_in, long long* __restrict__ word_out,
+                                 float* __restrict__ sums_out) {
+  const int r = threadIdx.x;
+  const int parity = (int)(epoch & 1ull);
+  long long word = word_in ? *word_in : -1;
+  if (word >= 0) word += (long long)rank << 48;           // a parse status word: tag it with the rank that failed
+  if (r < n) {
+    SyncSlot* dst = bases.base[r] + parity * kSyncMaxRanks + rank;
+    dst->word = word;
+    dst->a = a_in ? *a_in : 0.f;
+    dst->b = b_in ? *b_in : 0.f;
+    __threadfence_system();                               // payload (and everything this stream did before) first
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(&dst->epoch), "l"(epoch) : "memory");
+  }
+  float a = 0.f, b = 0.f;
+  word = -1;
+  if (r < n) {
+    const SyncSlot* src = bases.base[rank] + parity * kSyncMaxRanks + r;
+    unsigned long long seen;
+    unsigned polls = 0;
+    do {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(&src->epoch) : "memory");
+    } while (seen != epoch && ++polls < (1u << 26));       // tens of seconds: a rank that died must not hang the box
+    word = *reinterpret_cast<const volatile long long*>(&src->word);
+    if (seen != epoch) word = (1ll << 62) | ((long long)r << 48);   // "rank r never arrived": voids the step
+    a = *reinterpret_cast<const volatile float*>(&src->a);
+    b = *reinterpret_cast<const volatile float*>(&src->b);
+  }
+  // fixed-order reduction over the ranks (lane r holds rank r's contribution)
+  long long wmax = -1;
+  float asum = 0.f, bsum = 0.f;
+  for (int i = 0; i < n; ++i) {
+    const long long wi = __shfl_sync(kFull, word, i);
+    wmax = wi > wmax ? wi : wmax;
+    asum += __shfl_sync(kFull, a, i);
+    bsum += __shfl_sync(kFull, b, i);
+  }
+  if (r == 0) {
+    if (word_out) *word_out = wmax;
+    if (sums_out) { sums_out[0] = asum; sums_out[1] = bsum; }
+  }
+  __threadfence_system();
+}
+
+}  // namespace
+}  // namespace fm
+
+FM_EXPORT size_t fm_peer_sync_bytes(void) { return 2 * kSyncMaxRanks * sizeof(SyncSlot); }
+
+FM_EXPORT int fm_peer_sync(void* const* sync_bases, int64_t rank, int64_t n_ranks, uint64_t epoch,
+                           const int64_t* word_in, const float* a_in, const float* b_in, int64_t* word_out,
+                           float* sums_out, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (n_ranks < 1 || n_ranks > kSyncMaxRanks) return fm_fail(FM_E_LIMIT, "fm_peer_sync: 1..%d ranks", kSyncMaxRanks);
+  FM_REQUIRE(sync_bases && rank >= 0 && rank < n_ranks && epoch > 0, "fm_peer_sync: bad argument (epoch starts at 1)");
+  SyncBases bases;
+  for (int r = 0; r < kSyncMaxRanks; ++r) {
+    bases.base[r] = r < n_ranks ? static_cast<SyncSlot*>(sync_bases[r]) : nullptr;
+    FM_REQUIRE(r >= n_ranks || (bases.base[r] && ((uintptr_t)bases.base[r] & 31) == 0), "fm_peer_sync: bad base");
+  }
+  peer_sync_kernel<<<1, 32, 0, stream>>>(bases, (int)rank, (int)n_ranks, (unsigned long long)epoch,
+                                         reinterpret_cast<const long long*>(word_in), a_in, b_in,
+                                         reinterpret_cast<long long*>(word_out), sums_out);
+  FM_LAUNCH_CHECK();
+  return FM_OK;
+}

@@ -324,18 +324,22 @@ class PeerShardedModel:
         block = (3 * part + 31) // 32 * 32
         self.ld = self.gld = block
         n_store = rows * block
-        n_bits = ((rows + 31) // 32 + 3) // 4 * 4
-        self._symm = symm_mem.empty(n_store + n_bits, dtype=torch.float32, device=dev)
+        n_bits = ((rows + 31) // 32 + 7) // 8 * 8           # keeps what follows 32-byte aligned
+        n_sync = int(self.lib.fm_peer_sync_bytes()) // 4
+        self._symm = symm_mem.empty(n_store + n_bits + n_sync, dtype=torch.float32, device=dev)
         self._hdl = symm_mem.rendezvous(self._symm, self.group)
         self._symm.zero_()
         store = self._symm[:n_store].view(rows, block)
         self.table, self.accum, self.gtab = store[:, :part], store[:, part:2 * part], store[:, 2 * part:3 * part]
-        self.touched = self._symm[n_store:].view(torch.int32)
+        self.touched = self._symm[n_store:n_store + n_bits].view(torch.int32)
         ptrs = [int(p) for p in self._hdl.buffer_ptrs]
         arr = ctypes.c_void_p * g
         self._table_bases = arr(*ptrs)
         self._gtab_bases = arr(*[p + 4 * 2 * part for p in ptrs])
         self._touched_bases = arr(*[p + 4 * n_store for p in ptrs])
+        self._sync_bases = arr(*[p + 4 * (n_store + n_bits) for p in ptrs])
+        self._epoch = 0
+        self._sync_word = torch.zeros(1, dtype=torch.int64, device=dev)
         if init_table is not None:
             part = torch.as_tensor(init_table, dtype=torch.float32)[r::g, :k + 1]
             self.table[:part.shape[0], :k + 1] = part.to(dev)
@@ -506,10 +510,9 @@ class PeerShardedModel:
             _at(b["scal"], 1), ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st),
             "fm_peer_score_scatter")
         mark("score_scatter")
-        # barrier that also tells every rank whether any rank's parse failed
-        err = b["status"][0:1]
-        flag = torch.where(err >= 0, err + (self.rank << 48), err)
-        dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=self.group)
+        # barrier that also tells every rank whether any rank's parse failed (flags in peer-mapped memory)
+        flag = torch.empty(1, dtype=torch.int64, device=self.device)
+        self._sync(ptr(b["status"]), None, None, ptr(flag), None)
         mark("barrier")
         check(lib.fm_peer_touched_rows(ptr(self.touched), self.table.shape[0], ptr(self.row_list),
                                        self.row_list.numel(), ptr(self.n_rows), ptr(self.ws_touched),
@@ -519,8 +522,9 @@ class PeerShardedModel:
                                          cfg.learning_rate, cfg.factor_lambda, cfg.bias_lambda, 1.0 / cfg.batch_size,
                                          ptr(flag), 1, st), "fm_fused_adagrad_claim")
         mark("update")
-        out = b["scal"].clone()
-        dist.all_reduce(out, group=self.group)   # also: nobody reads rows of the next step before all updates ran
+        out = torch.empty(2, dtype=torch.float32, device=self.device)
+        # global loss and reg; also: nobody reads rows of the next step before all updates ran
+        self._sync(None, ptr(b["scal"]), _at(b["scal"], 1), None, ptr(out))
         mark("allreduce_loss")
         if parsed is not None:
             b["free"] = torch.cuda.Event()
@@ -528,6 +532,12 @@ class PeerShardedModel:
         self.global_step += 1
         self.last = dict(pred=b["pred"][:packed.n_lines], packed=packed, status=b["status"])
         return out, flag
+
+    def _sync(self, word_in, a_in, b_in, word_out, sums_out):
+        """fm_peer_sync on the current stream: barrier over the ranks + max / sums of three device values"""
+        self._epoch += 1
+        check(self.lib.fm_peer_sync(self._sync_bases, self.rank, self.world, self._epoch, word_in, a_in, b_in,
+                                    word_out, sums_out, stream()), "fm_peer_sync")
 
     def train_step(self, lines, weights=None, global_batch=None):
         out, flag = self.train_step_async(lines, weights, global_batch)

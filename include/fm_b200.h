@@ -339,6 +339,20 @@ int fm_peer_score_scatter(const int64_t* feature_ids, const float* feature_vals,
                           float factor_lambda, float bias_lambda, int loss_kind, int64_t loss_batch,
                           float* pred_score, float* loss, float* reg_score, const uint64_t* guard,
                           void* workspace, size_t workspace_bytes, void* stream);
+/* fm_peer_sync: the two synchronisation points of that step without a collective library: a barrier over the ranks
+ *   of the box that also reduces three values.  Every rank reserves fm_peer_sync_bytes() (32-byte aligned, zeroed
+ *   once) inside its peer-mapped allocation; sync_bases is the HOST array of those regions as mapped here.  The call
+ *   enqueues one small kernel that publishes {*word_in (+ rank << 48 when it is >= 0: a parser status word),
+ *   *a_in, *b_in} to every rank, waits (spinning on system-scope flags) until all n_ranks ranks have published for
+ *   this epoch, and writes max(word) to *word_out and the sums of a and b, added in rank order, to sums_out[0..1].
+ *   epoch: 1, 2, 3, ... the same sequence on every rank, one per call.  Everything this stream did before the call
+ *   (remote atomics included) is visible to every rank's work after its own call returns on the device.
+ *   NULL inputs count as -1 / 0.  Replaces the all_reduce pair (tffm has no counterpart: its parameter server
+ *   is asynchronous, run_tffm.py:181-206). */
+size_t fm_peer_sync_bytes(void);
+int fm_peer_sync(void* const* sync_bases, int64_t rank, int64_t n_ranks, uint64_t epoch,
+                 const int64_t* word_in, const float* a_in, const float* b_in, int64_t* word_out,
+                 float* sums_out, void* stream);
 size_t fm_peer_touched_workspace(int64_t shard_rows);
 int fm_peer_touched_rows(uint32_t* touched, int64_t shard_rows, int64_t* rows, int64_t capacity,
                          int64_t* n_rows, void* workspace, size_t workspace_bytes, void* stream);

@@ -4,6 +4,7 @@ are bit-exact (they are glibc strtof's bits); scores, losses and gradients are
 held to 1e-5 relative (north_star), with an absolute floor scaled to the size of
 the terms being summed because the second-order term cancels.
 """
+import os
 import random
 
 import numpy as np
@@ -647,6 +648,54 @@ def test_whole_step_at_baseline_shapes(shape, path):
     _close(m.accum[idx, :k + 1].cpu().numpy(), ref.acc[0, rows], 0.0)
     f = ref.forward(lines)
     _close(m.predict(lines).cpu().numpy(), f["pred"], _pred_scale(f))
+
+
+def _cfg1_files():
+    import glob
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lines, weights = [], []
+    for f, wf in zip(sorted(glob.glob(os.path.join(root, "data", "train_*"))),
+                     sorted(glob.glob(os.path.join(root, "data", "weight_*")))):
+        with open(f, "rb") as fh:
+            part = fh.read().split(b"\n")
+        if part and part[-1] == b"":
+            part.pop()
+        lines += part
+        with open(wf) as fh:
+            weights += [float(x) for x in fh.read().split()]
+    return os.path.join(root, "sample.cfg"), lines, np.float32(weights)
+
+
+@pytest.mark.parametrize("loss_type,steps", [("mse", 20), ("logistic", 6)])
+def test_cfg1_sample_cfg_on_the_reference_fixtures(loss_type, steps, capsys, monkeypatch):
+    """BASELINE.json config 1 as written: sample.cfg unmodified (V = 800 000 in 10 blocks, K = 100, batch 50 000,
+    Adagrad(0.01, 0.1), mse with the weight files, 20 epochs = 20 steps over data/train_0..4) and once with logistic
+    loss, files in sorted order, no shuffle, explicit initial table: every step's loss against the oracle model
+    (tffm/fm_model.py:311-348 restated), then the trained table"""
+    cfg, lines, weights = _cfg1_files()
+    monkeypatch.chdir(os.path.dirname(cfg))          # sample.cfg names its files relative to the repository root
+    m = Model(cfg)
+    capsys.readouterr()
+    assert (m.vocabulary_size, m.vocabulary_block_num, m.factor_num, m.batch_size) == (800000, 10, 100, 50000)
+    assert m.loss_type == "mse" and m.num_epochs == 20 and len(m.train_files) == 5 and len(lines) == 50000
+    m.loss_type = loss_type
+    use_w = loss_type == "mse"          # sample.cfg pairs the weight files with the mse objective
+    rng = np.random.default_rng(1)
+    k = m.factor_num
+    flat = rng.uniform(-m.init_value_range, m.init_value_range, (m.vocabulary_size, k + 1)).astype(np.float32)
+    ref = O.RefModel(m.vocabulary_size, m.vocabulary_block_num, k, flat, batch_size=m.batch_size,
+                     factor_lambda=m.factor_lambda, bias_lambda=m.bias_lambda, lr=m.learning_rate,
+                     init_acc=m.adagrad_init_accumulator, loss_type=loss_type)
+    m.build(DEV, init_table=flat)
+    packed = fm_ops.pack_lines(lines).to(DEV, False)
+    w = weights if use_w else None
+    w_dev = None if w is None else dev(w, torch.float32)
+    for step in range(steps):
+        e = ref.train_step(lines, w)
+        got = m.train_step(packed, w_dev)
+        np.testing.assert_allclose(got, e["loss"], rtol=RTOL, err_msg="step %d" % step)
+    _close(m._bufs["pred"][:50000].cpu().numpy(), e["pred"], _pred_scale(e))
+    _assert_model_state(m, ref, k, m.learning_rate, steps)
 
 
 def test_parse_ahead_pipeline_matches_inline_steps(criteo_lines):
