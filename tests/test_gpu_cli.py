@@ -12,10 +12,21 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+def _small_files(tmp_path):
+    """2 x 1000 training lines + weights and 500 test lines cut from the committed excerpt of the reference's
+    data/train_0 (the full fixtures in data/ are the cfg1 test's; these runs only need the command line to work)"""
+    golden = os.path.join(ROOT, "tests", "golden")
+    lines = open(os.path.join(golden, "criteo_excerpt.txt")).read().splitlines()
+    weights = open(os.path.join(golden, "criteo_excerpt_weights.txt")).read().splitlines()
+    for i in range(2):
+        (tmp_path / ("train_%d" % i)).write_text("\n".join(lines[1000 * i:1000 * (i + 1)]) + "\n")
+        (tmp_path / ("weight_%d" % i)).write_text("\n".join(weights[1000 * i:1000 * (i + 1)]) + "\n")
+    (tmp_path / "test_0").write_text("\n".join(lines[1500:2000]) + "\n")
+
+
 @pytest.mark.parametrize("loss_type", ["mse", "logistic"])
 def test_train_then_predict_cli(tmp_path, loss_type):
-    for f in ("train_0", "train_1", "weight_0", "weight_1", "test_0"):
-        shutil.copy(os.path.join(ROOT, "data", f), tmp_path / f)
+    _small_files(tmp_path)
     cfg = open(os.path.join(ROOT, "sample.cfg")).read()
     cfg = cfg.replace("./data/", str(tmp_path) + "/").replace("./log", str(tmp_path / "log"))
     cfg = cfg.replace("batch_size = 50000", "batch_size = 400").replace("epoch_num = 20", "epoch_num = 3")
@@ -54,8 +65,7 @@ def test_train_then_predict_cli(tmp_path, loss_type):
 def test_validation_and_tolerance_stop_early(tmp_path):
     """validation_files + tolerance: the loop prints the validation loss every save_steps and stops under it
     (run_tffm.py:69-77 of the reference)"""
-    for f in ("train_0", "train_1", "weight_0", "weight_1", "test_0"):
-        shutil.copy(os.path.join(ROOT, "data", f), tmp_path / f)
+    _small_files(tmp_path)
     cfg = open(os.path.join(ROOT, "sample.cfg")).read()
     cfg = cfg.replace("./data/", str(tmp_path) + "/").replace("./log", str(tmp_path / "log"))
     cfg = cfg.replace("batch_size = 50000", "batch_size = 400").replace("epoch_num = 20", "epoch_num = 50")
@@ -79,8 +89,7 @@ def test_train_under_torchrun_then_predict_on_one_gpu(tmp_path):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    for f in ("train_0", "train_1", "weight_0", "weight_1", "test_0"):
-        shutil.copy(os.path.join(ROOT, "data", f), tmp_path / f)
+    _small_files(tmp_path)
     cfg = open(os.path.join(ROOT, "sample.cfg")).read()
     cfg = cfg.replace("./data/", str(tmp_path) + "/").replace("./log", str(tmp_path / "log"))
     cfg = cfg.replace("batch_size = 50000", "batch_size = 400").replace("epoch_num = 20", "epoch_num = 3")
