@@ -63,7 +63,7 @@ def cfg4(args):
     gen_s = time.time() - t
     m = Model(vocabulary_size=vocab, factor_num=k, batch_size=b, hash_feature_id=False, loss_type="mse",
               learning_rate=0.01, adagrad_init_accumulator=0.1, factor_lambda=1e-5, bias_lambda=1e-5).build(
-        dev, seed=0, max_nnz_per_line=512)
+        dev, seed=0, max_nnz_per_line=512, path=args.path)
     it = [0]
 
     def step():
@@ -77,7 +77,7 @@ def cfg4(args):
     text_bytes = int(batches[0][0].offsets[-1])
     print(json.dumps({"config": "cfg4: mse, per-example weights, 1-512 nnz/row (mean 256.5), K=32, V=2^24, B=65536, 1xB200",
                       "metric": "fm_train_examples_per_sec", "value": b / (ms * 1e-3), "ms_per_step": ms,
-                      "nnz_per_step": int(st[1]), "text_mb": round(text_bytes / 1e6, 1), "path": "claim",
+                      "nnz_per_step": int(st[1]), "text_mb": round(text_bytes / 1e6, 1), "path": args.path,
                       "loss": float(st[6:8].view(torch.float32)[0]), "data_gen_s": round(gen_s, 1)}))
 
 
@@ -165,5 +165,6 @@ if __name__ == "__main__":
     ap.add_argument("which", choices=["cfg4", "cfg5"])
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--path", default="claim", choices=["claim", "sorted"], help="cfg4: training path")
     a = ap.parse_args()
     {"cfg4": cfg4, "cfg5": cfg5}[a.which](a)

@@ -826,3 +826,31 @@ def test_full_size_step_properties():
     assert changed.numel() > 0.9 * u                                   # (rows whose x == 0 move by less than an ulp)
     loss = float(st[6:8].view(torch.float32)[0])
     assert 0.6 < loss < 0.8                                            # ~log 2 for a fresh model
+
+
+def test_sorted_path_at_full_size_is_reproducible():
+    """cfg2 at BASELINE size through the sorted path: the counts the sort and the update report, the same rows
+    touched as the claim path, and -- what the stable sort and the atomic-free segment reduce are for -- the same
+    bits in the table when the same two steps are run again from the same start (zipf ids: hot rows, cut runs)"""
+    kw = dict(vocabulary_size=1 << 24, factor_num=16, batch_size=65536, hash_feature_id=True, loss_type="logistic",
+              factor_lambda=1e-5, bias_lambda=1e-5)
+    batches = []
+    for seed, dist in ((7, "uniform"), (8, "zipf")):
+        text, off, nnz = bench_data.criteo_batch(65536, seed, dist)
+        batches.append((fm_ops.PackedLines(torch.from_numpy(bench_data.pad16(text)), torch.from_numpy(off)).to(DEV, False), nnz))
+    tables = []
+    for run in range(2):
+        m = Model(**kw).build(DEV, seed=3, max_nnz_per_line=39, path="sorted")
+        for packed, nnz in batches:
+            b = m.train_step_async(packed)
+            st = b["status"].cpu()
+            assert int(st[0]) == -1 and int(st[1]) == nnz and int(st[3]) == nnz
+            assert int(st[4]) == torch.unique(b["ids"][:nnz]).numel()          # tf.unique's U, counted by the update
+        tables.append((m.table.clone(), m.accum.clone()))
+        del m
+    assert torch.equal(tables[0][0], tables[1][0]) and torch.equal(tables[0][1], tables[1][1])
+    c = Model(**kw).build(DEV, seed=3, max_nnz_per_line=39, path="claim")
+    for packed, _ in batches:
+        c.train_step_async(packed)
+    torch.testing.assert_close(tables[0][0][:, :17], c.table[:, :17], rtol=1e-5, atol=1e-7)
+    assert torch.equal((tables[0][1][:, :17] != 0.1).any(1), (c.accum[:, :17] != 0.1).any(1))   # the same rows moved

@@ -111,3 +111,32 @@ def test_numa_binding_reports_instead_of_failing():
     msg = fm_data.bind_host_to_gpu(0)          # no GPU here: nothing is bound, the reason comes back
     assert isinstance(msg, str) and msg
     assert os.sched_getaffinity(0) == before or "bound to" in msg
+
+
+def test_nnz_bound_comes_from_the_batch_not_from_the_buffer_behind_it():
+    """a batch selected from a resident file shares the file's text: its buffers are sized by its own lines"""
+    import torch
+    from fast_tffm_b200 import fm_ops
+    whole = fm_ops.pack_lines(["1 2:3 4:5"] * 1000 + ["0 " + " ".join("%d:1" % i for i in range(50))])
+    assert whole.nnz_bound() == whole.text.numel() // 2 + 1
+    batch = whole.select(torch.arange(10))
+    assert whole.max_line_bytes == len("0 " + " ".join("%d:1" % i for i in range(50))) + 1
+    assert batch.nnz_bound() == 10 * (whole.max_line_bytes // 2) + 1 < whole.nnz_bound()
+    assert batch.to("cpu").max_line_bytes == whole.max_line_bytes
+
+
+def test_optimizer_key_is_an_extension_with_a_safe_default(tmp_path):
+    import os
+    from fast_tffm_b200.fm_model import Model
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cfg = open(os.path.join(root, "sample.cfg")).read()
+    (tmp_path / "a.cfg").write_text(cfg)
+    assert Model(str(tmp_path / "a.cfg")).optimizer == "adagrad"          # the reference's only optimizer
+    (tmp_path / "b.cfg").write_text(cfg.replace("loss_type = mse", "loss_type = mse\noptimizer = sgd"))
+    assert Model(str(tmp_path / "b.cfg")).optimizer == "sgd"
+    (tmp_path / "c.cfg").write_text(cfg.replace("loss_type = mse", "loss_type = mse\noptimizer = adam"))
+    with pytest.raises(ValueError, match="optimizer"):
+        Model(str(tmp_path / "c.cfg"))
+    (tmp_path / "d.cfg").write_text(cfg.replace("adagrad.initial_accumulator = 0.1", "adagrad.initial_accumulator = 0"))
+    with pytest.raises(ValueError, match="initial_accumulator_value must be positive"):
+        Model(str(tmp_path / "d.cfg"))
