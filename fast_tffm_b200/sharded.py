@@ -305,6 +305,9 @@ class PeerShardedModel:
         self.world = dist.get_world_size(self.group)
         self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
         self.max_nnz_per_line = max_nnz_per_line
+        if getattr(model, "optimizer", "adagrad") != "adagrad":
+            raise ValueError("the sharded step is Adagrad (as the reference); optimizer = %r runs on one GPU, sorted path"
+                             % model.optimizer)
         self.lib = load()
         self.global_step = 0
         self._slots = {}
