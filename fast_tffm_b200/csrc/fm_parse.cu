@@ -293,9 +293,10 @@ struct Window {   // 32 bytes of text from the token start; bytes at and past th
 __device__ __forceinline__ Window load_window(const uint8_t* __restrict__ text, int64_t q, int64_t limit, int avail) {
   const int64_t a = q & ~(int64_t)7;
   uint64_t v[5];
+  const bool inside = a + 40 <= limit;        // nearly always: no per-word bound checks
 #pragma unroll
   for (int k = 0; k < 5; ++k)
-    v[k] = (a + 8 * k + 8 <= limit) ? __ldg(reinterpret_cast<const uint64_t*>(text + a + 8 * k)) : 0ull;
+    v[k] = (inside || a + 8 * k + 8 <= limit) ? __ldg(reinterpret_cast<const uint64_t*>(text + a + 8 * k)) : 0ull;
   const int sh = ((int)q & 7) * 8;
   Window w;
   if (sh) {
@@ -304,19 +305,27 @@ __device__ __forceinline__ Window load_window(const uint8_t* __restrict__ text, 
   } else {
     w.w0 = v[0]; w.w1 = v[1]; w.w2 = v[2]; w.w3 = v[3];
   }
-  w.w0 &= keep_low_bytes(avail); w.w1 &= keep_low_bytes(avail - 8);
-  w.w2 &= keep_low_bytes(avail - 16); w.w3 &= keep_low_bytes(avail - 24);
+  if (avail < 32) {                           // only a line's last tokens: bytes past the line end read as 0
+    w.w0 &= keep_low_bytes(avail); w.w1 &= keep_low_bytes(avail - 8);
+    w.w2 &= keep_low_bytes(avail - 16); w.w3 &= keep_low_bytes(avail - 24);
+  }
   return w;
 }
 // index of the first byte that is NUL, ' ' or (with_colon) ':' in the 32-byte window; 32 if none
-__device__ __forceinline__ int find_end(const Window& w, bool with_colon) {
+// *is_colon: the byte found is ':' (only meaningful with_colon and when the result is < 32)
+__device__ __forceinline__ int find_end(const Window& w, bool with_colon, bool* is_colon) {
   const uint64_t sp = 0x2020202020202020ull, co = 0x3a3a3a3a3a3a3a3aull;
+  *is_colon = false;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const uint64_t x = w.word(j);
     uint64_t f = zero_bytes(x) | zero_bytes(x ^ sp);
-    if (with_colon) f |= zero_bytes(x ^ co);
-    if (f) return 8 * j + ((__ffsll((long long)f) >> 3) - 1);
+    const uint64_t fc = with_colon ? zero_bytes(x ^ co) : 0ull;
+    f |= fc;
+    if (f) {
+      *is_colon = ((f & (0ull - f)) & fc) != 0;      // the lowest flag is a colon's
+      return 8 * j + ((__ffsll((long long)f) >> 3) - 1);
+    }
   }
   return 32;
 }
@@ -338,7 +347,8 @@ __device__ __forceinline__ int parse_token_regs(const uint8_t* __restrict__ text
   const Window w = load_window(text, q, limit, avail);
   int vstart = 0;
   if (!is_label) {
-    const int n = find_end(w, true);
+    bool colon;
+    const int n = find_end(w, true, &colon);
     if (n >= 32) return kTokFallback;
     if (n == 0) return kTokBad;  // empty token: the sequential path knows what the reference does with it
     int64_t id;
@@ -346,9 +356,10 @@ __device__ __forceinline__ int parse_token_regs(const uint8_t* __restrict__ text
       const uint64_t m = 0xc6a4a7935bd1e995ull;
       uint64_t h = 0xDECAFCAFFEull ^ ((uint64_t)n * m);
 #pragma unroll
-      for (int j = 0; j < 3; ++j)
+      for (int j = 0; j < 4; ++j) {             // n < 32: words 0..3 with static indices, the tail inside the loop
         if (8 * (j + 1) <= n) { uint64_t k = w.word(j); k *= m; k ^= k >> 47; k *= m; h ^= k; h *= m; }
-      if (n & 7) { h ^= w.word(n >> 3) & keep_low_bytes(n & 7); h *= m; }
+        else if (8 * j < n) { h ^= w.word(j) & ((1ull << (8 * (n - 8 * j))) - 1ull); h *= m; }
+      }
       h ^= h >> 47; h *= m; h ^= h >> 47;
       id = (int64_t)((vocab & (vocab - 1)) == 0 ? (h & (uint64_t)(vocab - 1)) : (h % (uint64_t)vocab));
     } else {
@@ -363,7 +374,7 @@ __device__ __forceinline__ int parse_token_regs(const uint8_t* __restrict__ text
       id = (int64_t)acc;
     }
     *id_out = id;
-    if (w.byte(n) != ':') { *bits_out = 0x3f800000u; return kTokOk; }  // ' ' or line end: value 1
+    if (!colon) { *bits_out = 0x3f800000u; return kTokOk; }  // ' ' or line end: value 1
     vstart = n + 1;
   }
   // the value (or label): must end at a space or at the line end, inside the window
