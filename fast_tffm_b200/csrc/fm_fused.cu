@@ -837,7 +837,10 @@ FM_EXPORT int fm_fused_adagrad_claim(float* table, float* accum, int64_t table_l
   }
   const int64_t rows_per_block = 8 * (32 / gs);
   int64_t blocks = (n + rows_per_block - 1) / rows_per_block;
-  if (blocks > 148 * 16) blocks = 148 * 16;
+  // grid: many short blocks, not a persistent one (profiles/r2_sweep_claim_blocks.txt: 148 x 6 blocks 0.31 ms, 148 x 16
+  // 0.256, 148 x 32 the same alone and 2 % better with the parse of the next batch running beside it)
+  static const int bpsm = fm_env_int("FM_CLAIM_BLOCKS_PER_SM", 32);
+  if (blocks > 148 * bpsm) blocks = 148 * bpsm;
 #define CALL(T)                                                                                           \
   fused_adagrad_claim_kernel<T><<<(unsigned)blocks, 256, 0, stream>>>(                                    \
       table, accum, table_ld, rows, n, n_dev, (int)factor_num, gtab, gtab_ld, learning_rate,              \
