@@ -20,6 +20,11 @@ from . import _lib
 from .fm_ops import FmParseError, PackedLines
 
 
+def check_sync_word(f):
+    from .sharded import check_sync_word as impl      # sharded imports torch.distributed: only when it is used
+    impl(f)
+
+
 class StepResult:
     """Outcome of one pipelined step.  loss() blocks until that step has finished on the device and
     raises FmParseError if its batch did not parse (the step was then void, as in train_step)."""
@@ -117,6 +122,7 @@ class HostBatchPipeline:
 
             def decode(rec=self._rec_status[r], scal=self._rec_scal[r]):
                 f = int(rec[0])
+                check_sync_word(f)
                 if f >= 0:
                     bad_rank, first = f >> 48, f & ((1 << 48) - 1)
                     line = host.line(first >> 3) if bad_rank == rank else "<rank %d, line %d>" % (bad_rank, first >> 3)

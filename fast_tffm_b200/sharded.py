@@ -158,6 +158,14 @@ def _exchange(send, send_counts, recv_counts, group):
     return out
 
 
+def check_sync_word(f):
+    """fm_peer_sync gives up on a rank that does not arrive within tens of seconds (word >= 2^62): that is a dead or
+    wedged process, not a parse error -- say so"""
+    if f >= (1 << 62):
+        raise RuntimeError("sharded step: rank %d never reached the barrier (fm_peer_sync timed out); the step was void"
+                           % ((f >> 48) & 0xFF))
+
+
 class ShardedModel:
     """Model (same config object) with the table row-partitioned over the ranks of `group`."""
 
@@ -545,6 +553,7 @@ class PeerShardedModel:
     def train_step(self, lines, weights=None, global_batch=None):
         out, flag = self.train_step_async(lines, weights, global_batch)
         f = int(flag.item())
+        check_sync_word(f)
         if f >= 0:
             rank, first = f >> 48, f & ((1 << 48) - 1)
             line = self.last["packed"].line(first >> 3) if rank == self.rank else "<rank %d, line %d>" % (rank, first >> 3)
