@@ -233,7 +233,8 @@ def workload_config(args, n_gpus, batch):
             "l2_policy": "inputs larger than L2: %d distinct text batches (~37 MB each) + random rows of a "
                          "1.3 GB table / accumulator per step" % args.batches,
             "parallelism": "single GPU" if n_gpus == 1 else "vocab-sharded x%d (id %% G), %s" % (
-                n_gpus, "NVLink peer loads + atomics" if args.shard_mode == "peer" else "NCCL all-to-all")}
+                n_gpus, {"peer": "NVLink peer loads + atomics", "merge": "NVLink peer loads + sorted records merged by the "
+                         "owners", "exchange": "NCCL all-to-all"}[args.shard_mode])}
 
 
 def run_ours(args):
@@ -472,8 +473,9 @@ def main():
                     help="default: pair ([w | h] per id) for the sorted path, interleaved ([w | h | g]) for the others")
     ap.add_argument("--no-parse-ahead", action="store_true",
                     help="parse each batch inline instead of on a side stream under the previous batch's kernels")
-    ap.add_argument("--shard-mode", default="peer", choices=["peer", "exchange"],
+    ap.add_argument("--shard-mode", default="peer", choices=["peer", "merge", "exchange"],
                     help="N > 1: peer = rows and gradients move by NVLink loads / atomics inside the kernels; "
+                         "merge = rows by NVLink loads, gradients as sorted records merged by the owners; "
                          "exchange = NCCL all-to-all of ids, rows and accumulator rows")
     ap.add_argument("--parse-blocks", type=int, default=None,
                     help="experiment: grid cap of the run-ahead parse (Model.BACKGROUND_PARSE_BLOCKS; 0 = full grid)")

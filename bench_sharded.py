@@ -84,8 +84,13 @@ def run_sharded(args, cfg, workload_config):
                   loss_type=cfg["loss_type"], learning_rate=cfg["learning_rate"],
                   adagrad_init_accumulator=cfg["init_acc"], factor_lambda=cfg["factor_lambda"],
                   bias_lambda=cfg["bias_lambda"])
-    peer = args.shard_mode == "peer"
-    cls = PeerShardedModel if peer else ShardedModel
+    peer = args.shard_mode in ("peer", "merge")
+    if peer:
+        def cls(mdl, device=None, max_nnz_per_line=None):
+            return PeerShardedModel(mdl, device=device, max_nnz_per_line=max_nnz_per_line,
+                                    exchange="records" if args.shard_mode == "merge" else "atomics")
+    else:
+        cls = ShardedModel
     parity = parity_check(cls, cfg, world, rank, dev)
     m = cls(model, device=dev, max_nnz_per_line=cfg["nnz_per_line"]).build(seed=0)
     host, devb = [], []
@@ -194,7 +199,12 @@ def run_sharded(args, cfg, workload_config):
         st = m.last["status"].cpu()
         nnz_local = int(st[1])
         remote = nnz_local * (world - 1) / world
-        stats = torch.tensor([nnz_local, int(m.n_rows.item()), remote], dtype=torch.float64, device=dev)
+        if args.shard_mode == "merge":      # no touched-row list in this mode: this rank's own distinct ids
+            bufs = next(v for v in m._slots.values() if v["status"] is m.last["status"])
+            n_rows = int(torch.unique(bufs["ids"][:nnz_local]).numel())
+        else:
+            n_rows = int(m.n_rows.item())
+        stats = torch.tensor([nnz_local, n_rows, remote], dtype=torch.float64, device=dev)
     else:
         stats = torch.tensor([m.last["nnz"], m.last["n_unique"], m.last["sent_rows"]], dtype=torch.float64, device=dev)
     dist.all_reduce(stats)
@@ -209,6 +219,8 @@ def run_sharded(args, cfg, workload_config):
         # per rank per step over NVLink: exchange mode moves id + row + accumulator row per remote distinct id
         # each way; peer mode reads a row and pushes an accumulator row per remote occurrence
         xbytes = sent * (8 + 4 * ld + 4 * gld)
+        if args.shard_mode == "merge":      # a row pulled per remote occurrence; a key word + (at most) a record pushed
+            xbytes = sent * (4 * ld + 4 + 4 * gld)
         line = {
             "metric": METRIC, "value": args.steps * b * world / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
@@ -229,7 +241,7 @@ def run_sharded(args, cfg, workload_config):
             "e2e": {"value": args.steps * b * world / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": int(host[0].text.numel() + host[0].offsets.numel() * 8) * world,
                     "d2h_bytes_per_step": 16 * world, "ms_per_step": e2e_ms / args.steps},
-            "gpu_launches": (9 if peer else 20) * args.steps, "shard_mode": args.shard_mode, "parse_ahead": ahead_on,
+            "gpu_launches": ({"peer": 9, "merge": 19, "exchange": 20}[args.shard_mode]) * args.steps, "shard_mode": args.shard_mode, "parse_ahead": ahead_on,
             "stage_ms_rank0": {k_: round(v, 4) for k_, v in stage_ms.items()},
             "host_affinity_rank0": affinity, "clocks": clocks, "final_loss": loss, "nnz_per_rank": nnz, "unique_per_rank": nuniq,
         }

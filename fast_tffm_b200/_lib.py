@@ -55,6 +55,14 @@ _SIGNATURES = {
                                         _i32, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "fm_peer_sync_bytes": (_sz, []),
     "fm_peer_sync": (C.c_int, [_vp, _i64, _i64, C.c_uint64, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "fm_merge_tile_rows": (_i64, [_i64]),
+    "fm_merge_inbox_bytes": (_sz, [_i64, _i64, _i64, _i64]),
+    "fm_merge_push_workspace": (_sz, [_i64]),
+    "fm_peer_sorted_score": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _i64, _f32, _f32, _i32, _i64, _vp,
+                                       _vp, _vp, _vp, _i64, _vp, _vp, _sz, _vp]),
+    "fm_peer_push_records": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _i64, _i64, _i64, _i64, _i64, _i64, _vp, _i64, _vp, _vp,
+                                       _sz, _vp]),
+    "fm_peer_merge_update": (C.c_int, [_vp, _vp, _i64, _i64, _vp, _i64, _i64, _i64, _f32, _f32, _f32, _f32, _vp, _vp]),
     "fm_peer_touched_workspace": (_sz, [_i64]),
     "fm_peer_touched_rows": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _vp, _sz, _vp]),
     "fm_shard_bucket_workspace": (_sz, [_i64, _i64]),

@@ -921,6 +921,55 @@ FM_EXPORT int fm_peer_score_scatter(const int64_t* feature_ids, const float* fea
   return FM_OK;
 }
 
+// the scorer of the record exchange (fm_merge.cu): rows pulled from their owners like fm_peer_score_scatter, nothing
+// pushed; per example the record [pg, s_1 .. s_K] stays in local memory for fm_peer_push_records
+FM_EXPORT int fm_peer_sorted_score(const int64_t* feature_ids, const float* feature_vals, const int32_t* feature_poses,
+                                   const float* labels, const float* weights, int64_t batch, int64_t factor_num,
+                                   int64_t n_ranks, const void* const* table_bases, int64_t table_ld,
+                                   float factor_lambda, float bias_lambda, int loss_kind, int64_t loss_batch,
+                                   float* pred_score, float* loss, float* reg_score, float* records, int64_t record_ld,
+                                   const uint64_t* guard, void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  FM_REQUIRE(batch >= 0 && factor_num >= 0, "fm_peer_sorted_score: bad shape");
+  if (n_ranks < 1 || n_ranks > kMaxPeers) return fm_fail(FM_E_LIMIT, "fm_peer_sorted_score: 1..%d ranks", kMaxPeers);
+  FM_REQUIRE(table_ld >= factor_num + 1 && table_ld % 4 == 0, "fm_peer_sorted_score: table_ld must be a multiple of 4 and >= K+1");
+  FM_REQUIRE(record_ld >= fm_sorted_record_ld(factor_num) && record_ld % 4 == 0, "fm_peer_sorted_score: bad record_ld");
+  FM_REQUIRE(loss_kind == FM_LOSS_LOGISTIC || loss_kind == FM_LOSS_MSE, "fm_peer_sorted_score: unknown loss kind");
+  FM_REQUIRE(table_bases && loss && reg_score && workspace, "fm_peer_sorted_score: null pointer");
+  FM_REQUIRE(batch == 0 || (feature_ids && feature_vals && feature_poses && pred_score && labels && records),
+             "fm_peer_sorted_score: null pointer");
+  FM_REQUIRE(((uintptr_t)records & 15) == 0, "fm_peer_sorted_score: records must be 16-byte aligned");
+  if (workspace_bytes < fm_fused_workspace(batch))
+    return fm_fail(FM_E_WORKSPACE, "fm_peer_sorted_score: workspace %zu < %zu", workspace_bytes, fm_fused_workspace(batch));
+  PeerPtrs peers;
+  peers.n = (int)n_ranks;
+  for (int r = 0; r < kMaxPeers; ++r) {
+    peers.table[r] = r < n_ranks ? static_cast<const float*>(table_bases[r]) : nullptr;
+    peers.gtab[r] = nullptr;
+    peers.touched[r] = nullptr;
+    FM_REQUIRE(r >= n_ranks || (peers.table[r] && ((uintptr_t)peers.table[r] & 15) == 0), "fm_peer_sorted_score: bad table base");
+  }
+  const int64_t chunks = (factor_num + 4) / 4;
+  const int gs = chunks <= 32 ? (int)chunks : 32;
+  const int t = (int)((chunks + gs - 1) / gs);
+  if (t > 3) return fm_fail(FM_E_LIMIT, "fm_peer_sorted_score: factor_num %lld too wide", (long long)factor_num);
+  const int blocks = fused_blocks(batch);
+  float* partials = reinterpret_cast<float*>(workspace);
+  const int64_t denom = loss_batch > 0 ? loss_batch : batch;
+  const float inv_batch = denom > 0 ? 1.0f / (float)denom : 0.f;
+#define CALL(T)                                                                                                     \
+  fused_score_scatter_kernel<T, true><<<blocks, kWarps * 32, 0, stream>>>(                                          \
+      feature_ids, nullptr, feature_vals, feature_poses, labels, weights, batch, (int)factor_num, peers.table[0],   \
+      table_ld, factor_lambda, bias_lambda, loss_kind, inv_batch, pred_score, nullptr, 0, partials,                 \
+      reinterpret_cast<const unsigned long long*>(guard), peers, gs, records, record_ld)
+  if (t == 1) { CALL(1); } else if (t == 2) { CALL(2); } else { CALL(3); }
+#undef CALL
+  FM_LAUNCH_CHECK();
+  reduce2_kernel<<<1, 256, 0, stream>>>(partials, blocks, inv_batch, loss, reg_score);
+  FM_LAUNCH_CHECK();
+  return FM_OK;
+}
+
 FM_EXPORT size_t fm_peer_touched_workspace(int64_t shard_rows) {
   return scan_scratch_bytes((shard_rows + 31) / 32, 8);
 }

@@ -306,7 +306,16 @@ class PeerShardedModel:
     of this path; the NCCL all-to-all form (ShardedModel) is the one that runs under gloo.
     """
 
-    def __init__(self, model: Model, group=None, device=None, max_nnz_per_line=None):
+    def __init__(self, model: Model, group=None, device=None, max_nnz_per_line=None, exchange="atomics"):
+        """exchange: how the gradient sums reach the rows' owners.  "atomics": system-scope vector atomics from inside
+        the scorer (fm_peer_score_scatter).  "records": the occurrences are sorted by (owner, row) ahead of the step,
+        one record per run is written into the owner's inbox and the owners merge their G sorted inboxes
+        (fm_peer_sorted_score / fm_peer_push_records / fm_peer_merge_update): 236 instead of 328 bytes on NVLink per
+        remote occurrence."""
+        if exchange not in ("atomics", "records"):
+            raise ValueError("exchange must be atomics or records")
+        self.exchange = exchange
+        self._inbox = None
         self.cfg = model
         self.group = group if group is not None else dist.group.WORLD
         self.rank = dist.get_rank(self.group)
@@ -476,9 +485,11 @@ class PeerShardedModel:
             side.wait_event(after)
         with torch.cuda.stream(side):
             packed, b = self._parse(lines, slot=self._ahead_slot, max_blocks=Model.BACKGROUND_PARSE_BLOCKS)
+            if self.exchange == "records":
+                self._sort(b, packed.n_lines, max_blocks=Model.BACKGROUND_PARSE_BLOCKS)
             done = torch.cuda.Event()
             done.record(side)
-        return dict(b=b, packed=packed, done=done)
+        return dict(b=b, packed=packed, done=done, sorted=self.exchange == "records")
 
     def _parse(self, lines, slot=0, max_blocks=0):
         lib, st, cfg = self.lib, stream(), self.cfg
@@ -495,6 +506,69 @@ class PeerShardedModel:
                                 ptr(b["status"]), ptr(b["ws_parse"]), b["ws_parse"].numel(), max_blocks, st),
               "fm_parse_fill")
         return packed, b
+
+    def _sort(self, b, n_lines, max_blocks=0):
+        """this rank's occurrences sorted by (owner, row): fm_sort_by_row with n_ranks = world; counts in status[3:5]"""
+        lib, dev, k = self.lib, self.device, self.cfg.factor_num
+        if b.get("skeys") is None:
+            cap = b["cap"]
+            b["skeys"] = torch.empty(cap, dtype=torch.int32, device=dev)
+            b["spairs"] = torch.empty(cap, 2, dtype=torch.int32, device=dev)
+            b["ws_sort"] = _lib.workspace(lib.fm_sort_workspace(cap), dev)
+            b["rec_ld"] = int(lib.fm_sorted_record_ld(k))
+            b["rec"] = torch.empty(b["lines"], b["rec_ld"], dtype=torch.float32, device=dev)
+            b["ws_push"] = _lib.workspace(lib.fm_merge_push_workspace(self.world), dev)
+        check(lib.fm_sort_by_row(ptr(b["ids"]), ptr(b["vals"]), ptr(b["poses"]), n_lines, b["cap"], _at(b["status"], 1),
+                                 self.cfg.vocabulary_size, self.world, ptr(b["skeys"]), ptr(b["spairs"]),
+                                 _at(b["status"], 3), ptr(b["status"]), ptr(b["ws_sort"]), b["ws_sort"].numel(),
+                                 max_blocks, stream()), "fm_sort_by_row")
+
+    def _ensure_inbox(self, cap):
+        """the peer-mapped inboxes of the record exchange, allocated by all ranks together at the first training step
+        (capacity: the largest per-rank id buffer + 25 %); a later batch that does not fit voids its step"""
+        if self._inbox is not None:
+            return
+        import torch.distributed._symmetric_memory as symm_mem
+        need = torch.tensor([int(cap)], dtype=torch.int64, device=self.device)
+        dist.all_reduce(need, op=dist.ReduceOp.MAX, group=self.group)
+        self._inbox_cap = int(need.item()) * 5 // 4 + 64
+        nbytes = int(self.lib.fm_merge_inbox_bytes(self._inbox_cap, self.table.shape[0], self.cfg.factor_num, self.world))
+        self._inbox = symm_mem.empty(nbytes // 4, dtype=torch.float32, device=self.device)
+        hdl = symm_mem.rendezvous(self._inbox, self.group)
+        self._inbox.zero_()
+        self._inbox_hdl = hdl
+        self._inbox_bases = (ctypes.c_void_p * self.world)(*[int(p) for p in hdl.buffer_ptrs])
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
+
+    def _train_records(self, packed, b, weights, global_batch, mark, presorted):
+        """the step with the record exchange (see __init__)"""
+        lib, st, cfg, k, g = self.lib, stream(), self.cfg, self.cfg.factor_num, self.world
+        if not presorted:
+            self._sort(b, packed.n_lines)
+        self._ensure_inbox(b["cap"])
+        check(lib.fm_peer_sorted_score(
+            ptr(b["ids"]), ptr(b["vals"]), ptr(b["poses"]), ptr(b["labels"]), ptr(weights), packed.n_lines, k, g,
+            self._table_bases, self.ld, cfg.factor_lambda, cfg.bias_lambda, _lib.LOSS_KIND[cfg.loss_type], global_batch,
+            ptr(b["pred"]), ptr(b["scal"]), _at(b["scal"], 1), ptr(b["rec"]), b["rec_ld"], ptr(b["status"]),
+            ptr(b["ws_fused"]), b["ws_fused"].numel(), st), "fm_peer_sorted_score")
+        mark("score")
+        check(lib.fm_peer_push_records(
+            ptr(b["skeys"]), ptr(b["spairs"]), _at(b["status"], 3), b["cap"], ptr(b["rec"]), b["rec_ld"], k, self.rank, g,
+            cfg.vocabulary_size, self.table.shape[0], self._inbox_bases, self._inbox_cap, ptr(b["status"]),
+            ptr(b["ws_push"]), b["ws_push"].numel(), st), "fm_peer_push_records")
+        mark("push")
+        flag = torch.empty(1, dtype=torch.int64, device=self.device)
+        self._sync(ptr(b["status"]), None, None, ptr(flag), None)      # every inbox is complete; did any rank fail?
+        mark("barrier")
+        check(lib.fm_peer_merge_update(ptr(self.table), ptr(self.accum), self.ld, self.table.shape[0], ptr(self._inbox),
+                                       self._inbox_cap, k, g, cfg.learning_rate, cfg.factor_lambda, cfg.bias_lambda,
+                                       1.0 / cfg.batch_size, ptr(flag), st), "fm_peer_merge_update")
+        mark("update")
+        out = torch.empty(2, dtype=torch.float32, device=self.device)
+        self._sync(None, ptr(b["scal"]), _at(b["scal"], 1), None, ptr(out))
+        mark("allreduce_loss")
+        return out, flag
 
     def train_step_async(self, lines, weights=None, global_batch=None, mark=lambda name: None, parsed=None):
         """Returns (scalars, flag): scalars = device f32 [global mean loss, global reg_score];
@@ -514,6 +588,15 @@ class PeerShardedModel:
             weights = torch.as_tensor(weights, dtype=torch.float32)
         if weights is not None:
             weights = weights.to(self.device)
+        if self.exchange == "records":
+            out, flag = self._train_records(packed, b, weights, global_batch, mark,
+                                            parsed is not None and parsed.get("sorted", False))
+            if parsed is not None:
+                b["free"] = torch.cuda.Event()
+                b["free"].record(torch.cuda.current_stream(self.device))
+            self.global_step += 1
+            self.last = dict(pred=b["pred"][:packed.n_lines], packed=packed, status=b["status"])
+            return out, flag
         check(lib.fm_peer_score_scatter(
             ptr(b["ids"]), ptr(b["vals"]), ptr(b["poses"]), ptr(b["labels"]), ptr(weights), packed.n_lines, k, g,
             self._table_bases, self.ld, self._gtab_bases, self.gld, self._touched_bases, cfg.factor_lambda,

@@ -354,6 +354,42 @@ int fm_peer_sync(void* const* sync_bases, int64_t rank, int64_t n_ranks, uint64_
                  const int64_t* word_in, const float* a_in, const float* b_in, int64_t* word_out,
                  float* sums_out, void* stream);
 size_t fm_peer_touched_workspace(int64_t shard_rows);
+
+/* ---- D1, record exchange: the same sharded step with the gradients sent as sorted records, not as remote atomics ----
+ * (fm_peer_score_scatter puts 192 bytes on NVLink per remote occurrence for 84 bytes of gradient sums.)  A rank sorts
+ * its occurrences with fm_sort_by_row(n_ranks = G) -- grouped by owner, rows ascending --, scores with
+ * fm_peer_sorted_score (rows pulled from their owners; records [pg, s_1..s_K] per example stay local), then
+ * fm_peer_push_records writes, into every owner's inbox (peer-mapped; inbox_bases[r] = rank r's inbox as mapped here):
+ *   - per sorted position one key word: the shard row | 2^31 where a piece (a run of equal rows, cut at multiples of
+ *     FM_SORT_CHUNK) starts;
+ *   - per piece one record {C, B_1..B_K, D, cnt} (the columns of fm_fused_score_scatter's accumulator rows), at the
+ *     piece's position;
+ *   - per tile of fm_merge_tile_rows(K) shard rows the position where its rows begin in this sender's segment.
+ * An inbox holds fm_merge_inbox_bytes(inbox_capacity, shard_rows, K, G) bytes (256-byte aligned), one part per sender,
+ * each for up to inbox_capacity positions; a segment that does not fit voids the step (status->first_error gets kind
+ * FM_PARSE_E_CAPACITY).  All ranks must have finished pushing (fm_peer_sync) before any owner calls
+ * fm_peer_merge_update: per tile of rows a block adds the G senders' sub-lists to an accumulator tile in shared
+ * memory and applies TF1 SparseApplyAdagrad to the rows that received something.  flag (device int64, fm_peer_sync's
+ * word_out): the call is a no-op when *flag >= 0.  A second fm_peer_sync separates it from the next step's reads.
+ * No accumulator table, no bitmap, no global float atomics; about 236 instead of 328 wire bytes per remote occurrence. */
+int64_t fm_merge_tile_rows(int64_t factor_num);
+size_t fm_merge_inbox_bytes(int64_t capacity, int64_t shard_rows, int64_t factor_num, int64_t n_ranks);
+size_t fm_merge_push_workspace(int64_t n_ranks);
+int fm_peer_sorted_score(const int64_t* feature_ids, const float* feature_vals, const int32_t* feature_poses,
+                         const float* labels, const float* weights, int64_t batch, int64_t factor_num,
+                         int64_t n_ranks, const void* const* table_bases, int64_t table_ld,
+                         float factor_lambda, float bias_lambda, int loss_kind, int64_t loss_batch,
+                         float* pred_score, float* loss, float* reg_score, float* records, int64_t record_ld,
+                         const uint64_t* guard, void* workspace, size_t workspace_bytes, void* stream);
+int fm_peer_push_records(const uint32_t* sorted_keys, const uint32_t* sorted_pairs, const int64_t* counts,
+                         int64_t capacity, const float* records, int64_t record_ld, int64_t factor_num,
+                         int64_t rank, int64_t n_ranks, int64_t vocab_size, int64_t shard_rows,
+                         void* const* inbox_bases, int64_t inbox_capacity, fm_parse_status* status,
+                         void* workspace, size_t workspace_bytes, void* stream);
+int fm_peer_merge_update(float* table, float* accum, int64_t table_ld, int64_t shard_rows, const void* inbox,
+                         int64_t inbox_capacity, int64_t factor_num, int64_t n_ranks, float learning_rate,
+                         float factor_lambda, float bias_lambda, float reg_grad, const int64_t* flag,
+                         void* stream);
 int fm_peer_touched_rows(uint32_t* touched, int64_t shard_rows, int64_t* rows, int64_t capacity,
                          int64_t* n_rows, void* workspace, size_t workspace_bytes, void* stream);
 

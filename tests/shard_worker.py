@@ -17,8 +17,9 @@ def run(rank, world, port, backend, lines, weights, cfg_kw, init, steps, out_dir
     dist.init_process_group(backend, rank=rank, world_size=world)
     from fast_tffm_b200.fm_model import Model
     from fast_tffm_b200.sharded import PeerShardedModel, ShardedModel
-    if mode == "peer":
-        m = PeerShardedModel(Model(**cfg_kw), device=device).build(init_table=init)
+    if mode in ("peer", "merge"):
+        m = PeerShardedModel(Model(**cfg_kw), device=device,
+                             exchange="records" if mode == "merge" else "atomics").build(init_table=init)
     else:
         m = ShardedModel(Model(**cfg_kw), kernels=kernels, device=device).build(init_table=init)
     bs = cfg_kw["batch_size"]
@@ -47,8 +48,11 @@ def run_bad_line(rank, world, port, lines, cfg_kw, init, out_dir, mode):
     from fast_tffm_b200.fm_model import Model
     from fast_tffm_b200.fm_ops import FmParseError
     from fast_tffm_b200.sharded import PeerShardedModel, ShardedModel
-    cls = PeerShardedModel if mode == "peer" else ShardedModel
-    m = cls(Model(**cfg_kw), device=device).build(init_table=init)
+    if mode == "exchange":
+        m = ShardedModel(Model(**cfg_kw), device=device).build(init_table=init)
+    else:
+        m = PeerShardedModel(Model(**cfg_kw), device=device,
+                             exchange="records" if mode == "merge" else "atomics").build(init_table=init)
     per = cfg_kw["batch_size"] // world
     mine = list(lines[rank * per:(rank + 1) * per])
     if rank == 1:

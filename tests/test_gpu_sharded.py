@@ -12,7 +12,7 @@ from test_sharded_gloo import _reference
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("mode", ["exchange", "peer"])
+@pytest.mark.parametrize("mode", ["exchange", "peer", "merge"])
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_nccl_ranks_equal_single_process(criteo_lines, tmp_path, world, mode):
     if torch.cuda.device_count() < world:
@@ -23,7 +23,7 @@ def test_nccl_ranks_equal_single_process(criteo_lines, tmp_path, world, mode):
                   bias_lambda=1e-3, learning_rate=0.05, adagrad_init_accumulator=0.1, loss_type="logistic")
     init = rng.uniform(-0.01, 0.01, (cfg_kw["vocabulary_size"], 17)).astype(np.float32)
     steps = 3
-    port = 29700 + world + (50 if mode == "peer" else 0)
+    port = 29700 + world + {"exchange": 0, "peer": 50, "merge": 25}[mode]
     mp.spawn(shard_worker.run, args=(world, port, "nccl", lines, weights, cfg_kw, init, steps, str(tmp_path), mode),
              nprocs=world, join=True)
     ref, exp_losses = _reference(lines, weights, cfg_kw, init, steps, world)
@@ -34,7 +34,8 @@ def test_nccl_ranks_equal_single_process(criteo_lines, tmp_path, world, mode):
     close(got, f["pred"], pred_scale(f))
 
 
-@pytest.mark.parametrize("mode,k", [("peer", 5), ("peer", 100), ("peer", 400), ("exchange", 100), ("exchange", 400)])
+@pytest.mark.parametrize("mode,k", [("peer", 5), ("peer", 100), ("peer", 400), ("exchange", 100), ("exchange", 400),
+                                    ("merge", 5), ("merge", 100)])
 def test_sharded_steps_other_factor_nums(criteo_lines, tmp_path, mode, k):
     """row widths beyond the benchmark's: 2 and 26 chunks per row, and the wide-row kernels (K > 378)"""
     if torch.cuda.device_count() < 2:
@@ -44,7 +45,7 @@ def test_sharded_steps_other_factor_nums(criteo_lines, tmp_path, mode, k):
     cfg_kw = dict(vocabulary_size=170003, factor_num=k, batch_size=200, hash_feature_id=False, factor_lambda=2e-3,
                   bias_lambda=1e-3, learning_rate=0.05, adagrad_init_accumulator=0.1, loss_type="mse")
     init = rng.uniform(-0.01, 0.01, (cfg_kw["vocabulary_size"], k + 1)).astype(np.float32)
-    port = 29820 + (k % 97) + (100 if mode == "peer" else 0)
+    port = 29820 + (k % 97) + {"exchange": 0, "peer": 100, "merge": 200}[mode]
     mp.spawn(shard_worker.run, args=(2, port, "nccl", lines, weights, cfg_kw, init, 2, str(tmp_path), mode),
              nprocs=2, join=True)
     ref, exp_losses = _reference(lines, weights, cfg_kw, init, 2, 2)
@@ -55,7 +56,7 @@ def test_sharded_steps_other_factor_nums(criteo_lines, tmp_path, mode, k):
     close(got, f["pred"], pred_scale(f))
 
 
-@pytest.mark.parametrize("mode", ["exchange", "peer"])
+@pytest.mark.parametrize("mode", ["exchange", "peer", "merge"])
 def test_parse_error_on_one_rank_voids_the_step_everywhere(criteo_lines, tmp_path, mode):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
@@ -64,7 +65,7 @@ def test_parse_error_on_one_rank_voids_the_step_everywhere(criteo_lines, tmp_pat
     cfg_kw = dict(vocabulary_size=200003, factor_num=8, batch_size=200, hash_feature_id=False, factor_lambda=0.0,
                   bias_lambda=0.0, learning_rate=0.05, adagrad_init_accumulator=0.1, loss_type="logistic")
     init = rng.uniform(-0.01, 0.01, (cfg_kw["vocabulary_size"], 9)).astype(np.float32)
-    port = 29790 + (1 if mode == "peer" else 0)
+    port = 29790 + {"exchange": 0, "peer": 1, "merge": 2}[mode]
     mp.spawn(shard_worker.run_bad_line, args=(2, port, lines, cfg_kw, init, str(tmp_path), mode), nprocs=2, join=True)
     for r in range(2):
         raised, loss = np.load(tmp_path / ("bad%d.npy" % r))
