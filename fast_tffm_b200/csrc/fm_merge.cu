@@ -25,7 +25,8 @@ constexpr unsigned long long kNoError = 0xffffffffffffffffull;
 constexpr int kMaxRanks = 16;
 constexpr unsigned kStartBit = 0x80000000u;
 constexpr int kMergeThreads = 256;
-constexpr size_t kTileSmem = 96 * 1024;      // accumulator tile per block: two blocks per SM
+constexpr size_t kTileSmem = 20 * 1024;      // accumulator tile per block (K = 16: 256 rows): small tiles, many blocks
+                                             // per SM -- the merge is a chain of short latencies, not a bandwidth problem
 
 static inline int64_t grad_record_ld(int64_t k) { return (k + 3 + 3) / 4 * 4; }
 static inline int64_t tile_rows(int64_t k) {
@@ -117,8 +118,10 @@ push_kernel(const PushIn in, int K, int n_ranks, int row_bits, InboxBases inbox,
   for (int64_t base = warp_id * 32; base < n; base += warps_total * 32) {
     const int64_t mine = base + lane;
     bool opens = false;
+    uint2 my_pair = make_uint2(0u, 0u);
     if (mine < n) {
       const unsigned k0 = __ldg(in.keys + mine);
+      my_pair = __ldg(in.pairs + mine);                 // one coalesced read for the warp's 32 positions
       opens = mine == 0 || __ldg(in.keys + mine - 1) != k0 || (mine % FM_SORT_CHUNK) == 0;
       const int o = row_bits >= 32 ? 0 : (int)(k0 >> row_bits);
       const int64_t slot = mine - seg_start[o];
@@ -130,8 +133,11 @@ push_kernel(const PushIn in, int K, int n_ranks, int row_bits, InboxBases inbox,
     const unsigned opening = __ballot_sync(kFull, opens);
     const int n_open = __popc(opening);
     for (int taken = 0; taken < n_open; taken += per_warp) {       // warp-uniform
-      if (!(lane_on && taken + g < n_open)) continue;              // no warp-wide operation below
-      const unsigned p0 = (unsigned)(base + __fns(opening, 0, taken + g + 1));
+      const bool busy = lane_on && taken + g < n_open;
+      const int src = busy ? (int)__fns(opening, 0, taken + g + 1) : 0;
+      const unsigned first_ex = __shfl_sync(kFull, my_pair.x, src), first_x = __shfl_sync(kFull, my_pair.y, src);
+      if (!busy) continue;                                         // no warp-wide operation below
+      const unsigned p0 = (unsigned)(base + src);
       const unsigned key = __ldg(in.keys + p0);
       unsigned p1 = p0 + 1;
       while (p1 < n && (p1 % FM_SORT_CHUNK) != 0 && __ldg(in.keys + p1) == key) ++p1;
@@ -140,7 +146,7 @@ push_kernel(const PushIn in, int K, int n_ranks, int row_bits, InboxBases inbox,
       for (int t = 0; t < T; ++t) G[t] = make_float4(0.f, 0.f, 0.f, 0.f);
       float C = 0.f, D = 0.f, cnt = 0.f;
       for (unsigned p = p0; p < p1; ++p) {
-        const uint2 pr = __ldg(in.pairs + p);
+        const uint2 pr = p == p0 ? make_uint2(first_ex, first_x) : __ldg(in.pairs + p);
         const float x = __uint_as_float(pr.y);
         const float* r = in.rec + (int64_t)pr.x * in.rec_ld;
         const float pgx = __ldg(r) * x;
@@ -200,6 +206,9 @@ merge_kernel(float* __restrict__ table, float* __restrict__ accum, int64_t ld, i
   const int g = lane / gs, c = lane - g * gs;
   const bool lane_on = g < per_warp;
   const int vc_table = (K + 4) >> 2, vc_acc = (K + 6) >> 2;
+  // the accumulator tile is zeroed once; a row is cleared again by the group that applied it
+  for (int i = tid; i < rows * (int)rl / 4; i += kMergeThreads)
+    reinterpret_cast<float4*>(acc)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
     if (tid == 0) s_total = 0;
     __syncthreads();
@@ -213,37 +222,30 @@ merge_kernel(float* __restrict__ table, float* __restrict__ accum, int64_t ld, i
     }
     __syncthreads();
     if (s_total == 0) continue;                        // block-uniform: nothing for these rows this step
-    for (int i = tid; i < rows * (int)rl / 4; i += kMergeThreads)
-      reinterpret_cast<float4*>(acc)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    __syncthreads();
     const int64_t row0 = tile << log2_rows;
-    // ---- the G sorted sub-lists -> the accumulator tile ----
-    for (int s = warp; s < n_ranks; s += warps) {
-      const unsigned* keys = reinterpret_cast<const unsigned*>(inbox + (size_t)s * lay.stride + lay.keys);
-      const float* recs = reinterpret_cast<const float*>(inbox + (size_t)s * lay.stride + lay.recs);
-      for (unsigned base = s_a[s]; base < s_b[s]; base += 32) {          // warp-uniform
-        const unsigned p = base + lane;
-        const unsigned kw = p < s_b[s] ? __ldg(keys + p) : 0u;
-        const unsigned starts = __ballot_sync(kFull, (kw & kStartBit) != 0u);
-        const int n_open = __popc(starts);
-        for (int taken = 0; taken < n_open; taken += per_warp) {         // warp-uniform
-          const bool mine = lane_on && taken + g < n_open;
-          const int src = mine ? (int)__fns(starts, 0, taken + g + 1) : 0;
-          const unsigned k2 = __shfl_sync(kFull, kw, src);
-          if (!mine) continue;
-          const int r = (int)((int64_t)(k2 & ~kStartBit) - row0);
-          if (r < 0 || r >= rows) continue;                              // cannot happen for a well-formed inbox
-          const float* rec = recs + (size_t)(base + src) * rl;
-          float* dst = acc + (size_t)r * rl;
+    // ---- the G sorted sub-lists -> the accumulator tile: a thread per position, all senders' positions in one
+    //      flat range, so every load of the tile's records is in flight at once ----
+    for (unsigned i = tid; i < s_total; i += kMergeThreads) {
+      unsigned j = i;
+      int s = 0;
+      while (j >= s_b[s] - s_a[s]) { j -= s_b[s] - s_a[s]; ++s; }       // which sender's sub-list (at most G steps)
+      const unsigned p = s_a[s] + j;
+      const unsigned kw = __ldg(reinterpret_cast<const unsigned*>(inbox + (size_t)s * lay.stride + lay.keys) + p);
+      if (!(kw & kStartBit)) continue;
+      const int r = (int)((int64_t)(kw & ~kStartBit) - row0);
+      if (r < 0 || r >= rows) continue;                                  // cannot happen for a well-formed inbox
+      const float4* rec = reinterpret_cast<const float4*>(
+          reinterpret_cast<const float*>(inbox + (size_t)s * lay.stride + lay.recs) + (size_t)p * rl);
+      float* dst = acc + (size_t)r * rl;
+      for (int c4 = 0; c4 < vc_acc; c4 += 4) {                           // four 16-byte loads in flight per thread
+        float4 v[4];
 #pragma unroll
-          for (int t = 0; t < T; ++t) {
-            const int chunk = c + t * gs;
-            if (chunk < vc_acc) {
-              const float4 v = __ldg(reinterpret_cast<const float4*>(rec + 4 * chunk));
-              atomicAdd(dst + 4 * chunk + 0, v.x); atomicAdd(dst + 4 * chunk + 1, v.y);
-              atomicAdd(dst + 4 * chunk + 2, v.z); atomicAdd(dst + 4 * chunk + 3, v.w);
-            }
-          }
+        for (int u = 0; u < 4; ++u) v[u] = c4 + u < vc_acc ? __ldg(rec + c4 + u) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (c4 + u >= vc_acc) continue;
+          float* d = dst + 4 * (c4 + u);
+          atomicAdd(d + 0, v[u].x); atomicAdd(d + 1, v[u].y); atomicAdd(d + 2, v[u].z); atomicAdd(d + 3, v[u].w);
         }
       }
     }
@@ -251,21 +253,30 @@ merge_kernel(float* __restrict__ table, float* __restrict__ accum, int64_t ld, i
     // ---- Adagrad on the rows that got something (G_0 = C + cnt rg lb b, G_k = v_k (cnt rg lf - D) + B_k) ----
     const int groups = (kMergeThreads / 32) * per_warp;
     const int my_group = warp * per_warp + g;
+    const unsigned gmask = gs >= 32 ? kFull : (((1u << gs) - 1u) << (g * gs));
     for (int r = my_group; lane_on && r < rows; r += groups) {
-      const float* a = acc + (size_t)r * rl;
+      float* a = acc + (size_t)r * rl;
       const float cnt = a[K + 2];
-      if (cnt == 0.f || row0 + r >= shard_rows) continue;
+      if (cnt == 0.f) continue;
       const float D = a[K + 1];
       const float fac_scale = cnt * rf - D, bias_scale = cnt * rb;
       const int64_t row = (row0 + r) * ld;
+      const bool in_shard = row0 + r < shard_rows;
+      float4 a4[T];
 #pragma unroll
       for (int t = 0; t < T; ++t) {
         const int chunk = c + t * gs;
-        if (chunk >= vc_table) continue;
-        const float4 a4 = *reinterpret_cast<const float4*>(a + 4 * chunk);
+        a4[t] = chunk < vc_acc ? *reinterpret_cast<const float4*>(a + 4 * chunk) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      __syncwarp(gmask);                              // every lane of the group has read the row before it is cleared
+#pragma unroll
+      for (int t = 0; t < T; ++t) {
+        const int chunk = c + t * gs;
+        if (chunk < vc_acc) *reinterpret_cast<float4*>(a + 4 * chunk) = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (chunk >= vc_table || !in_shard) continue;
         const float4 w4 = *reinterpret_cast<const float4*>(table + row + 4 * chunk);
         const float4 h4 = *reinterpret_cast<const float4*>(accum + row + 4 * chunk);
-        const float av[4] = {a4.x, a4.y, a4.z, a4.w};
+        const float av[4] = {a4[t].x, a4[t].y, a4[t].z, a4[t].w};
         float wv[4] = {w4.x, w4.y, w4.z, w4.w};
         float hv[4] = {h4.x, h4.y, h4.z, h4.w};
 #pragma unroll
