@@ -30,6 +30,7 @@ orchestration can be exercised on CPU tensors with gloo in tests; the default is
 library and there is no CPU implementation in this package.
 """
 import ctypes
+import os
 
 import torch
 import torch.distributed as dist
@@ -476,7 +477,7 @@ class PeerShardedModel:
     def parse_ahead(self, lines, after=None):
         """parse of the next batch on a side stream (see Model.parse_ahead)"""
         if self._parse_stream is None:
-            self._parse_stream = torch.cuda.Stream(device=self.device)
+            self._parse_stream = torch.cuda.Stream(device=self.device, priority=int(os.environ.get("FM_AHEAD_PRIORITY", "0")))
         self._ahead_slot = 3 - self._ahead_slot
         main, side = torch.cuda.current_stream(self.device), self._parse_stream
         b = self._slots.get(self._ahead_slot)
@@ -484,9 +485,10 @@ class PeerShardedModel:
         if after is not None:
             side.wait_event(after)
         with torch.cuda.stream(side):
-            packed, b = self._parse(lines, slot=self._ahead_slot, max_blocks=Model.BACKGROUND_PARSE_BLOCKS)
+            bg = int(os.environ.get("FM_AHEAD_BLOCKS", Model.BACKGROUND_PARSE_BLOCKS))
+            packed, b = self._parse(lines, slot=self._ahead_slot, max_blocks=bg)
             if self.exchange == "records":
-                self._sort(b, packed.n_lines, max_blocks=Model.BACKGROUND_PARSE_BLOCKS)
+                self._sort(b, packed.n_lines, max_blocks=bg)
             done = torch.cuda.Event()
             done.record(side)
         return dict(b=b, packed=packed, done=done, sorted=self.exchange == "records")

@@ -361,18 +361,19 @@ size_t fm_peer_touched_workspace(int64_t shard_rows);
  * fm_peer_sorted_score (rows pulled from their owners; records [pg, s_1..s_K] per example stay local), then
  * fm_peer_push_records writes, into every owner's inbox (peer-mapped; inbox_bases[r] = rank r's inbox as mapped here):
  *   - per sorted position one key word: the shard row | 2^31 where a piece (a run of equal rows, cut at multiples of
- *     FM_SORT_CHUNK) starts;
+ *     FM_SORT_CHUNK) starts | 2^30 when the run goes on in a further piece (hence at most 2^30 rows per shard);
  *   - per piece one record {C, B_1..B_K, D, cnt} (the columns of fm_fused_score_scatter's accumulator rows), at the
  *     piece's position;
- *   - per tile of fm_merge_tile_rows(K) shard rows the position where its rows begin in this sender's segment.
+ *   - per tile of fm_merge_tile_rows(G) shard rows the position where its rows begin in this sender's segment.
  * An inbox holds fm_merge_inbox_bytes(inbox_capacity, shard_rows, K, G) bytes (256-byte aligned), one part per sender,
  * each for up to inbox_capacity positions; a segment that does not fit voids the step (status->first_error gets kind
  * FM_PARSE_E_CAPACITY).  All ranks must have finished pushing (fm_peer_sync) before any owner calls
- * fm_peer_merge_update: per tile of rows a block adds the G senders' sub-lists to an accumulator tile in shared
- * memory and applies TF1 SparseApplyAdagrad to the rows that received something.  flag (device int64, fm_peer_sync's
+ * fm_peer_merge_update: per tile of rows a block finds every row's records through a directory in shared memory,
+ * adds them in registers in sender order (the same sum on every run) and applies TF1 SparseApplyAdagrad to the rows
+ * that received something.  flag (device int64, fm_peer_sync's
  * word_out): the call is a no-op when *flag >= 0.  A second fm_peer_sync separates it from the next step's reads.
  * No accumulator table, no bitmap, no global float atomics; about 236 instead of 328 wire bytes per remote occurrence. */
-int64_t fm_merge_tile_rows(int64_t factor_num);
+int64_t fm_merge_tile_rows(int64_t n_ranks);
 size_t fm_merge_inbox_bytes(int64_t capacity, int64_t shard_rows, int64_t factor_num, int64_t n_ranks);
 size_t fm_merge_push_workspace(int64_t n_ranks);
 int fm_peer_sorted_score(const int64_t* feature_ids, const float* feature_vals, const int32_t* feature_poses,

@@ -96,5 +96,5 @@ torch.cuda.synchronize()
 assert all(int(d["status"][0]) == -1 for d in ranks)
 out = {"virtual_ranks": g, "sort_ms": timed(lambda: sort(ranks[0]), reps), "score_local_ms": timed(lambda: score(ranks[0]), reps),
        "push_local_ms": timed(lambda: push(0), reps), "merge_ms": timed(lambda: merge(0), reps),
-       "tile_rows": int(lib.fm_merge_tile_rows(k)), "shard_rows": rows}
+       "tile_rows": int(lib.fm_merge_tile_rows(g)), "shard_rows": rows}
 print(json.dumps(out))
