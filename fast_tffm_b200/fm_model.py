@@ -651,6 +651,8 @@ class Model(object):
         packed, weights = self._to_device(lines, weights)
         b = self.train_step_async(packed, weights, path=path)
         host = b["status"].cpu()
+        if int(host[0]) & 0xFFFFFFFFFFFFFFFF != _lib.NO_ERROR:
+            self.global_step -= 1        # the guard voided the step: the reference's global_step does not advance either
         _raise(host, packed)
         return float(host[6:8].view(torch.float32)[0])
 

@@ -27,11 +27,13 @@ def check_sync_word(f):
 
 class StepResult:
     """Outcome of one pipelined step.  loss() blocks until that step has finished on the device and
-    raises FmParseError if its batch did not parse (the step was then void, as in train_step)."""
+    raises FmParseError if its batch did not parse (the step was then void, as in train_step: the table is
+    untouched and the model's global_step does not count it).  The steps enqueued behind it have run by then --
+    the reference stops at the failing step; a pipelined caller learns of it up to RING steps later."""
 
-    def __init__(self, index, n_lines, done, decode):
+    def __init__(self, index, n_lines, done, decode, on_void=None):
         self.index, self.n_lines = index, n_lines
-        self._done, self._decode, self._value = done, decode, None
+        self._done, self._decode, self._value, self._on_void = done, decode, None, on_void
 
     def resolve(self):
         if self._decode is not None:
@@ -41,6 +43,8 @@ class StepResult:
                 self._value = decode()
             except FmParseError as e:
                 self._value = e
+                if self._on_void is not None:
+                    self._on_void()
         return self
 
     def loss(self):
@@ -140,10 +144,13 @@ class HostBatchPipeline:
         done = torch.cuda.Event()
         done.record(main)
         item["slot"]["free"] = done                 # staging slot (text, weights) reusable after this step
-        res = StepResult(self._count, n_lines, done, decode)
+        res = StepResult(self._count, n_lines, done, decode, on_void=self._uncount_step)
         self._ring[r] = res
         self._count += 1
         return res
+
+    def _uncount_step(self):
+        self.model.global_step -= 1      # a void step is not a step (the save_steps cadence follows the reference's)
 
     def run(self, batches):
         """generator of StepResult, one per batch, yielded as soon as the step is enqueued"""

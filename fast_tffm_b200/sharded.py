@@ -640,6 +640,7 @@ class PeerShardedModel:
         f = int(flag.item())
         check_sync_word(f)
         if f >= 0:
+            self.global_step -= 1        # void on every rank: not a step
             rank, first = f >> 48, f & ((1 << 48) - 1)
             line = self.last["packed"].line(first >> 3) if rank == self.rank else "<rank %d, line %d>" % (rank, first >> 3)
             raise FmParseError(first & 7, first >> 3, line)
