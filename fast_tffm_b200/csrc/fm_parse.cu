@@ -31,9 +31,8 @@ constexpr int kLPL = 8;                    // lanes per line
 constexpr int kLinesPerWarp = 32 / kLPL;
 constexpr int kLinesPerBlock = kWarpsPerBlock * kLinesPerWarp;
 constexpr int kChunk = kLPL * 16;          // bytes per group iteration (count pass)
-constexpr int kFillChunk = kLPL * 32;      // fill pass: 32 bytes per lane, so that a chunk's ~18 tokens fill the
-                                           // group's 8 lanes three times (a 128-byte chunk's ~9 left the second
-                                           // round nearly empty)
+constexpr int kFillChunk = kLPL * 32;      // fill pass: 32 bytes per lane and chunk; the tokens found are parsed
+                                           // kLPL at a time in full rounds, left-overs wait for the next chunk's
 constexpr int kSlowThreads = 128, kSlowBlocks = 148;
 
 struct ParseWs {
@@ -279,7 +278,7 @@ __device__ __forceinline__ uint64_t zero_bytes(uint64_t x) {
 __device__ __forceinline__ uint64_t keep_low_bytes(int n) {  // mask of the n lowest bytes, n clipped to 0..8
   return n >= 8 ? ~0ull : n <= 0 ? 0ull : ((1ull << (8 * n)) - 1ull);
 }
-struct Window {   // 32 bytes of text from the token start; bytes at and past the line end are 0
+struct Window {   // 32 bytes of text from the token start (a line's last token: bytes at and past its end are 0)
   uint64_t w0, w1, w2, w3;
   __device__ __forceinline__ uint64_t word(int j) const { return j == 0 ? w0 : j == 1 ? w1 : j == 2 ? w2 : j == 3 ? w3 : 0ull; }
   __device__ __forceinline__ uint32_t byte(int i) const { return (uint32_t)(word(i >> 3) >> (8 * (i & 7))) & 0xffu; }
@@ -290,13 +289,16 @@ struct Window {   // 32 bytes of text from the token start; bytes at and past th
     return sh ? ((lo >> sh) | (word(j + 1) << (64 - sh))) : lo;
   }
 };
-__device__ __forceinline__ Window load_window(const uint8_t* __restrict__ text, int64_t q, int64_t limit, int avail) {
+__device__ __forceinline__ Window load_window(const uint8_t* __restrict__ text, int64_t q, int64_t limit, int len,
+                                              bool mask_tail) {
   const int64_t a = q & ~(int64_t)7;
+  const int span = ((int)q & 7) + len;        // bytes from a to the token's end: only the words that hold them are read
   uint64_t v[5];
   const bool inside = a + 40 <= limit;        // nearly always: no per-word bound checks
 #pragma unroll
   for (int k = 0; k < 5; ++k)
-    v[k] = (inside || a + 8 * k + 8 <= limit) ? __ldg(reinterpret_cast<const uint64_t*>(text + a + 8 * k)) : 0ull;
+    v[k] = (8 * k < span && (inside || a + 8 * k + 8 <= limit)) ? __ldg(reinterpret_cast<const uint64_t*>(text + a + 8 * k))
+                                                               : 0ull;
   const int sh = ((int)q & 7) * 8;
   Window w;
   if (sh) {
@@ -305,52 +307,52 @@ __device__ __forceinline__ Window load_window(const uint8_t* __restrict__ text, 
   } else {
     w.w0 = v[0]; w.w1 = v[1]; w.w2 = v[2]; w.w3 = v[3];
   }
-  if (avail < 32) {                           // only a line's last tokens: bytes past the line end read as 0
-    w.w0 &= keep_low_bytes(avail); w.w1 &= keep_low_bytes(avail - 8);
-    w.w2 &= keep_low_bytes(avail - 16); w.w3 &= keep_low_bytes(avail - 24);
+  if (mask_tail) {                            // a line's last token: no space behind it, whatever follows reads as 0
+    w.w0 &= keep_low_bytes(len); w.w1 &= keep_low_bytes(len - 8);
+    w.w2 &= keep_low_bytes(len - 16); w.w3 &= keep_low_bytes(len - 24);
   }
   return w;
 }
-// index of the first byte that is NUL, ' ' or (with_colon) ':' in the 32-byte window; 32 if none
-// *is_colon: the byte found is ':' (only meaningful with_colon and when the result is < 32)
-__device__ __forceinline__ int find_end(const Window& w, bool with_colon, bool* is_colon) {
-  const uint64_t sp = 0x2020202020202020ull, co = 0x3a3a3a3a3a3a3a3aull;
-  *is_colon = false;
+// index of the first ':' in the first len (< 32) bytes of the window; len if none
+__device__ __forceinline__ int find_colon(const Window& w, int len) {
+  const uint64_t co = 0x3a3a3a3a3a3a3a3aull;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    const uint64_t x = w.word(j);
-    uint64_t f = zero_bytes(x) | zero_bytes(x ^ sp);
-    const uint64_t fc = with_colon ? zero_bytes(x ^ co) : 0ull;
-    f |= fc;
-    if (f) {
-      *is_colon = ((f & (0ull - f)) & fc) != 0;      // the lowest flag is a colon's
-      return 8 * j + ((__ffsll((long long)f) >> 3) - 1);
-    }
+    if (8 * j >= len) break;
+    const uint64_t f = zero_bytes(w.word(j) ^ co);
+    if (f) { const int at = 8 * j + ((__ffsll((long long)f) >> 3) - 1); return at < len ? at : len; }
   }
-  return 32;
+  return len;
 }
-struct RegBytes {  // up to 16 bytes held in two registers
-  uint64_t lo, hi; int n;
+struct RegBytes {  // 16 bytes held in two registers: a value of up to 15 bytes and what ends it (a space or 0)
+  uint64_t lo, hi;
   __device__ __forceinline__ uint32_t operator()(int i) const {
-    return i < n ? (uint32_t)((i < 8 ? lo : hi) >> (8 * (i & 7))) & 0xffu : 0u;
+    return i < 16 ? (uint32_t)((i < 8 ? lo : hi) >> (8 * (i & 7))) & 0xffu : 0u;
   }
 };
 
 enum { kTokOk = 0, kTokFallback = 1, kTokBad = 2 };
 
-// one token "id[:val]" (or the label when is_label) starting at q, from registers.
+// four decimal digits held as byte values 0..9, the most significant in the lowest byte -> their number
+__device__ __forceinline__ uint32_t four_digits(uint32_t t) {
+  t = (t * 10u + (t >> 8)) & 0x00ff00ffu;         // bytes 0 and 2: 10 d0 + d1, 10 d2 + d3
+  return (t * 100u + (t >> 16)) & 0xffffu;
+}
+
+// one token "id[:val]" (or the label when is_label) in [q, e), from registers: e is the token's end -- the tokenizer
+// already knows it --, line_end says that it is the line's end too (else text[e] is a space).
 // kTokFallback: the token does not fit the window, use the byte-wise parser.
 __device__ __forceinline__ int parse_token_regs(const uint8_t* __restrict__ text, int64_t q, int64_t e, int64_t limit,
-                                                int hash, int64_t vocab, bool is_label, int64_t* id_out,
-                                                uint32_t* bits_out) {
-  const int avail = e - q >= 32 ? 32 : (int)(e - q);
-  const Window w = load_window(text, q, limit, avail);
+                                                int hash, int64_t vocab, bool is_label, bool line_end,
+                                                int64_t* id_out, uint32_t* bits_out) {
+  if (e - q >= 32) return kTokFallback;
+  const int len = (int)(e - q);
+  if (len == 0) return kTokBad;    // empty token: the sequential path knows what the reference does with it
+  const Window w = load_window(text, q, limit, len, line_end);
   int vstart = 0;
   if (!is_label) {
-    bool colon;
-    const int n = find_end(w, true, &colon);
-    if (n >= 32) return kTokFallback;
-    if (n == 0) return kTokBad;  // empty token: the sequential path knows what the reference does with it
+    const int n = find_colon(w, len);
+    if (n == 0) return kTokBad;
     int64_t id;
     if (hash) {
       const uint64_t m = 0xc6a4a7935bd1e995ull;
@@ -374,19 +376,33 @@ __device__ __forceinline__ int parse_token_regs(const uint8_t* __restrict__ text
       id = (int64_t)acc;
     }
     *id_out = id;
-    if (!colon) { *bits_out = 0x3f800000u; return kTokOk; }  // ' ' or line end: value 1
+    if (n == len) { *bits_out = 0x3f800000u; return kTokOk; }  // no colon: value 1
     vstart = n + 1;
   }
-  // the value (or label): must end at a space or at the line end, inside the window
+  // the value (or label): the rest of the token
+  const int vlen = len - vstart;
+  if (vlen >= 16) return kTokFallback;
+  if (vlen == 0) return kTokBad;
   RegBytes v;
   v.lo = w.at(vstart);
+  if (vlen <= 8) {
+    // digits[.digits] in at most 8 bytes, no sign, no exponent -- what a feature value nearly always is -- without a
+    // loop: the dot is taken out, the (at most 8) digits are checked and converted in registers.  Anything else
+    // falls through to the general scanner; both end in the same dec_to_f32_fast(w, -frac).
+    const uint64_t x = v.lo & keep_low_bytes(vlen);
+    const uint64_t dotf = zero_bytes(x ^ 0x2e2e2e2e2e2e2e2eull);
+    const int dp = dotf ? (__ffsll((long long)dotf) >> 3) - 1 : vlen;
+    const int ndig = dotf ? vlen - 1 : vlen;
+    const uint64_t below = keep_low_bytes(dp);
+    const uint64_t dg = (x & below) | ((dotf ? x >> 8 : x) & ~below);
+    uint64_t t = dg ^ (0x3030303030303030ull & keep_low_bytes(ndig));
+    if (ndig > 0 && (((t + 0x7676767676767676ull) | t) & 0x8080808080808080ull) == 0) {
+      t <<= 8 * (8 - ndig);                       // leading zeros in front (the low bytes): eight digits, d0 first
+      const uint64_t wv = (uint64_t)four_digits((uint32_t)t) * 10000u + four_digits((uint32_t)(t >> 32));
+      return fmnp::dec_to_f32_fast(wv, -(int64_t)(ndig - dp), bits_out) ? kTokOk : kTokBad;
+    }
+  }
   v.hi = w.at(vstart + 8);
-  const uint64_t sp = 0x2020202020202020ull;
-  const uint64_t f0 = zero_bytes(v.lo) | zero_bytes(v.lo ^ sp), f1 = zero_bytes(v.hi) | zero_bytes(v.hi ^ sp);
-  const int vlen = f0 ? (__ffsll((long long)f0) >> 3) - 1 : f1 ? 8 + (__ffsll((long long)f1) >> 3) - 1 : 16;
-  if (vstart + vlen >= 32 || vlen >= 16) return kTokFallback;   // may continue past what we hold
-  v.n = vlen;
-  if (vlen == 0) return kTokBad;
   const int used = scan_value_fast(v, bits_out);
   return used == vlen ? kTokOk : kTokBad;
 }
@@ -428,7 +444,9 @@ parse_fill_kernel(const uint8_t* __restrict__ text, int64_t limit, const int64_t
                   int64_t vocab, int hash, const int32_t* __restrict__ poses, float* __restrict__ labels,
                   int64_t* __restrict__ ids, float* __restrict__ vals, int64_t capacity,
                   int32_t* __restrict__ slow_list, int* __restrict__ slow_count) {
-  __shared__ uint16_t s_tok[kWarpsPerBlock][kLinesPerWarp][kFillChunk + 4];
+  // token starts of a line, as byte offsets from (pos - kFillChunk): a chunk's tokens, behind the few (< kLPL) the
+  // previous chunk left over -- tokens are parsed kLPL at a time, in full rounds, whatever chunk they began in
+  __shared__ uint16_t s_tok[kWarpsPerBlock][kLinesPerWarp][kFillChunk + kLPL + 6];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane / kLPL, c = lane % kLPL;
   const unsigned gm = group_mask(lane);
   for (int64_t line = ((int64_t)blockIdx.x * kWarpsPerBlock + warp) * kLinesPerWarp + g; line < n_lines;
@@ -439,6 +457,7 @@ parse_fill_kernel(const uint8_t* __restrict__ text, int64_t limit, const int64_t
   uint16_t* tok = s_tok[warp][g];
   bool bad = out_base + cnt > capacity || e <= s;
   int32_t ord_base = -1;  // token -1 is the label
+  int pending = 0;        // tokens carried over from the previous chunk (group-uniform)
   for (int64_t pos = s & ~(int64_t)15; pos < e && !bad; pos += kFillChunk) {
     const int64_t p = pos + c * 32;
     uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -449,14 +468,19 @@ parse_fill_kernel(const uint8_t* __restrict__ text, int64_t limit, const int64_t
     // one bit per byte of the lane's 32: spaces and NULs inside [lo, hi)
     const uint32_t below_hi = hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u);
     const uint32_t in_line = hi > lo ? (below_hi & ~((1u << lo) - 1u)) : 0u;
-    uint32_t sp32 = 0, nul32 = 0;
+    uint32_t sp32 = 0, zero_somewhere = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       sp32 |= flag_bits(flag_eq(w[k], ' ')) << (4 * k);
-      nul32 |= flag_bits(flag_eq(w[k], 0)) << (4 * k);
+      zero_somewhere |= (w[k] - 0x01010101u) & ~w[k];         // bit 7 of some byte set <=> the word has a zero byte
     }
     sp32 &= in_line;
-    bad |= (nul32 & in_line) != 0;  // a NUL ends the line early: sequential path
+    if (zero_somewhere & 0x80808080u) {           // a NUL ends the line early: sequential path.  Exact where: only
+      uint32_t nul32 = 0;                         // the lanes at a line's two ends get here for nothing
+#pragma unroll
+      for (int k = 0; k < 8; ++k) nul32 |= flag_bits(flag_eq(w[k], 0)) << (4 * k);
+      bad |= (nul32 & in_line) != 0;
+    }
     int n_here = __popc(sp32);
     const bool first = pos <= s;                  // the chunk that holds the line start also lists the label
     if (first && c == 0) n_here += 1;
@@ -466,14 +490,19 @@ parse_fill_kernel(const uint8_t* __restrict__ text, int64_t limit, const int64_t
       const int t = __shfl_up_sync(gm, incl, o, kLPL);
       if (c >= o) incl += t;
     }
-    const int tot = __shfl_sync(gm, incl, kLPL - 1, kLPL);
-    int wpos = incl - n_here;
-    if (first && c == 0) tok[wpos++] = (uint16_t)(s - pos);
-    for (uint32_t f = sp32; f; f &= f - 1) tok[wpos++] = (uint16_t)(c * 32 + __ffs(f));  // the byte after the space
+    const int total = pending + __shfl_sync(gm, incl, kLPL - 1, kLPL);
+    int wpos = pending + incl - n_here;
+    if (first && c == 0) tok[wpos++] = (uint16_t)(kFillChunk + (s - pos));
+    for (uint32_t f = sp32; f; f &= f - 1) tok[wpos++] = (uint16_t)(kFillChunk + c * 32 + __ffs(f));  // the byte after the space
+    // full rounds of kLPL tokens, each with its successor already listed (a token ends one byte before the next
+    // begins); the line's last chunk takes what is left: its last token ends with the line
+    const bool last = pos + kFillChunk >= e;
+    const int n_proc = last ? total : total > 0 ? ((total - 1) & ~(kLPL - 1)) : 0;
+    if (last && c == 0) tok[total] = (uint16_t)(kFillChunk + (e - pos) + 1);
     __syncwarp(gm);
-    for (int t = c; t < tot; t += kLPL) {
-      // tok[] holds 0..256 (256 = the byte after a space that ends the chunk)
-      const int64_t q = pos + tok[t];
+    for (int t = c; t < n_proc; t += kLPL) {
+      const int64_t q = pos - kFillChunk + tok[t];
+      const int64_t q_end = pos - kFillChunk + tok[t + 1] - 1;
       const int32_t ordinal = ord_base + t;
       const bool is_label = ordinal < 0;
       if (!is_label) {
@@ -482,8 +511,8 @@ parse_fill_kernel(const uint8_t* __restrict__ text, int64_t limit, const int64_t
       }
       int64_t id = 0;
       uint32_t bits = 0x3f800000u;
-      int rc = parse_token_regs(text, q, e, limit, hash, vocab, is_label, &id, &bits);
-      if (rc == kTokFallback) rc = parse_token_bytes(text, q, e, hash, vocab, is_label, &id, &bits);
+      int rc = parse_token_regs(text, q, q_end, limit, hash, vocab, is_label, q_end >= e, &id, &bits);
+      if (rc == kTokFallback) rc = parse_token_bytes(text, q, q_end, hash, vocab, is_label, &id, &bits);
       if (rc != kTokOk) { bad = true; continue; }
       if (is_label) {
         labels[line] = __uint_as_float(bits);
@@ -492,8 +521,14 @@ parse_fill_kernel(const uint8_t* __restrict__ text, int64_t limit, const int64_t
         vals[out_base + ordinal] = __uint_as_float(bits);
       }
     }
-    ord_base += tot;
+    ord_base += n_proc;
+    // the tokens left over move to the front, re-based for the next chunk (at most kLPL: one per lane)
+    pending = total - n_proc;
+    const int carried = c < pending ? (int)tok[n_proc + c] - kFillChunk : 0;
+    bad |= carried < 0;                           // a token that spans a whole chunk: not a regular line
     bad = __any_sync(gm, bad);
+    __syncwarp(gm);                               // every read of tok[] above is done
+    if (c < pending) tok[c] = (uint16_t)carried;
     __syncwarp(gm);
   }
   bad = __any_sync(gm, bad);
