@@ -280,7 +280,7 @@ class Model(object):
 
     # ---- the vocabulary table ------------------------------------------------------
     def build(self, device=None, init_table=None, seed=None, max_nnz_per_line=None, ld=None,
-              layout=None, path=None):
+              layout=None, path=None, inference=False):
         """Allocates table + Adagrad accumulator (+ table-shaped gradient accumulator) in HBM.
         The table is [vocabulary_size, ld] (row = feature id, see _stride_for); the reference's
         vocabulary_block_num blocks (fm_model.py:269-284) are a relabelling applied when
@@ -294,7 +294,8 @@ class Model(object):
         B200 at cfg2 it is the faster of the two (uniform ids 0.56 vs 0.63 ms per step, zipf 0.34 vs 0.57;
         profiles/README.md r2); "sorted" is the reproducible one and the one that needs no third table.
         init: uniform(-init_value_range, init_value_range) (:278-281) or `init_table`
-        ([vocabulary_size, K+1], for parity runs)."""
+        ([vocabulary_size, K+1], for parity runs).
+        inference: the weight table alone (layout "split", no Adagrad accumulator): predict only."""
         lib = load()
         if not self.adagrad_init_accumulator > 0:      # tf.train.AdagradOptimizer raises the same way
             raise ValueError("initial_accumulator_value must be positive: %s" % self.adagrad_init_accumulator)
@@ -310,6 +311,8 @@ class Model(object):
         sortable = (k + 4) // 4 <= 96 and v <= 1 << 32
         if path is None:
             path = "sorted" if self.optimizer == "sgd" else "claim"
+        if inference:
+            layout = "split"
         if layout is None:
             layout = "pair" if path == "sorted" else "interleaved"
         if layout not in ("pair", "interleaved", "split"):
@@ -346,7 +349,9 @@ class Model(object):
             if seed is not None:
                 gen.manual_seed(seed)
             self.table[:, :k + 1].uniform_(-self.init_value_range, self.init_value_range, generator=gen)
-        if layout in ("pair", "interleaved"):
+        if inference:
+            self.accum = None
+        elif layout in ("pair", "interleaved"):
             self.accum = self._store[:, part:2 * part]
             self.accum.fill_(self.adagrad_init_accumulator)
         else:
@@ -529,6 +534,8 @@ class Model(object):
         path = self.default_path if path is None else path
         if path not in self.PATHS:
             raise ValueError("path must be one of %s" % (self.PATHS,))
+        if self.accum is None:
+            raise RuntimeError("this model was built with inference=True: it has no optimizer state to train with")
         if parsed is not None and path not in ("claim", "sorted"):
             raise ValueError("parse_ahead() feeds the sorted and claim paths only")
         if self.optimizer != "adagrad" and path != "sorted":

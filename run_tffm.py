@@ -5,9 +5,11 @@
     python run_tffm.py predict sample.cfg
 
 Same config file, same stdout lines ("-- Global Step: %d; Avg loss: %.5f;",
-"Average speed: ...  ex/s", "Model saved to ..."), same <file>_score outputs.  Not carried over
-(TensorFlow-runtime features, out of scope): `generate` / --export_path (SavedModel), --dist /
---protocol / --wait-for-workers (gRPC parameter server).  The replacement for --dist is
+"Average speed: ...  ex/s", "Model saved to ..."), same <file>_score outputs.
+    python run_tffm.py generate sample.cfg --export_path DIR
+writes the serving artefact of the newest checkpoint: not a TF SavedModel (no TF runtime here) but the same content
+and contract, the weight table + a scorer for unlabeled "id:val ..." lines (fast_tffm_b200/serving.py).  Not carried
+over: --dist / --protocol / --wait-for-workers (gRPC parameter server).  The replacement for --dist is
 
     python -m torch.distributed.run --nproc-per-node G --master-addr 127.0.0.1 run_tffm.py train sample.cfg
 
@@ -241,20 +243,23 @@ def main():
     parser.add_argument("-t", "--trace", metavar='OUTPUT_FILE_NAME',
                         help="Stores per-step timings as a chrome trace file")
     parser.add_argument("-m,", "--monitor", action="store_true", help="Prints execution speed to screen")
-    parser.add_argument("--export_path", help="(SavedModel export: not available in this build)")
+    parser.add_argument("--export_path", help="Specifies the location to which the model is to be exported.")
     parser.add_argument("--stream-mb", type=int, default=None, metavar='MB',
                         help="Stream the training files through the GPU in segments of MB megabytes instead of "
                              "keeping them resident (automatic when they exceed half of the free GPU memory)")
     args = parser.parse_args()
 
-    if args.task == 'generate' or args.dist is not None:
-        print("This build replaces the hot path only: 'generate' (TF SavedModel) and --dist (TF parameter "
-              "server) are not provided. Multi-GPU training: python -m torch.distributed.run --nproc-per-node G "
-              "--master-addr 127.0.0.1 run_tffm.py train <cfg>.")
+    if args.dist is not None:
+        print("This build replaces the hot path only: --dist (TF parameter server) is not provided. Multi-GPU "
+              "training: python -m torch.distributed.run --nproc-per-node G --master-addr 127.0.0.1 run_tffm.py "
+              "train <cfg>.")
+        sys.exit(2)
+    if args.task == 'generate' and args.export_path is None:
+        print("Export path is not specified. Use --export_path.")
         sys.exit(2)
 
     model = Model(args.config_file)
-    if args.task == 'predict' and model.log_dir is None:
+    if args.task in ('predict', 'generate') and model.log_dir is None:
         print("Missing log directory. Must include a checkpoint file.")
         sys.exit(1)
     if not torch.cuda.is_available():
@@ -262,16 +267,21 @@ def main():
         sys.exit(3)
     if int(os.environ.get("WORLD_SIZE", "1")) > 1:
         if args.task != 'train':
-            print("predict runs on one GPU (the checkpoint of a sharded run is in the single-GPU layout).")
+            print("predict and generate run on one GPU (the checkpoint of a sharded run is in the single-GPU layout).")
             sys.exit(2)
         train_sharded(model, args.monitor, args.stream_mb)
         return
     model.build(seed=int(time.time()))
     if model.log_dir is not None and latest_checkpoint(_ckpt_path(model)) is not None:
         model.restore(_ckpt_path(model))     # MonitoredTrainingSession(checkpoint_dir=log_dir) restores
-    elif args.task == 'predict':
+    elif args.task in ('predict', 'generate'):
         print("No checkpoint in", model.log_dir)
         sys.exit(1)
+    if args.task == 'generate':
+        from fast_tffm_b200.serving import export_serving
+        print('Exporting trained model to', args.export_path)
+        export_serving(model, args.export_path)
+        return
     print("========", args.task, "========")
     if args.task == 'train':
         train(model, args.monitor, args.trace, args.stream_mb)

@@ -56,10 +56,25 @@ def test_train_then_predict_cli(tmp_path, loss_type):
     m.restore(str(tmp_path / "log" / "model.ckpt.pt"))
     lines = open(tmp_path / "test_0").read().splitlines()
     np.testing.assert_allclose(m.predict(lines).cpu().numpy(), np.float32(scores), rtol=1e-6)
-    # unsupported tasks say so
+    # generate: like the reference it wants --export_path; the exported table scores unlabeled "id:val ..." lines
+    # (serving_parser / serving_scorer, tffm/fm_model.py:194-252) like predict scores the labeled ones
     out = subprocess.run([sys.executable, os.path.join(ROOT, "run_tffm.py"), "generate", str(tmp_path / "t.cfg")],
                          capture_output=True, text=True, env=env, cwd=ROOT)
-    assert out.returncode == 2
+    assert out.returncode == 2 and "Export path is not specified" in out.stdout
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "run_tffm.py"), "generate", str(tmp_path / "t.cfg"),
+                          "--export_path", str(tmp_path / "export")], capture_output=True, text=True, env=env, cwd=ROOT)
+    assert out.returncode == 0 and "Exporting trained model to" in out.stdout, out.stdout + out.stderr
+    from fast_tffm_b200.fm_ops import FmParseError
+    from fast_tffm_b200.serving import ServingScorer
+    srv = ServingScorer(str(tmp_path / "export"))
+    assert srv.model.accum is None
+    unlabeled = [ln.split(" ", 1)[1] for ln in lines]
+    np.testing.assert_allclose(srv.score(unlabeled).cpu().numpy(), np.float32(scores), rtol=1e-6)
+    assert float(srv.score([""])[0]) == 0.0
+    with pytest.raises(FmParseError):
+        srv.score(["3:1 4"])                      # the serving parser needs a value on every token
+    with pytest.raises(RuntimeError):
+        srv.model.train_step(lines[:4])
 
 
 def test_validation_and_tolerance_stop_early(tmp_path):
