@@ -367,10 +367,17 @@ __device__ __forceinline__ int parse_token_regs(const uint8_t* __restrict__ text
     } else {
       if (n > 18) return kTokBad;
       uint64_t acc = 0;
-      for (int i = 0; i < n; ++i) {
-        const uint32_t d = w.byte(i) - '0';
-        if (d >= 10u) return kTokBad;
-        acc = acc * 10 + d;
+      if (n <= 8) {                              // the usual id: up to eight digits, checked and folded in registers
+        uint64_t t = (w.w0 & keep_low_bytes(n)) ^ (0x3030303030303030ull & keep_low_bytes(n));
+        if ((((t + 0x7676767676767676ull) | t) & 0x8080808080808080ull) != 0) return kTokBad;
+        t <<= 8 * (8 - n);
+        acc = (uint64_t)four_digits((uint32_t)t) * 10000u + four_digits((uint32_t)(t >> 32));
+      } else {
+        for (int i = 0; i < n; ++i) {
+          const uint32_t d = w.byte(i) - '0';
+          if (d >= 10u) return kTokBad;
+          acc = acc * 10 + d;
+        }
       }
       if ((int64_t)acc >= vocab) return kTokBad;
       id = (int64_t)acc;
@@ -385,24 +392,37 @@ __device__ __forceinline__ int parse_token_regs(const uint8_t* __restrict__ text
   if (vlen == 0) return kTokBad;
   RegBytes v;
   v.lo = w.at(vstart);
-  if (vlen <= 8) {
-    // digits[.digits] in at most 8 bytes, no sign, no exponent -- what a feature value nearly always is -- without a
-    // loop: the dot is taken out, the (at most 8) digits are checked and converted in registers.  Anything else
-    // falls through to the general scanner; both end in the same dec_to_f32_fast(w, -frac).
-    const uint64_t x = v.lo & keep_low_bytes(vlen);
+  v.hi = w.at(vstart + 8);
+  if (vlen <= 10) {
+    // [+-]digits[.digits] with at most 8 digits, no exponent -- what a feature value nearly always is ("0.6931",
+    // "-0.123456") -- without a loop: sign and dot are taken out, the digits are checked and converted in
+    // registers.  Anything else falls through to the general scanner; both end in the same dec_to_f32_fast(w, -frac).
+    const uint32_t c0 = (uint32_t)v.lo & 0xffu;
+    const bool neg = c0 == '-';
+    const int sgn = (neg || c0 == '+') ? 1 : 0;
+    const int blen = vlen - sgn;                  // the body: digits and at most one dot, 9 bytes at most to be fast
+    const uint64_t lo = sgn ? (v.lo >> 8) | (v.hi << 56) : v.lo;              // body bytes 0..7
+    const uint64_t b8 = (sgn ? v.hi >> 8 : v.hi) & 0xffull;                   // body byte 8
+    const uint64_t x = lo & keep_low_bytes(blen);
     const uint64_t dotf = zero_bytes(x ^ 0x2e2e2e2e2e2e2e2eull);
-    const int dp = dotf ? (__ffsll((long long)dotf) >> 3) - 1 : vlen;
-    const int ndig = dotf ? vlen - 1 : vlen;
-    const uint64_t below = keep_low_bytes(dp);
-    const uint64_t dg = (x & below) | ((dotf ? x >> 8 : x) & ~below);
-    uint64_t t = dg ^ (0x3030303030303030ull & keep_low_bytes(ndig));
-    if (ndig > 0 && (((t + 0x7676767676767676ull) | t) & 0x8080808080808080ull) == 0) {
-      t <<= 8 * (8 - ndig);                       // leading zeros in front (the low bytes): eight digits, d0 first
-      const uint64_t wv = (uint64_t)four_digits((uint32_t)t) * 10000u + four_digits((uint32_t)(t >> 32));
-      return fmnp::dec_to_f32_fast(wv, -(int64_t)(ndig - dp), bits_out) ? kTokOk : kTokBad;
+    const bool dot8 = !dotf && blen == 9 && b8 == '.';                        // "12345678."
+    const bool has_dot = dotf != 0 || dot8;
+    const int dp = dotf ? (__ffsll((long long)dotf) >> 3) - 1 : dot8 ? 8 : blen;
+    const int ndig = blen - (has_dot ? 1 : 0);
+    if (ndig >= 1 && ndig <= 8) {
+      const uint64_t below = keep_low_bytes(dp);
+      const uint64_t up = dotf ? (x >> 8) | (blen == 9 ? b8 << 56 : 0ull) : x;   // the bytes behind the dot move down
+      uint64_t t = ((x & below) | (up & ~below)) ^ (0x3030303030303030ull & keep_low_bytes(ndig));
+      if ((((t + 0x7676767676767676ull) | t) & 0x8080808080808080ull) == 0) {
+        t <<= 8 * (8 - ndig);                     // leading zeros in front (the low bytes): eight digits, d0 first
+        const uint64_t wv = (uint64_t)four_digits((uint32_t)t) * 10000u + four_digits((uint32_t)(t >> 32));
+        uint32_t r;
+        if (!fmnp::dec_to_f32_fast(wv, -(int64_t)(ndig - dp), &r)) return kTokBad;
+        *bits_out = (neg ? 0x80000000u : 0u) | r;
+        return kTokOk;
+      }
     }
   }
-  v.hi = w.at(vstart + 8);
   const int used = scan_value_fast(v, bits_out);
   return used == vlen ? kTokOk : kTokBad;
 }
