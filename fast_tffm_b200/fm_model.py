@@ -663,21 +663,39 @@ class Model(object):
         _raise(host, packed)
         return float(host[6:8].view(torch.float32)[0])
 
-    def predict_async(self, packed: PackedLines, path="claim"):
+    def predict_async(self, packed: PackedLines, path="claim", parsed=None):
         """scores of a device-resident batch in b["pred"].  Default: parse, then the scorer reads
         the rows straight from the table by feature id (no unique, no gathered copy);
-        path="composed" runs the reference's chain parse -> unique -> lookup -> fm_scorer."""
-        b = self._buffers(packed.n_lines, packed.nnz_bound())
+        path="composed" runs the reference's chain parse -> unique -> lookup -> fm_scorer.
+        parsed: handle from parse_ahead(packed, sort=False) for THIS batch: its parse ran on the side stream, under
+        the previous batch's scorer (the parser is instruction-bound, the scorer memory-bound); read the scores
+        before the buffer set comes round again (two sets: before the parse_ahead after the next one)."""
+        if parsed is not None:
+            if path == "composed":
+                raise ValueError("parse_ahead() feeds the default predict path only")
+            b = parsed["b"]
+            main = torch.cuda.current_stream(self.device)
+            need = torch.cuda.Event(enable_timing=True)
+            need.record(main)
+            main.wait_event(parsed["done"])
+            self._adapt_parse_grid(need, parsed["done"])
+            self._bufs = b
+        else:
+            b = self._buffers(packed.n_lines, packed.nnz_bound())
         if path == "composed":
             self._forward(packed, b)
             return b
         lib, st = load(), stream()
-        self._parse_unique(packed, b, unique=False)
+        if parsed is None:
+            self._parse_unique(packed, b, unique=False)
         check(lib.fm_fused_score_scatter(
             ptr(b["ids"]), None, ptr(b["vals"]), ptr(b["poses"]), None, None, packed.n_lines, self.factor_num,
             ptr(self.table), self.table.stride(0), self.factor_lambda, self.bias_lambda, 0, 0, ptr(b["pred"]),
             _off(b["status"], 6), _off(b["status"], 7), None, 4 * ((self.factor_num + 6) // 4), ptr(b["status"]),
             ptr(b["ws_fused"]), b["ws_fused"].numel(), st), "fm_fused_score_scatter")
+        if parsed is not None:       # the buffer set may be refilled once the scorer is through with it
+            b["free"] = torch.cuda.Event()
+            b["free"].record(torch.cuda.current_stream(self.device))
         return b
 
     def predict(self, lines, path="claim"):

@@ -793,6 +793,23 @@ def test_host_batch_pipeline_matches_step_by_step(criteo_lines):
                                    rtol=1e-6)
 
 
+def test_predict_with_parse_ahead_equals_predict(criteo_lines):
+    """a stream of predict batches with the next batch's parse running ahead: the same scores as one at a time"""
+    lines, _ = criteo_lines
+    m = Model(vocabulary_size=200003, factor_num=16, batch_size=256, hash_feature_id=True).build(DEV, seed=5, layout="split")
+    batches = [fm_ops.pack_lines(list(lines[i * 300:(i + 1) * 300 - 7 * i])).to(DEV, False) for i in range(5)]
+    want = [m.predict(p).cpu().numpy() for p in batches]
+    got = []
+    ahead = m.parse_ahead(batches[0], sort=False)
+    for i, p in enumerate(batches):
+        nxt = m.parse_ahead(batches[i + 1], sort=False) if i + 1 < len(batches) else None
+        b = m.predict_async(p, parsed=ahead)
+        got.append(b["pred"][:p.n_lines].clone())     # before the set is refilled (stream-ordered: no sync needed)
+        ahead = nxt
+    for g, w in zip(got, want):
+        np.testing.assert_array_equal(g.cpu().numpy(), w)
+
+
 def test_failed_parse_leaves_the_table_untouched():
     m = Model(vocabulary_size=100, factor_num=4, batch_size=2).build(DEV, seed=0)
     before = m.table.clone()
