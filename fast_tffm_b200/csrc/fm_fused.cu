@@ -618,23 +618,68 @@ static cudaError_t wide_smem_opt_in(bool peer) {
   return e;
 }
 
-// bitmap of touched rows -> list of row numbers (and the bitmap is cleared on the way)
-struct TouchedIn {
-  unsigned* bits; int64_t n_words;
-  __device__ int64_t count() const { return n_words; }
-  __device__ long long operator()(int64_t w) const { return __popc(bits[w]); }
-};
-struct TouchedOut {
-  unsigned* bits; int64_t* rows; int64_t capacity; int64_t* n_out;
-  __device__ void operator()(int64_t w, long long excl, long long cnt) const {
-    if (cnt == 0) return;
-    unsigned m = bits[w];
-    bits[w] = 0u;
-    for (long long r = excl; m; m &= m - 1, ++r)
-      if (r < capacity) rows[r] = w * 32 + (__ffs(m) - 1);
+// bitmap of touched rows -> ascending list of row numbers (and the bitmap is cleared on the way).
+// A tile = 256 threads x kTouchedRounds words, read round by round so that a warp reads 32 consecutive words and its
+// lanes write consecutive pieces of the list (the first version gave each thread 8 consecutive words: a serial loop
+// over ~36 rows per thread and 8-byte stores 256 bytes apart, 0.043-0.051 ms for a 2 MB bitmap).  Tiles take their
+// number from a ticket and find their place in the list by decoupled look-back (fm_scan.cuh).
+constexpr int kTouchedRounds = 4;
+__global__ void __launch_bounds__(kScanThreads)
+touched_rows_kernel(unsigned* __restrict__ bits, int64_t n_words, int64_t* __restrict__ rows, int64_t capacity,
+                    int64_t* __restrict__ n_out, ScanScratch st, int64_t n_tiles) {
+  constexpr int kW = kScanThreads / 32;
+  __shared__ unsigned s_tile;
+  __shared__ int s_warp[kTouchedRounds][kW];
+  __shared__ long long s_prefix;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_tile = atomicAdd(st.ticket, 1u);
+  __syncthreads();
+  const int64_t tile = s_tile;
+  const int64_t base = tile * (int64_t)(kScanThreads * kTouchedRounds);
+  unsigned w[kTouchedRounds];
+  int incl[kTouchedRounds];
+#pragma unroll
+  for (int r = 0; r < kTouchedRounds; ++r) {
+    const int64_t idx = base + r * kScanThreads + tid;
+    w[r] = idx < n_words ? bits[idx] : 0u;
+    int v = __popc(w[r]);
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(kFull, v, o);
+      if (lane >= o) v += u;
+    }
+    incl[r] = v;
+    if (lane == 31) s_warp[r][warp] = v;
   }
-  __device__ void total(long long t) const { *n_out = t; }
-};
+  __syncthreads();
+  // list order: round-major, then warp, then lane (= ascending words)
+  int before[kTouchedRounds], block_sum = 0;
+#pragma unroll
+  for (int r = 0; r < kTouchedRounds; ++r) {
+    before[r] = block_sum;
+#pragma unroll
+    for (int x = 0; x < kW; ++x) {
+      const int v = s_warp[r][x];
+      if (x < warp) before[r] += v;
+      block_sum += v;
+    }
+  }
+  if (warp == 0) {
+    const long long prefix = scan_look_back(st, tile, block_sum);
+    if (lane == 0) s_prefix = prefix;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < kTouchedRounds; ++r) {
+    unsigned m = w[r];
+    if (m == 0u) continue;
+    const int64_t idx = base + r * kScanThreads + tid;
+    bits[idx] = 0u;
+    for (long long at = s_prefix + before[r] + incl[r] - __popc(m); m; m &= m - 1, ++at)
+      if (at < capacity) rows[at] = idx * 32 + (__ffs(m) - 1);
+  }
+  if (tile == n_tiles - 1 && tid == 0) *n_out = s_prefix + block_sum;
+}
 
 struct Shape { int lpr, t; };
 static inline bool pick_shape(int64_t chunks, Shape* s) {
@@ -970,8 +1015,13 @@ FM_EXPORT int fm_peer_sorted_score(const int64_t* feature_ids, const float* feat
   return FM_OK;
 }
 
+static inline int64_t touched_tiles(int64_t words) {
+  const int64_t per = (int64_t)kScanThreads * kTouchedRounds;
+  return words <= 0 ? 1 : (words + per - 1) / per;
+}
+
 FM_EXPORT size_t fm_peer_touched_workspace(int64_t shard_rows) {
-  return scan_scratch_bytes((shard_rows + 31) / 32, 8);
+  return fm_align_up((size_t)touched_tiles((shard_rows + 31) / 32) * 8 + 16, 256);
 }
 
 FM_EXPORT int fm_peer_touched_rows(uint32_t* touched, int64_t shard_rows, int64_t* rows, int64_t capacity,
@@ -980,13 +1030,13 @@ FM_EXPORT int fm_peer_touched_rows(uint32_t* touched, int64_t shard_rows, int64_
   FM_REQUIRE(shard_rows >= 0 && capacity >= 0, "fm_peer_touched_rows: bad size");
   FM_REQUIRE(touched && n_rows && workspace && (capacity == 0 || rows), "fm_peer_touched_rows: null pointer");
   const int64_t words = (shard_rows + 31) / 32;
-  if (workspace_bytes < scan_scratch_bytes(words, 8))
-    return fm_fail(FM_E_WORKSPACE, "fm_peer_touched_rows: workspace %zu < %zu", workspace_bytes, scan_scratch_bytes(words, 8));
-  FM_CUDA(cudaMemsetAsync(workspace, 0, scan_scratch_bytes(words, 8), stream));
-  TouchedIn in{touched, words};
-  TouchedOut out{touched, rows, capacity, n_rows};
-  const int64_t tiles = scan_tiles(words, 8);
-  scan_kernel<8><<<(unsigned)tiles, kScanThreads, 0, stream>>>(in, out, scan_scratch_at(workspace, words, 8), tiles);
+  const size_t need = fm_peer_touched_workspace(shard_rows);
+  if (workspace_bytes < need)
+    return fm_fail(FM_E_WORKSPACE, "fm_peer_touched_rows: workspace %zu < %zu", workspace_bytes, need);
+  FM_CUDA(cudaMemsetAsync(workspace, 0, need, stream));
+  const int64_t tiles = touched_tiles(words);
+  touched_rows_kernel<<<(unsigned)tiles, kScanThreads, 0, stream>>>(touched, words, rows, capacity, n_rows,
+                                                                    scan_scratch_at(workspace, words, 1), tiles);
   FM_LAUNCH_CHECK();
   return FM_OK;
 }

@@ -34,6 +34,43 @@ static inline ScanScratch scan_scratch_at(void* p, int64_t n_items, int items_pe
   return s;
 }
 
+// Warp 0 of a tile: publish the tile's sum, then look back over the predecessors (32 tiles at a time) for the
+// exclusive prefix of the tile; every lane returns it.
+__device__ __forceinline__ long long scan_look_back(const ScanScratch& st, int64_t tile, long long block_sum) {
+  const int lane = threadIdx.x & 31;
+  if (lane == 0) {
+    const unsigned long long flag = tile == 0 ? 2ull : 1ull;
+    __threadfence();
+    atomicExch(&st.status[tile], (flag << 62) | (unsigned long long)block_sum);
+  }
+  long long prefix = 0;
+  int64_t look = tile - 1;
+  while (look >= 0) {  // warp-uniform
+    const int64_t idx = look - lane;
+    unsigned long long s = 0;
+    bool done = false;
+    while (!done) {
+      s = idx >= 0 ? *reinterpret_cast<volatile unsigned long long*>(&st.status[idx]) : (2ull << 62);
+      done = __all_sync(kFull, (s >> 62) != 0);
+    }
+    const unsigned flags = __ballot_sync(kFull, (s >> 62) == 2ull);
+    // lanes up to and including the first inclusive prefix contribute
+    const int first_incl = flags ? __ffs(flags) - 1 : 32;
+    long long v = (lane <= first_incl) ? (long long)(s & ((1ull << 62) - 1)) : 0;
+    if (idx < 0) v = 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+    prefix += v;
+    if (flags) break;
+    look -= 32;
+  }
+  if (lane == 0 && tile != 0) {
+    __threadfence();
+    atomicExch(&st.status[tile], (2ull << 62) | (unsigned long long)(prefix + block_sum));
+  }
+  return prefix;
+}
+
 // In:  int64_t count() const;  long long operator()(int64_t i) const   (i < count())
 // Out: void operator()(int64_t i, long long exclusive_prefix, long long item) const;
 //      void total(long long t) const    -- called once by the last tile
@@ -72,41 +109,9 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(In in, Out out, Scan
     if (w < warp) warp_off += v;
     block_sum += v;
   }
-  // publish, then look back over the predecessors (warp 0, 32 tiles at a time)
   if (warp == 0) {
-    if (lane == 0) {
-      const unsigned long long flag = tile == 0 ? 2ull : 1ull;
-      __threadfence();
-      atomicExch(&st.status[tile], (flag << 62) | (unsigned long long)block_sum);
-    }
-    long long prefix = 0;
-    int64_t look = tile - 1;
-    while (look >= 0) {  // warp-uniform
-      const int64_t idx = look - lane;
-      unsigned long long s = 0;
-      bool done = false;
-      while (!done) {
-        s = idx >= 0 ? *reinterpret_cast<volatile unsigned long long*>(&st.status[idx]) : (2ull << 62);
-        done = __all_sync(kFull, (s >> 62) != 0);
-      }
-      const unsigned flags = __ballot_sync(kFull, (s >> 62) == 2ull);
-      // lanes up to and including the first inclusive prefix contribute
-      const int first_incl = flags ? __ffs(flags) - 1 : 32;
-      long long v = (lane <= first_incl) ? (long long)(s & ((1ull << 62) - 1)) : 0;
-      if (idx < 0) v = 0;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
-      prefix += v;
-      if (flags) break;
-      look -= 32;
-    }
-    if (lane == 0) {
-      if (tile != 0) {
-        __threadfence();
-        atomicExch(&st.status[tile], (2ull << 62) | (unsigned long long)(prefix + block_sum));
-      }
-      s_prefix = prefix;
-    }
+    const long long prefix = scan_look_back(st, tile, block_sum);
+    if (lane == 0) s_prefix = prefix;
   }
   __syncthreads();
   long long run = s_prefix + warp_off + (incl - tsum);

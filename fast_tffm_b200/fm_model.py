@@ -16,6 +16,7 @@ queue runners, the gRPC parameter server, SavedModel export, summaries.
 """
 import collections
 import configparser
+import ctypes
 import glob
 import os
 
@@ -201,6 +202,9 @@ class Model(object):
         self._ahead_slot = 2     # parse_ahead alternates between buffer sets 1 and 2; set 0 serves inline steps / predict
         self._parse_stream = None
         self._bg_blocks, self._late, self._late_q = None, 0.0, collections.deque()
+        # claim path: which of its two forms runs (see _claim_form); "auto" measures, "rows" / "occurrences" pin it
+        self.claim_form = "auto"
+        self._form, self._form_q, self._form_age, self._rows_state = "rows", collections.deque(), 0, None
 
     # ---- INI config, same sections / keys as tffm/fm_model.py:367-475 -----------------
     def _get_config(self, config_file, verbose=True):
@@ -401,6 +405,51 @@ class Model(object):
             self._bg_blocks = self._bg_blocks * 2 if self._bg_blocks < 1024 else 0    # 0 = no cap
             self._late = 0.0
 
+    # ---- the two forms of the claim path ------------------------------------------------------------------
+    # "occurrences": fm_fused_score_scatter + fm_fused_adagrad_claim over the N occurrences (each tries to claim its
+    #                row; a row that occurs m times costs m - 1 lost claims of three row loads each);
+    # "rows":        the scorer also sets one bit per touched row (fm_peer_score_scatter with one rank), the bitmap
+    #                becomes an ascending row list (fm_peer_touched_rows) and the update walks the U distinct rows.
+    # One B200, cfg2 (profiles/r2_claim_forms_probe.txt): uniform ids (U = 0.93 N) 0.489 against 0.499 ms for the
+    # two table kernels, skewed ids (U = 0.10 N) 0.239 against 0.199 -- the bitmap scan costs what it costs, the lost
+    # claims scale with N - U.  So the model measures: a "rows" step leaves U and N behind, read a few steps later
+    # without blocking; U / N above ROWS_FORM_BELOW switches to "occurrences", and every FORM_PROBE_EVERY steps one
+    # "rows" step looks again.
+    ROWS_FORM_BELOW = 0.7
+    FORM_PROBE_EVERY = 512
+
+    def _claim_form(self):
+        if self.claim_form != "auto":
+            return self.claim_form
+        q = self._form_q
+        while q and q[0][0].query():
+            _, rec = q.popleft()
+            n_rows, nnz = int(rec[0]), int(rec[1])
+            if nnz > 0:
+                self._form = "rows" if n_rows < self.ROWS_FORM_BELOW * nnz else "occurrences"
+        if self._form == "occurrences":
+            self._form_age += 1
+            if self._form_age >= self.FORM_PROBE_EVERY:
+                self._form_age = 0
+                return "rows"
+        return self._form
+
+    def _rows_buffers(self, cap):
+        """bitmap, row list and scan scratch of the "rows" form (one set per model; grown with the batch capacity)"""
+        r = self._rows_state
+        if r is not None and r["cap"] >= cap:
+            return r
+        if r is not None:
+            torch.cuda.synchronize(self.device)          # enqueued kernels may still use the old set
+        lib, dev, v = load(), self.device, self.vocabulary_size
+        r = dict(cap=cap, touched=torch.zeros((v + 31) // 32, dtype=torch.int32, device=dev),
+                 rows=torch.empty(min(cap, v), dtype=torch.int64, device=dev),
+                 n_rows=torch.zeros(1, dtype=torch.int64, device=dev),
+                 ws=_lib.workspace(lib.fm_peer_touched_workspace(v), dev),
+                 rec=[torch.zeros(2, dtype=torch.int64).pin_memory() for _ in range(4)], at=0)
+        self._rows_state = r
+        return r
+
     def _gtab(self):
         if self.gtab is None:
             self.gtab = torch.zeros(self.vocabulary_size, self.gld, dtype=torch.float32, device=self.device)
@@ -590,22 +639,52 @@ class Model(object):
                 mark("parse_fill")
             else:
                 self._parse_unique(packed, b, mark, unique=False)
-            check(lib.fm_fused_score_scatter(
-                ptr(b["ids"]), None, ptr(b["vals"]), ptr(b["poses"]), ptr(b["labels"]), ptr(weights),
-                n_lines, k, ptr(self.table), tstride, self.factor_lambda, self.bias_lambda,
-                _lib.LOSS_KIND[self.loss_type], 0, ptr(b["pred"]), _off(b["status"], 6), _off(b["status"], 7),
-                ptr(gtab), gtab.stride(0), ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st),
-                "fm_fused_score_scatter")
+            form = self._claim_form()
+            rs = self._rows_buffers(b["cap"]) if form == "rows" else None
+            if rs is not None:
+                one = ctypes.c_void_p * 1                # the sharded scorer with a single rank: this GPU's arrays
+                check(lib.fm_peer_score_scatter(
+                    ptr(b["ids"]), ptr(b["vals"]), ptr(b["poses"]), ptr(b["labels"]), ptr(weights), n_lines, k, 1,
+                    one(self.table.data_ptr()), tstride, one(gtab.data_ptr()), gtab.stride(0),
+                    one(rs["touched"].data_ptr()), self.factor_lambda,
+                    self.bias_lambda, _lib.LOSS_KIND[self.loss_type], 0, ptr(b["pred"]), _off(b["status"], 6),
+                    _off(b["status"], 7), ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st),
+                    "fm_peer_score_scatter")
+            else:
+                check(lib.fm_fused_score_scatter(
+                    ptr(b["ids"]), None, ptr(b["vals"]), ptr(b["poses"]), ptr(b["labels"]), ptr(weights),
+                    n_lines, k, ptr(self.table), tstride, self.factor_lambda, self.bias_lambda,
+                    _lib.LOSS_KIND[self.loss_type], 0, ptr(b["pred"]), _off(b["status"], 6), _off(b["status"], 7),
+                    ptr(gtab), gtab.stride(0), ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st),
+                    "fm_fused_score_scatter")
             mark("score_scatter")
             ahead = None
             if prefetch is not None:
                 scored = torch.cuda.Event()
                 scored.record(torch.cuda.current_stream(self.device))
                 ahead = self.parse_ahead(prefetch, after=scored)
-            check(lib.fm_fused_adagrad_claim(
-                ptr(self.table), ptr(self.accum), tstride, ptr(b["ids"]), b["cap"], _off(b["status"], 1), k,
-                ptr(gtab), gtab.stride(0), self.learning_rate, self.factor_lambda, self.bias_lambda,
-                1.0 / self.batch_size, ptr(b["status"]), 0, st), "fm_fused_adagrad_claim")
+            if rs is not None:
+                # a batch that did not parse scattered nothing: the bitmap is empty, the list too, the update a no-op
+                check(lib.fm_peer_touched_rows(ptr(rs["touched"]), self.vocabulary_size, ptr(rs["rows"]),
+                                               rs["rows"].numel(), ptr(rs["n_rows"]), ptr(rs["ws"]), rs["ws"].numel(), st),
+                      "fm_peer_touched_rows")
+                check(lib.fm_fused_adagrad_claim(
+                    ptr(self.table), ptr(self.accum), tstride, ptr(rs["rows"]), rs["rows"].numel(), ptr(rs["n_rows"]), k,
+                    ptr(gtab), gtab.stride(0), self.learning_rate, self.factor_lambda, self.bias_lambda,
+                    1.0 / self.batch_size, ptr(b["status"]), 0, st), "fm_fused_adagrad_claim")
+                if self.claim_form == "auto":            # U and N of this step, for _claim_form a few steps on
+                    rec = rs["rec"][rs["at"] % len(rs["rec"])]
+                    rs["at"] += 1
+                    rec[0:1].copy_(rs["n_rows"], non_blocking=True)
+                    rec[1:2].copy_(b["status"][1:2], non_blocking=True)
+                    seen = torch.cuda.Event()
+                    seen.record(torch.cuda.current_stream(self.device))
+                    self._form_q.append((seen, rec))
+            else:
+                check(lib.fm_fused_adagrad_claim(
+                    ptr(self.table), ptr(self.accum), tstride, ptr(b["ids"]), b["cap"], _off(b["status"], 1), k,
+                    ptr(gtab), gtab.stride(0), self.learning_rate, self.factor_lambda, self.bias_lambda,
+                    1.0 / self.batch_size, ptr(b["status"]), 0, st), "fm_fused_adagrad_claim")
             mark("adagrad")
             b["ahead"] = ahead
             if parsed is not None:   # the buffer set may be refilled once this step is through with it

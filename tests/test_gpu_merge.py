@@ -114,3 +114,28 @@ def test_inbox_too_small_voids_the_step(criteo_lines):
                                                 200, inbox_cap=100)
     assert all(s & 7 == 5 for s in statuses if s != -1) and any(s != -1 for s in statuses)   # FM_PARSE_E_CAPACITY
     np.testing.assert_array_equal(table, flat)           # nobody merged: the flag said the step was void
+
+
+@pytest.mark.parametrize("rows,density", [(1, 1.0), (31, 0.5), (1000, 0.0), (4096 * 32 + 5, 0.14), (1 << 24, 0.14),
+                                           (3_000_001, 0.9), (70_000, 1.0)])
+def test_touched_rows_lists_the_bitmap_in_ascending_order(rows, density):
+    """fm_peer_touched_rows (owner side of the atomics exchange): bitmap -> ascending row list, bitmap cleared"""
+    lib, dev = _lib.load(), torch.device(DEV)
+    rng = np.random.default_rng(rows)
+    want = np.flatnonzero(rng.random(rows) < density).astype(np.int64)
+    words = (rows + 31) // 32
+    host = np.zeros(words, dtype=np.uint32)
+    np.bitwise_or.at(host, want >> 5, np.uint32(1) << (want & 31).astype(np.uint32))
+    bits = torch.from_numpy(host.view(np.int32)).to(dev)
+    ws = _lib.workspace(lib.fm_peer_touched_workspace(rows), dev)
+    for cap in (rows, max(1, len(want) // 2)):
+        b = bits.clone()
+        out = torch.full((cap,), -7, dtype=torch.int64, device=dev)
+        n = torch.zeros(1, dtype=torch.int64, device=dev)
+        ws.fill_(0x55)                                   # whatever the last call left behind
+        check(lib.fm_peer_touched_rows(ptr(b), rows, ptr(out), cap, ptr(n), ptr(ws), ws.numel(), stream()), "touched_rows")
+        torch.cuda.synchronize()
+        assert int(n) == len(want)
+        kept = min(cap, len(want))
+        np.testing.assert_array_equal(out[:kept].cpu().numpy(), want[:kept])
+        assert (out[kept:] == -7).all() and int(b.abs().sum()) == 0

@@ -587,13 +587,16 @@ def test_train_steps_any_factor_num(k):
     flat = rng.uniform(-0.05, 0.05, (vocab, k + 1)).astype(np.float32)
     kw = dict(factor_lambda=3e-3, bias_lambda=2e-3, loss_type="logistic")
     w = rng.uniform(0.5, 2.0, bs).astype(np.float32)
-    combos = [("claim", "interleaved"), ("claim", "split"), ("fused", "split"), ("composed", "split"), ("claim", "pair")]
+    combos = [("claim", "interleaved"), ("claim", "split"), ("fused", "split"), ("composed", "split"), ("claim", "pair"),
+              ("claim/rows", "interleaved"), ("claim/rows", "split")]
     if (k + 4) // 4 <= 96:      # the sorted path's lane groups cover rows of up to 96 chunks
         combos += [("sorted", "pair"), ("sorted", "interleaved"), ("sorted", "split")]
     for path, layout in combos:
         ref = O.RefModel(vocab, 7, k, flat, batch_size=bs, lr=0.05, init_acc=0.1, **kw)
         m = Model(vocabulary_size=vocab, vocabulary_block_num=7, factor_num=k, batch_size=bs, learning_rate=0.05,
                   adagrad_init_accumulator=0.1, **kw).build(DEV, init_table=flat, layout=layout)
+        path, _, form = path.partition("/")
+        m.claim_form = form or "occurrences"
         for step in range(2):
             sl = slice(step * bs, (step + 1) * bs)
             e = ref.train_step(lines[sl], w if step else None)
@@ -616,9 +619,10 @@ _SHAPES = {
 }
 
 
-@pytest.mark.parametrize("path", [p for p in PATHS if p != "composed"])
+@pytest.mark.parametrize("path", [p for p in PATHS if p != "composed"] + ["claim/rows", "claim/occurrences"])
 @pytest.mark.parametrize("shape", sorted(_SHAPES))
 def test_whole_step_at_baseline_shapes(shape, path):
+    path, _, form = path.partition("/")              # the claim path's two forms, pinned (default: it measures)
     c = _SHAPES[shape]
     vocab, k, bs = c["vocab"], c["k"], c["bs"]
     rng = np.random.default_rng(7)
@@ -627,6 +631,8 @@ def test_whole_step_at_baseline_shapes(shape, path):
     ref = O.RefModel(vocab, 1, k, flat, batch_size=bs, hash_feature_id=c["hashed"], lr=0.01, init_acc=0.1, **kw)
     m = Model(vocabulary_size=vocab, vocabulary_block_num=1, factor_num=k, batch_size=bs, hash_feature_id=c["hashed"],
               learning_rate=0.01, adagrad_init_accumulator=0.1, **kw).build(DEV, init_table=flat)
+    if form:
+        m.claim_form = form
     touched = []
     steps = 2
     for step in range(steps):
@@ -791,6 +797,40 @@ def test_host_batch_pipeline_matches_step_by_step(criteo_lines):
     for i, r in enumerate(more):
         np.testing.assert_allclose(r.loss(), b.train_step(batches[i][2], None if batches[i][1] is None else batches[i][1].numpy()),
                                    rtol=1e-6)
+
+
+def test_claim_path_picks_its_form_from_the_ids_it_sees():
+    """claim_form = "auto": batches whose ids repeat a lot run the row-list form, batches of distinct ids the
+    occurrence walk; the switch follows the ids with a few steps' delay and never changes the result"""
+    rng = np.random.default_rng(77)
+    vocab, k, bs = 50021, 8, 256
+
+    def batch(hot):
+        out = []
+        for _ in range(bs):
+            ids = rng.integers(0, 30 if hot else vocab, 20)
+            out.append(("1 " + " ".join("%d:%.2f" % (t, rng.normal()) for t in ids)).encode())
+        return out
+    flat = rng.uniform(-0.01, 0.01, (vocab, k + 1)).astype(np.float32)
+    ref = O.RefModel(vocab, 1, k, flat, batch_size=bs, lr=0.05, init_acc=0.1, loss_type="logistic")
+    m = Model(vocabulary_size=vocab, factor_num=k, batch_size=bs, learning_rate=0.05, adagrad_init_accumulator=0.1,
+              loss_type="logistic").build(DEV, init_table=flat)
+    assert m.claim_form == "auto"
+    forms = []
+    for step in range(12):
+        lines = batch(hot=step < 6)
+        e = ref.train_step(lines, None)
+        np.testing.assert_allclose(m.train_step(lines), e["loss"], rtol=RTOL)     # train_step synchronises
+        forms.append(m._form)
+    assert forms[2:6] == ["rows"] * 4 and forms[-3:] == ["occurrences"] * 3, forms
+    _assert_model_state(m, ref, k, 0.05, 12)
+    m.FORM_PROBE_EVERY = 2                       # a look at the ids every other step: back to the row list
+    for step in range(6):
+        lines = batch(hot=True)
+        e = ref.train_step(lines, None)
+        np.testing.assert_allclose(m.train_step(lines), e["loss"], rtol=RTOL)
+    assert m._form == "rows"
+    _assert_model_state(m, ref, k, 0.05, 18)
 
 
 def test_predict_with_parse_ahead_equals_predict(criteo_lines):
