@@ -132,9 +132,30 @@ def cfg5_multi(args):
             if mode == "sharded":
                 m = PeerShardedModel(cfg, device=dev, max_nnz_per_line=39).build(seed=0)
                 run, status = (lambda b: m.predict_async(data[b])), (lambda: m._slots[0]["status"])
+                if not args.no_parse_ahead:      # a stream of batches: the next one's parse under this one's scorer
+                    os.environ.setdefault("FM_AHEAD_BLOCKS", "0")
+                    state = {}
+
+                    def run(b, m=m, state=state):
+                        if state.get("b") != b:
+                            state.update(b=b, ahead=m.parse_ahead(data[b]))
+                        nxt = m.parse_ahead(data[b])
+                        m.predict_async(data[b], parsed=state["ahead"])
+                        state["ahead"] = nxt
+                    status = lambda: m._slots[1]["status"]
             else:
                 m = cfg.build(dev, seed=0, max_nnz_per_line=39, layout="split")
                 run, status = (lambda b: m.predict_async(data[b])), (lambda: m._bufs["status"])
+                if not args.no_parse_ahead:
+                    m._bg_blocks = 0
+                    state = {}
+
+                    def run(b, m=m, state=state):
+                        if state.get("b") != b:
+                            state.update(b=b, ahead=m.parse_ahead(data[b], sort=False))
+                        nxt = m.parse_ahead(data[b], sort=False)
+                        m.predict_async(data[b], parsed=state["ahead"])
+                        state["ahead"] = nxt
             for b in sizes:
                 steps = max(3, min(args.steps, int(2e6 // b) + 3))
                 for _ in range(3):
@@ -208,6 +229,7 @@ if __name__ == "__main__":
     ap.add_argument("which", choices=["cfg4", "cfg5"])
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--no-parse-ahead", action="store_true", help="cfg5 at G > 1: parse each batch inline")
     ap.add_argument("--path", default="claim", choices=["claim", "sorted"], help="cfg4: training path")
     a = ap.parse_args()
     {"cfg4": cfg4, "cfg5": cfg5}[a.which](a)

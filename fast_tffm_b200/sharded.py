@@ -646,15 +646,23 @@ class PeerShardedModel:
             raise FmParseError(first & 7, first >> 3, line)
         return float(out[0].item())
 
-    def predict_async(self, lines):
-        """scores of this rank's lines in b["pred"], rows read from whichever GPU owns them; no host sync"""
+    def predict_async(self, lines, parsed=None):
+        """scores of this rank's lines in b["pred"], rows read from whichever GPU owns them; no host sync.
+        parsed: handle from parse_ahead(lines) for THIS batch (its parse ran under the previous batch's scorer)"""
         lib, st, cfg, k, g = self.lib, stream(), self.cfg, self.cfg.factor_num, self.world
-        packed, b = self._parse(lines)
+        if parsed is not None:
+            torch.cuda.current_stream(self.device).wait_event(parsed["done"])
+            packed, b = parsed["packed"], parsed["b"]
+        else:
+            packed, b = self._parse(lines)
         check(lib.fm_peer_score_scatter(
             ptr(b["ids"]), ptr(b["vals"]), ptr(b["poses"]), None, None, packed.n_lines, k, g, self._table_bases,
             self.ld, None, self.gld, None, cfg.factor_lambda, cfg.bias_lambda, 0, 0, ptr(b["pred"]), ptr(b["scal"]),
             _at(b["scal"], 1), ptr(b["status"]), ptr(b["ws_fused"]), b["ws_fused"].numel(), st),
             "fm_peer_score_scatter")
+        if parsed is not None:
+            b["free"] = torch.cuda.Event()
+            b["free"].record(torch.cuda.current_stream(self.device))
         return packed, b
 
     def predict(self, lines):

@@ -30,6 +30,10 @@ def run(rank, world, port, backend, lines, weights, cfg_kw, init, steps, out_dir
         w = None if weights is None or s % 2 else np.float32(weights[lo:lo + per])
         losses.append(m.train_step(lines[lo:lo + per], w))
     pred = m.predict(lines[rank * per:(rank + 1) * per]).cpu().numpy()
+    if mode == "peer":      # the same scores when the batch's parse ran ahead on the side stream
+        mine = lines[rank * per:(rank + 1) * per]
+        _, b = m.predict_async(mine, parsed=m.parse_ahead(mine))
+        assert np.array_equal(b["pred"][:per].cpu().numpy(), pred)
     full = m.gather_full_table().cpu().numpy()
     if rank == 0:
         np.save(os.path.join(out_dir, "table.npy"), full)
