@@ -445,8 +445,7 @@ def run_ours(args):
         "cpu_baseline": None if base is None else {k_: base[k_] for k_ in ("value", "unit", "cores", "kind", "sample", "stage_ms")},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / args.steps},
-        # the claim path's row-list form (skewed ids) launches one more kernel per step: the bitmap scan
-        "gpu_launches": (KERNELS_PER_STEP[fused] + (1 if fused == "claim" and m._form == "rows" else 0)) * args.steps,
+        "gpu_launches": KERNELS_PER_STEP[fused] * args.steps,      # either form of the claim path: the same count
         "claim_form": m._form if fused == "claim" else None,
         "path": fused, "layout": args.layout, "unique_per_step": n_unique, "parse_ahead": ahead_on,
         "host_affinity": affinity, "clocks": clocks,

@@ -51,6 +51,8 @@ _SIGNATURES = {
                                          _vp, _vp, _vp, _vp, _i64, _vp, _vp, _sz, _vp]),
     "fm_fused_adagrad_claim": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _f32, _f32, _f32, _f32, _vp,
                                          _i32, _vp]),
+    "fm_fused_adagrad_bitmap": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _i64, _vp, _i64, _f32, _f32, _f32, _f32, _vp, _i32,
+                                          _vp, _vp]),
     "fm_peer_score_scatter": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _i64, _vp, _f32, _f32,
                                         _i32, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "fm_peer_sync_bytes": (_sz, []),

@@ -393,6 +393,17 @@ int fm_peer_merge_update(float* table, float* accum, int64_t table_ld, int64_t s
                          void* stream);
 int fm_peer_touched_rows(uint32_t* touched, int64_t shard_rows, int64_t* rows, int64_t capacity,
                          int64_t* n_rows, void* workspace, size_t workspace_bytes, void* stream);
+/* fm_peer_touched_rows + fm_fused_adagrad_claim in one kernel, and what the training step uses: the update walks the
+ * bitmap itself (a warp per 1024 rows: clears the words, lists the set bits in shared memory, its lane groups take the
+ * rows), so every touched row is visited once, in ascending order, with no claim atomics, no scan and no row list.
+ * touched: the bitmap fm_peer_score_scatter filled (n_rows bits; any number of ranks, one included: the single-GPU
+ * training step is fm_peer_score_scatter with one rank + this call).  guard / discard_on_guard as in
+ * fm_fused_adagrad_claim.  rows_seen (optional, device): the number of rows visited is ADDED to it (zero it to get
+ * the step's count of distinct rows).  factor_num <= 378 (wider rows: the two-call form above). */
+int fm_fused_adagrad_bitmap(float* table, float* accum, int64_t table_ld, uint32_t* touched, int64_t n_rows,
+                            int64_t factor_num, float* gtab, int64_t gtab_ld, float learning_rate,
+                            float factor_lambda, float bias_lambda, float reg_grad, const uint64_t* guard,
+                            int discard_on_guard, int64_t* rows_seen, void* stream);
 
 #ifdef __cplusplus
 }

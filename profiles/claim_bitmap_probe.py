@@ -1,6 +1,6 @@
 """Single GPU: the claim path's two kernels as Model runs them (the update walks the N occurrences and claims rows)
 against the sharded step's form run with ONE rank (the scorer also sets a bit per touched row; the bitmap becomes a
-row list; the update walks the U distinct rows).  Question: which form pays on one GPU -- for uniform ids
+row list; the update walks the U distinct rows) and against the update walking the bitmap itself.  Question: which form pays on one GPU -- for uniform ids
 (U = 0.93 N) and for skewed ones (U << N)?  (r2_claim_forms_probe.txt also has a third form, tried and removed.)
     python profiles/claim_bitmap_probe.py [uniform|zipf] [reps]"""
 import ctypes
@@ -74,6 +74,16 @@ def row_listed(d):
     yield "update"
 
 
+def bitmap_walk(d):
+    check(lib.fm_peer_score_scatter(ptr(d["ids"]), ptr(d["vals"]), ptr(d["poses"]), ptr(d["labels"]), None, b, k, 1,
+                                    table_bases, block, gtab_bases, block, touched_bases, 1e-5, 1e-5, 0, b, ptr(pred),
+                                    ptr(scal), at(scal, 2), None, ptr(ws), ws.numel(), stream()), "peer_score_scatter")
+    yield "score_scatter"
+    check(lib.fm_fused_adagrad_bitmap(ptr(table), ptr(accum), block, ptr(touched), rows, k, ptr(gtab), block, 0.01, 1e-5,
+                                      1e-5, 1.0 / b, None, 0, None, stream()), "adagrad_bitmap")
+    yield "update"
+
+
 def timed(form):
     for d in batches:                      # warm-up
         for _ in form(d):
@@ -98,7 +108,7 @@ def timed(form):
 
 
 out = {"ids": dist, "nnz": batches[0]["nnz"], "distinct_rows": batches[0]["uniq"],
-       "walk_occurrences": timed(occurrences), "walk_row_list": timed(row_listed)}
-for f in ("walk_occurrences", "walk_row_list"):
+       "walk_occurrences": timed(occurrences), "walk_row_list": timed(row_listed), "walk_bitmap": timed(bitmap_walk)}
+for f in ("walk_occurrences", "walk_row_list", "walk_bitmap"):
     out[f]["sum"] = round(sum(out[f].values()), 4)
 print(json.dumps(out))

@@ -139,3 +139,54 @@ def test_touched_rows_lists_the_bitmap_in_ascending_order(rows, density):
         kept = min(cap, len(want))
         np.testing.assert_array_equal(out[:kept].cpu().numpy(), want[:kept])
         assert (out[kept:] == -7).all() and int(b.abs().sum()) == 0
+
+
+@pytest.mark.parametrize("k", [4, 16, 64])
+def test_bitmap_update_equals_list_update_and_honours_the_guard(k):
+    """fm_fused_adagrad_bitmap against fm_peer_touched_rows + fm_fused_adagrad_claim on the same accumulated rows;
+    a tripped guard with discard_on_guard throws the sums away and leaves the table alone"""
+    lib, dev = _lib.load(), torch.device(DEV)
+    rows, part = 70_001, (k + 3 + 3) // 4 * 4
+    rng = np.random.default_rng(k)
+    touched_rows = np.unique(rng.integers(0, rows, 9000))
+    words = (rows + 31) // 32
+    host_bits = np.zeros(words, dtype=np.uint32)
+    np.bitwise_or.at(host_bits, touched_rows >> 5, np.uint32(1) << (touched_rows & 31).astype(np.uint32))
+
+    def fresh():
+        g = torch.Generator(device=dev).manual_seed(5)
+        store = torch.zeros(rows, 3 * part, device=dev)
+        store[:, :k + 1].uniform_(-0.1, 0.1, generator=g)
+        store[:, part:2 * part] = 0.1
+        idx = torch.from_numpy(touched_rows).to(dev)
+        sums = torch.zeros(len(touched_rows), part, device=dev)
+        sums[:, :k + 3].uniform_(-1.0, 1.0, generator=g)
+        sums[:, k + 2] = torch.randint(1, 5, (len(touched_rows),), generator=g, device=dev).float()      # cnt
+        store[idx, 2 * part:] = sums
+        return store, torch.from_numpy(host_bits.view(np.int32)).to(dev)
+    args = (0.05, 2e-3, 1e-3, 1.0 / 256)
+    a, bits_a = fresh()
+    lst = torch.empty(rows, dtype=torch.int64, device=dev)
+    n = torch.zeros(1, dtype=torch.int64, device=dev)
+    ws = _lib.workspace(lib.fm_peer_touched_workspace(rows), dev)
+    check(lib.fm_peer_touched_rows(ptr(bits_a), rows, ptr(lst), rows, ptr(n), ptr(ws), ws.numel(), stream()), "touched")
+    check(lib.fm_fused_adagrad_claim(ptr(a), _at(a, part), 3 * part, ptr(lst), rows, ptr(n), k, _at(a, 2 * part), 3 * part,
+                                     *args, None, 0, stream()), "claim")
+    b, bits_b = fresh()
+    seen = torch.zeros(1, dtype=torch.int64, device=dev)
+    check(lib.fm_fused_adagrad_bitmap(ptr(b), _at(b, part), 3 * part, ptr(bits_b), rows, k, _at(b, 2 * part), 3 * part,
+                                      *args, None, 0, ptr(seen), stream()), "bitmap")
+    torch.cuda.synchronize()
+    assert int(seen) == len(touched_rows) == int(n) and int(bits_b.abs().sum()) == 0
+    assert torch.equal(a, b) and not b[:, 2 * part:].any()
+    c, bits_c = fresh()
+    before = c.clone()
+    bad = torch.tensor([5], dtype=torch.int64, device=dev)          # a status word that says "a line failed"
+    check(lib.fm_fused_adagrad_bitmap(ptr(c), _at(c, part), 3 * part, ptr(bits_c), rows, k, _at(c, 2 * part), 3 * part,
+                                      *args, ptr(bad), 0, None, stream()), "bitmap, guard: no-op")
+    torch.cuda.synchronize()
+    assert torch.equal(c, before) and int(bits_c.abs().sum()) > 0
+    check(lib.fm_fused_adagrad_bitmap(ptr(c), _at(c, part), 3 * part, ptr(bits_c), rows, k, _at(c, 2 * part), 3 * part,
+                                      *args, ptr(bad), 1, None, stream()), "bitmap, guard: discard")
+    torch.cuda.synchronize()
+    assert torch.equal(c[:, :2 * part], before[:, :2 * part]) and not c[:, 2 * part:].any() and int(bits_c.abs().sum()) == 0
