@@ -140,3 +140,33 @@ def test_optimizer_key_is_an_extension_with_a_safe_default(tmp_path):
     (tmp_path / "d.cfg").write_text(cfg.replace("adagrad.initial_accumulator = 0.1", "adagrad.initial_accumulator = 0"))
     with pytest.raises(ValueError, match="initial_accumulator_value must be positive"):
         Model(str(tmp_path / "d.cfg"))
+
+
+def test_claim_form_follows_the_measured_share_of_distinct_rows():
+    """Model._claim_form: the records (distinct rows U, occurrences N) a row-form step left behind are read once their
+    event has passed; U / N picks the form; the occurrence form looks again every FORM_PROBE_EVERY steps"""
+    from fast_tffm_b200.fm_model import Model
+
+    class Ev:
+        def __init__(self, done):
+            self.done = done
+
+        def query(self):
+            return self.done
+    m = Model(vocabulary_size=1000, factor_num=4, batch_size=8)
+    assert m.claim_form == "auto" and m._claim_form() == "rows"          # the first step measures
+    pending = Ev(False)
+    m._form_q.append((pending, torch.tensor([950, 1000])))
+    assert m._claim_form() == "rows"                                      # not there yet: nothing is read, nothing blocks
+    pending.done = True
+    assert m._claim_form() == "occurrences" and not m._form_q             # U / N = 0.95: the occurrence walk
+    m._form_q.append((Ev(True), torch.tensor([0, 0])))                    # a void step says nothing
+    assert m._claim_form() == "occurrences"
+    m.FORM_PROBE_EVERY = 4
+    m._form_age = 0
+    forms = [m._claim_form() for _ in range(8)]
+    assert forms == ["occurrences"] * 3 + ["rows"] + ["occurrences"] * 3 + ["rows"]
+    m._form_q.append((Ev(True), torch.tensor([100, 1000])))               # ids repeat: back to the row form, and it stays
+    assert [m._claim_form() for _ in range(3)] == ["rows"] * 3
+    m.claim_form = "occurrences"                                          # pinned: no measuring
+    assert m._claim_form() == "occurrences"
