@@ -578,6 +578,76 @@ FMO_API void fmo_adagrad_mod_f32(float* blocks, float* acc_blocks, int64_t vocab
 }
 
 /*
+ * The optimizer's row loop the way the TF runtime schedules it: AdagradOptimizer.minimize over nb block variables is
+ * one SparseApplyAdagrad per block (tffm/fm_model.py:269-291, :341-348), and independent ops run side by side on the
+ * inter-op pool.  One task per block, each serial over its rows like the op kernel; the result equals the serial loop
+ * (distinct rows, disjoint blocks).  The lookup stays the serial gather: as per-block tasks writing one output it was
+ * SLOWER on the 16-core box (119 against 85 ms: the threads contend on the first-touch page faults of the 161 MB
+ * result), and TF's form adds a dynamic_stitch copy on top, so the serial loop is the kinder estimate.
+ */
+typedef struct {
+  float* blocks; float* acc; int64_t vocab, nb, k;
+  const int64_t* ori; const float* grad; float lr;
+  const int64_t* start;      /* [nb + 1]: block b owns order[start[b] .. start[b + 1]) */
+  const int64_t* order;      /* positions 0..u-1 grouped by block (tf.dynamic_partition's output, serial like the op) */
+} fmo_block_ctx;
+static void partition_by_block(const int64_t* ori, int64_t u, int64_t nb, int64_t* start, int64_t* order) {
+  for (int64_t b = 0; b <= nb; ++b) start[b] = 0;
+  for (int64_t i = 0; i < u; ++i) ++start[ori[i] % nb + 1];
+  for (int64_t b = 0; b < nb; ++b) start[b + 1] += start[b];
+  int64_t* at = (int64_t*)malloc(sizeof(int64_t) * (size_t)nb);
+  for (int64_t b = 0; b < nb; ++b) at[b] = start[b];
+  for (int64_t i = 0; i < u; ++i) order[at[ori[i] % nb]++] = i;
+  free(at);
+}
+static void adagrad_block_task(int64_t lo, int64_t hi, void* p) {
+  const fmo_block_ctx* c = (const fmo_block_ctx*)p;
+  const int64_t rows = c->vocab / c->nb + 1, w = c->k + 1;
+  for (int64_t blk = lo; blk < hi; ++blk)
+    for (int64_t j = c->start[blk]; j < c->start[blk + 1]; ++j) {
+      const int64_t i = c->order[j];
+      const int64_t base = (blk * rows + c->ori[i] / c->nb) * w;
+      for (int64_t col = 0; col < w; ++col) {
+        const float g = c->grad[i * w + col];
+        const float a = c->acc[base + col] + g * g;
+        c->acc[base + col] = a;
+        c->blocks[base + col] -= c->lr * g / sqrtf(a);
+      }
+    }
+}
+/* one thread per task (parallel_for keeps small n serial: right for its per-element jobs, wrong for ten heavy ones) */
+static void parallel_tasks(int64_t n, int nthreads, void (*fn)(int64_t, int64_t, void*), void* ctx) {
+  pthread_t* th = (pthread_t*)malloc(sizeof(pthread_t) * (size_t)nthreads);
+  fmo_job* jobs = (fmo_job*)malloc(sizeof(fmo_job) * (size_t)nthreads);
+  for (int t = 0; t < nthreads; ++t) {
+    jobs[t].fn = fn;
+    jobs[t].ctx = ctx;
+    jobs[t].lo = n * t / nthreads;
+    jobs[t].hi = n * (t + 1) / nthreads;
+    pthread_create(&th[t], NULL, fmo_thread_main, &jobs[t]);
+  }
+  for (int t = 0; t < nthreads; ++t) pthread_join(th[t], NULL);
+  free(th);
+  free(jobs);
+}
+static void by_block(fmo_block_ctx* c, int64_t u, int nthreads, void (*task)(int64_t, int64_t, void*)) {
+  int64_t* start = (int64_t*)malloc(sizeof(int64_t) * (size_t)(c->nb + 1));
+  int64_t* order = (int64_t*)malloc(sizeof(int64_t) * (size_t)(u + 1));
+  partition_by_block(c->ori, u, c->nb, start, order);
+  c->start = start;
+  c->order = order;
+  const int tasks = (int)(c->nb < nthreads ? c->nb : nthreads);
+  if (tasks <= 1) task(0, c->nb, c); else parallel_tasks(c->nb, tasks, task, c);
+  free(order);
+  free(start);
+}
+static void adagrad_by_block(float* blocks, float* acc, int64_t vocab, int64_t nb, int64_t k, const int64_t* ori,
+                             int64_t u, const float* grad, float lr, int nthreads) {
+  fmo_block_ctx c = {blocks, acc, vocab, nb, k, ori, grad, lr, NULL, NULL};
+  by_block(&c, u, nthreads, adagrad_block_task);
+}
+
+/*
  * One whole reference train step on the CPU, timed per stage (seconds in
  * t[0..6]: parse, unique+poses, lookup, score, loss, grad, adagrad), the way
  * tffm/fm_model.py strings the ops together (:69-73, :291-293, :311-348).
@@ -634,7 +704,7 @@ FMO_API double fmo_train_step_faithful(const uint8_t* text, const int64_t* off, 
                         1.0f / (float)cfg_batch, u, g, nthreads);
       double t6 = now_s();
       t[5] = t6 - t5;
-      fmo_adagrad_mod_f32(blocks, acc_blocks, vocab, nb, k, ori, u, g, lr);
+      adagrad_by_block(blocks, acc_blocks, vocab, nb, k, ori, u, g, lr, nthreads);
       t[6] = now_s() - t6;
       free(g);
     }
