@@ -13,6 +13,7 @@ parser and scorer kernels as `predict` (no Adagrad state, a third of the trainin
 """
 import json
 import os
+import re
 
 import numpy as np
 import torch
@@ -21,6 +22,7 @@ from .fm_model import Model
 from .fm_ops import FmParseError
 
 META, TABLE = "fm_serving.json", "fm_table.f32"
+_PAIRS = re.compile(r"[^ :]+:[^ :]+(?: [^ :]+:[^ :]+)*")      # "id:val id:val ...": one colon in every token
 _ROWS_PER_WRITE = 1 << 20
 
 
@@ -59,10 +61,8 @@ class ServingScorer:
         an empty line scores 0 (the dense formula over nothing)."""
         lines = []
         for i, line in enumerate(data_lines):
-            toks = line.split(" ") if line else []
-            for t in toks:
-                if t.count(":") != 1:                    # tf.reshape(split(':').values, [-1, 2]) fails on these
-                    raise FmParseError(2, i, line)
+            if line and _PAIRS.fullmatch(line) is None:  # tf.reshape(split(':').values, [-1, 2]) fails on these
+                raise FmParseError(2, i, line)
             lines.append("0 " + line if line else "0")
         if not lines:
             return torch.empty(0, dtype=torch.float32, device=self.model.device)
