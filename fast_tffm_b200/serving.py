@@ -61,7 +61,8 @@ class ServingScorer:
         an empty line scores 0 (the dense formula over nothing)."""
         lines = []
         for i, line in enumerate(data_lines):
-            if line and _PAIRS.fullmatch(line) is None:  # tf.reshape(split(':').values, [-1, 2]) fails on these
+            line = " ".join(t for t in line.split(" ") if t)     # tf.string_split(' ') skips empty tokens
+            if line and _PAIRS.fullmatch(line) is None:          # tf.reshape(split(':').values, [-1, 2]) fails on these
                 raise FmParseError(2, i, line)
             lines.append("0 " + line if line else "0")
         if not lines:
